@@ -1,0 +1,79 @@
+"""ctypes binding of the C ABI declared in include/burgers_b200.h.
+
+The shared library is built in-tree (``finitedifference_b200/_burgers_b200.so``) by
+``__graft_entry__.build()`` / ``finitedifference_b200._build``.  There is no CPU fallback:
+if the library is missing, loading raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "_burgers_b200.so")
+
+BFD_OK = 0
+ERRORS = {-1: "BFD_EINVAL", -2: "BFD_ECUDA", -3: "BFD_EWORKSPACE", -4: "BFD_ETIMEOUT",
+          -5: "BFD_ENOTCONVERGED"}
+
+
+class FomDesc(C.Structure):
+    """``bfd_fom_desc``."""
+    _fields_ = [("nx", C.c_int32), ("ny", C.c_int32), ("batch", C.c_int32),
+                ("num_steps", C.c_int32), ("max_its", C.c_int32),
+                ("cells_per_lane", C.c_int32), ("rel_tol", C.c_double)]
+
+
+class FomCoef(C.Structure):
+    """``bfd_fom_coef``."""
+    _fields_ = [(n, C.c_void_p) for n in ("cx", "cxl", "cy", "cyd", "src", "lbc")]
+
+
+_P = C.c_void_p
+# name -> (restype, argtypes): every symbol include/burgers_b200.h declares
+SIGNATURES = {
+    "bfd_abi_version": (C.c_int, []),
+    "bfd_last_cuda_error": (C.c_char_p, []),
+    "bfd_launch_count": (C.c_uint64, []),
+    "bfd_fom_workspace_bytes": (C.c_size_t, [C.POINTER(FomDesc)]),
+    "bfd_fom_init": (C.c_int, [C.POINTER(FomDesc), _P, C.c_size_t, _P]),
+    "bfd_fom_set_initial": (C.c_int, [C.POINTER(FomDesc), _P, _P, C.c_size_t, _P]),
+    "bfd_fom_run": (C.c_int, [C.POINTER(FomDesc), _P, C.POINTER(FomCoef), _P, _P]),
+    "bfd_fom_export": (C.c_int, [C.POINTER(FomDesc), _P, C.c_int, C.c_int, C.c_int, C.c_int,
+                                 C.c_size_t, _P, _P]),
+    "bfd_fom_diagnostics": (C.c_int, [C.POINTER(FomDesc), _P, _P, _P, _P]),
+    "bfd_residual": (C.c_int, [C.c_int, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+}
+
+
+class BurgersError(RuntimeError):
+    pass
+
+
+def bind(path: str) -> C.CDLL:
+    """Load a library exporting the ABI and attach the signatures."""
+    if not os.path.exists(path):
+        raise BurgersError(
+            f"{path} not found: build the CUDA extension first "
+            "(python -c 'import __graft_entry__ as g; g.build()'); there is no CPU fallback")
+    lib = C.CDLL(path)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError if the symbol is missing: loud by design
+        fn.restype, fn.argtypes = res, args
+    return lib
+
+
+_lib = None
+
+
+def get_lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        _lib = bind(LIB_PATH)
+    return _lib
+
+
+def check(rc: int, lib: C.CDLL, what: str) -> None:
+    if rc != BFD_OK:
+        detail = lib.bfd_last_cuda_error().decode() if rc == -2 else ""
+        raise BurgersError(f"{what} failed: {ERRORS.get(rc, rc)} {detail}")

@@ -1,0 +1,134 @@
+"""Batched full-order solver on one B200: host side of the FOM path.
+
+``FomSolver`` owns the device workspace of ``bfd_fom_*`` (include/burgers_b200.h) for a batch
+of parameter samples and mirrors what ``inviscid_burgers_implicit2D``
+(reference hypernet2D.py:72-131) does for one.  PyTorch is used for device memory and streams
+only; all arithmetic happens in the hand-written kernels of csrc/fom.cu.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from .discretisation import parameter_terms, stencil_coefficients
+
+
+def _require_cuda(device=None) -> torch.device:
+    if not torch.cuda.is_available():
+        raise _lib.BurgersError("finitedifference_b200 needs a CUDA device (sm_100a); there is no CPU path")
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    if dev.type != "cuda":
+        raise _lib.BurgersError(f"device must be a CUDA device, got {dev}")
+    return dev
+
+
+def _dev(a: np.ndarray, device) -> torch.Tensor:
+    return torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(device, non_blocking=False)
+
+
+class FomSolver:
+    """Advance ``len(mus)`` samples ``num_steps`` trapezoidal steps with Newton (rel. tol 1e-12).
+
+    Snapshots stay resident in HBM (skewed strip layout, csrc/common.cuh) until exported.
+    """
+
+    def __init__(self, grid_x, grid_y, dt, num_steps, mus, device=None, cells_per_lane=1,
+                 max_its=100, rel_tol=1e-12):
+        self.lib = _lib.get_lib()
+        self.device = _require_cuda(device)
+        self.grid_x = np.asarray(grid_x, dtype=np.float64)
+        self.grid_y = np.asarray(grid_y, dtype=np.float64)
+        self.mus = np.atleast_2d(np.asarray(mus, dtype=np.float64))
+        self.nx, self.ny = self.grid_x.size - 1, self.grid_y.size - 1
+        self.batch, self.num_steps, self.dt = self.mus.shape[0], int(num_steps), float(dt)
+        self.desc = _lib.FomDesc(self.nx, self.ny, self.batch, self.num_steps, int(max_its),
+                                 int(cells_per_lane), float(rel_tol))
+        nbytes = self.lib.bfd_fom_workspace_bytes(C.byref(self.desc))
+        if nbytes == 0:
+            raise _lib.BurgersError("invalid FOM description")
+        self.workspace_bytes = nbytes
+        with torch.cuda.device(self.device):
+            self.ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+            cx, cxl, cy, cyd = stencil_coefficients(self.grid_x, self.grid_y, self.dt)
+            src, lbc = parameter_terms(self.grid_x, self.grid_y, self.dt, self.mus)
+            self._coef_t = [_dev(a, self.device) for a in (cx, cxl, cy, cyd, src, lbc)]
+            self.coef = _lib.FomCoef(*[t.data_ptr() for t in self._coef_t])
+            self._pinned = torch.zeros(16, dtype=torch.int32).pin_memory()
+        self.sweeps_launched = 0
+        self._ready = False
+
+    # -- helpers ---------------------------------------------------------------------------
+    def _stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _check(self, rc, what):
+        _lib.check(rc, self.lib, what)
+
+    # -- API -------------------------------------------------------------------------------
+    def set_initial(self, w0) -> None:
+        """``w0``: (2N,) broadcast to every sample, or (batch, 2N); NumPy or CUDA tensor."""
+        n2 = 2 * self.nx * self.ny
+        with torch.cuda.device(self.device):
+            if isinstance(w0, torch.Tensor):
+                w = w0.to(self.device, dtype=torch.float64).contiguous()
+            else:
+                w = _dev(np.asarray(w0, dtype=np.float64), self.device)
+            if w.numel() == n2:
+                stride = 0
+            elif w.numel() == n2 * self.batch:
+                stride = n2
+            else:
+                raise ValueError(f"w0 has {w.numel()} entries, expected {n2} or {self.batch}x{n2}")
+            st = self._stream()
+            self._check(self.lib.bfd_fom_init(C.byref(self.desc), self.ws.data_ptr(),
+                                              self.workspace_bytes, st), "bfd_fom_init")
+            self._check(self.lib.bfd_fom_set_initial(C.byref(self.desc), self.ws.data_ptr(),
+                                                     w.data_ptr(), stride, st), "bfd_fom_set_initial")
+            self._w0_keepalive = w
+        self._ready = True
+
+    def run(self) -> None:
+        """Run all time steps of all samples; returns when the device has finished."""
+        if not self._ready:
+            raise _lib.BurgersError("set_initial() first")
+        with torch.cuda.device(self.device):
+            rc = self.lib.bfd_fom_run(C.byref(self.desc), self.ws.data_ptr(), C.byref(self.coef),
+                                      self._pinned.data_ptr(), self._stream())
+        self.sweeps_launched = int(self._pinned[2])
+        self._check(rc, "bfd_fom_run")
+        self._ready = False
+
+    def snapshots_device(self, m: int, t0: int = 0, t1: int | None = None, layout: int = 1,
+                         out: torch.Tensor | None = None) -> torch.Tensor:
+        """Snapshots of sample ``m`` as a CUDA tensor: layout 1 -> (2N, t1-t0) as the reference
+        returns them, layout 0 -> (t1-t0, 2N)."""
+        t1 = self.num_steps + 1 if t1 is None else t1
+        n2, nt = 2 * self.nx * self.ny, t1 - t0
+        shape = (n2, nt) if layout == 1 else (nt, n2)
+        with torch.cuda.device(self.device):
+            if out is None:
+                out = torch.empty(shape, dtype=torch.float64, device=self.device)
+            self._check(self.lib.bfd_fom_export(C.byref(self.desc), self.ws.data_ptr(), int(m), int(t0),
+                                                int(t1), int(layout), nt, out.data_ptr(),
+                                                self._stream()), "bfd_fom_export")
+        return out
+
+    def snapshots(self, m: int, pinned: bool = True) -> np.ndarray:
+        """(2N, T+1) float64 C-order NumPy array, the reference's return value (:89, :126)."""
+        dev = self.snapshots_device(m, layout=1)
+        host = torch.empty(dev.shape, dtype=torch.float64, pin_memory=pinned)
+        host.copy_(dev, non_blocking=False)
+        return host.numpy()
+
+    def diagnostics(self):
+        """(its, relnorm): per sample and step, len(resnorms) of newton_raphson and the last
+        relative residual."""
+        with torch.cuda.device(self.device):
+            its = torch.empty((self.batch, self.num_steps), dtype=torch.int32, device=self.device)
+            rel = torch.empty((self.batch, self.num_steps), dtype=torch.float64, device=self.device)
+            self._check(self.lib.bfd_fom_diagnostics(C.byref(self.desc), self.ws.data_ptr(), its.data_ptr(),
+                                                     rel.data_ptr(), self._stream()), "bfd_fom_diagnostics")
+            return its.cpu().numpy(), rel.cpu().numpy()

@@ -1,0 +1,106 @@
+"""Drop-in for the hot path of the reference's ``hypernet2D.py``.
+
+Same function names, positional signatures, array layouts and return tuples as
+SADPR/FiniteDifference ``BurgersFD_Clean{Coarse,Fine,TestAE}/hypernet2D.py`` for the implicit
+2D inviscid-Burgers steppers, so ``run_fom.py`` / ``run_prom.py`` / ``run_HPROM*.py`` can do
+``from finitedifference_b200.hypernet2D import ...`` unchanged.  Inputs are NumPy arrays and are
+never mutated; outputs are fresh NumPy arrays.  The work runs in hand-written sm_100a kernels
+behind the C ABI of include/burgers_b200.h; without the built extension or without a CUDA
+device every solver here raises -- there is no CPU path.
+
+Extra, keyword-only arguments (device, cells_per_lane, ...) default to the reference's
+behaviour.
+"""
+from __future__ import annotations
+
+import glob
+import os
+import time
+
+import numpy as np
+
+from .discretisation import make_2D_grid  # noqa: F401  (re-exported, hypernet2D.py:2501)
+from .fom import FomSolver
+
+__all__ = [
+    "make_2D_grid", "inviscid_burgers_implicit2D", "inviscid_burgers_implicit2D_batch",
+    "load_or_compute_snaps", "param_to_snap_fn", "get_saved_params", "compute_error",
+]
+
+
+def inviscid_burgers_implicit2D(grid_x, grid_y, w0, dt, num_steps, mu, *, device=None,
+                                cells_per_lane=1, return_info=False):
+    """Full-order trajectory; reference hypernet2D.py:72-131.
+
+    Returns ``snaps`` of shape ``(2N, num_steps+1)``, float64, C order: column ``i`` is the
+    state after ``i`` trapezoidal steps, Newton-converged to a relative residual of 1e-12
+    (at most 100 iterations) exactly as ``newton_raphson`` decides it.  ``return_info=True``
+    also returns ``{"newton_its": ..., "relnorm": ...}`` per step.
+    """
+    solver = FomSolver(grid_x, grid_y, dt, num_steps, [list(mu)[:2]], device=device,
+                       cells_per_lane=cells_per_lane)
+    solver.set_initial(np.asarray(w0, dtype=np.float64).ravel())
+    solver.run()
+    snaps = solver.snapshots(0)
+    if return_info:
+        its, rel = solver.diagnostics()
+        return snaps, {"newton_its": its[0], "relnorm": rel[0], "sweeps": solver.sweeps_launched}
+    return snaps
+
+
+def inviscid_burgers_implicit2D_batch(grid_x, grid_y, w0, dt, num_steps, mus, *, device=None,
+                                      cells_per_lane=1):
+    """Parameter sweep: the FOM for every ``mu`` in ``mus`` advanced together on one GPU.
+
+    Not in the reference (which loops ``load_or_compute_snaps`` over mu serially,
+    run_prom.py:59-71); returns the ready-to-export ``FomSolver`` so that callers choose
+    between ``snapshots(m)`` (host) and ``snapshots_device(m)`` (HBM-resident).
+    """
+    solver = FomSolver(grid_x, grid_y, dt, num_steps, mus, device=device, cells_per_lane=cells_per_lane)
+    solver.set_initial(w0)
+    solver.run()
+    return solver
+
+
+# -- snapshot cache (hypernet2D.py:3157-3221) ------------------------------------------------
+def param_to_snap_fn(mu, snap_folder="param_snaps", suffix=".npy"):
+    """``param_snaps/mu1_<str(mu1)>+mu2_<str(mu2)>.npy`` -- same names as the reference."""
+    npar = len(mu)
+    snapfn = snap_folder + "/"
+    for i in range(npar):
+        if i > 0:
+            snapfn += "+"
+        snapfn += "mu{}_{}".format(i + 1, mu[i])
+    return snapfn + suffix
+
+
+def get_saved_params(snap_folder="param_snaps"):
+    return set(glob.glob(snap_folder + "/*"))
+
+
+def load_or_compute_snaps(mu, grid_x, grid_y, w0, dt, num_steps, snap_folder="param_snaps"):
+    """Load ``(2N, T+1)`` snapshots from the mu-keyed ``.npy`` cache or compute and save them.
+
+    File names and contents are interchangeable with the reference's cache.
+    """
+    if not os.path.exists(snap_folder):
+        os.makedirs(snap_folder)
+    snap_fn = param_to_snap_fn(mu, snap_folder=snap_folder)
+    if snap_fn in get_saved_params(snap_folder=snap_folder):
+        print(f"Loading saved snaps for mu1={mu[0]}, mu2={mu[1]}")
+        snaps = np.load(snap_fn)[:, :num_steps + 1]
+    else:
+        print(f"Computing new snaps for mu1={mu[0]}, mu2={mu[1]}")
+        t0 = time.time()
+        snaps = inviscid_burgers_implicit2D(grid_x, grid_y, w0, dt, num_steps, mu)
+        print("Elapsed time: {:3.3e}".format(time.time() - t0))
+        np.save(snap_fn, snaps)
+    return snaps
+
+
+def compute_error(rom_snaps, hdm_snaps):
+    """Relative error at each time step and its mean (hypernet2D.py:3150-3155)."""
+    sq_hdm = np.sqrt(np.square(rom_snaps).sum(axis=0))
+    sq_err = np.sqrt(np.square(rom_snaps - hdm_snaps).sum(axis=0))
+    rel_err = sq_err / sq_hdm
+    return rel_err, rel_err.mean()

@@ -1,0 +1,110 @@
+/*
+ * burgers_b200.h -- C ABI of the B200-native (sm_100a) implicit 2D inviscid-Burgers hot path.
+ *
+ * The reference (SADPR/FiniteDifference) has no FFI layer: its boundary is the module-level
+ * Python functions of BurgersFD_Clean{Coarse,Fine,TestAE}/hypernet2D.py.  The Python shim
+ * finitedifference_b200/hypernet2D.py keeps those names and signatures and calls the entry
+ * points below through ctypes.  Every entry point names the reference function it replaces.
+ *
+ * Conventions
+ *   - all pointers are raw DEVICE pointers unless the name starts with `h_` (host);
+ *   - all real data is float64, index sets are int64;
+ *   - "natural" state layout is the reference's: w = [u.ravel(), v.ravel()], each (ny, nx)
+ *     row-major, cell id p = r*nx + c (run_fom.py:33-35, hypernet2D.py:2614);
+ *   - nothing allocates: callers size a workspace with the matching *_workspace_bytes();
+ *   - every function returns 0 on success, a negative BFD_E* code otherwise, and never throws;
+ *   - `stream` is a cudaStream_t passed as void*.
+ */
+#ifndef BURGERS_B200_H
+#define BURGERS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BFD_OK 0
+#define BFD_EINVAL (-1)       /* bad argument */
+#define BFD_ECUDA (-2)        /* CUDA runtime error, see bfd_last_cuda_error() */
+#define BFD_EWORKSPACE (-3)   /* workspace too small */
+#define BFD_ETIMEOUT (-4)     /* a wavefront hand-off timed out on the device */
+#define BFD_ENOTCONVERGED (-5)
+
+/* Library / device identification. */
+int bfd_abi_version(void);
+const char *bfd_last_cuda_error(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Full-order model: replaces inviscid_burgers_implicit2D (hypernet2D.py:72-131) together with
+ * newton_raphson (:1887-1933), inviscid_burgers_res2D_alt (:2588-2646),
+ * inviscid_burgers_exact_jac2D (:2703-2732) and scipy's spsolve, batched over `batch`
+ * parameter samples mu.
+ *
+ * Discretisation inputs (device, float64), computed by the caller exactly as the reference does:
+ *   cx[nx]   = 0.5*dt*(1/dx[c])           diagonal of 0.5*dt*Dx        (make_ddx, :2486-2492)
+ *   cxl[nx]  = 0.5*dt*(1/dx[c-1]), 0 at c=0   minus the sub-diagonal
+ *   cy[ny], cyd[ny]                        same along y
+ *   src[batch][nx] = dt*0.02*exp(mu2*xc)   source term             (:2625)
+ *   lbc[batch][ny] = 0.5*dt*mu1^2/dx       inlet ghost flux, applied at c == 0 (:2628-2631)
+ * ------------------------------------------------------------------------------------------ */
+typedef struct bfd_fom_desc {
+    int32_t nx, ny;          /* cells in x (fast axis) and y */
+    int32_t batch;           /* number of mu samples advanced together */
+    int32_t num_steps;       /* T; T+1 snapshots are kept per mu */
+    int32_t max_its;         /* Newton cap; the reference passes 100 (:123) */
+    int32_t cells_per_lane;  /* 1 or 2 : columns owned by one lane of the wavefront */
+    double rel_tol;          /* relnorm_cutoff; the reference passes 1e-12 (:123) */
+} bfd_fom_desc;
+
+/* Device pointers to the discretisation inputs listed above. */
+typedef struct bfd_fom_coef {
+    const double *cx, *cxl, *cy, *cyd, *src, *lbc;
+} bfd_fom_coef;
+
+size_t bfd_fom_workspace_bytes(const bfd_fom_desc *d);
+
+/* Lay the workspace out and reset the per-sample control blocks (asynchronous on `stream`). */
+int bfd_fom_init(const bfd_fom_desc *d, void *workspace, size_t workspace_bytes, void *stream);
+
+/* Initial condition, natural layout.  w0_stride = 0 broadcasts one (2N) state to every mu,
+ * otherwise w0 + m*w0_stride is sample m's state. */
+int bfd_fom_set_initial(const bfd_fom_desc *d, void *workspace, const double *w0,
+                        size_t w0_stride, void *stream);
+
+/* Advance every sample num_steps steps (Newton to rel_tol each step); returns when done.
+ * h_pinned: >= 64 bytes of page-locked host memory used to poll completion.
+ * On return h_pinned[0..2] (int32) = {samples finished, device error code, sweeps launched}. */
+int bfd_fom_run(const bfd_fom_desc *d, void *workspace, const bfd_fom_coef *coef, void *h_pinned,
+                void *stream);
+
+/* Copy out snapshots t0 <= t < t1 of sample `mu_index`.
+ * layout 0: out[(t-t0)*2N + dof]         (time-major, one contiguous state per snapshot)
+ * layout 1: out[dof*ld + (t-t0)]         (the reference's (2N, T+1) C-order array, ld >= t1-t0) */
+int bfd_fom_export(const bfd_fom_desc *d, const void *workspace, int mu_index, int t0, int t1,
+                   int layout, size_t ld, double *out, void *stream);
+
+/* Per-sample, per-step diagnostics: number of residual-norm evaluations (== len(resnorms) of
+ * newton_raphson) and the last relative residual.  its: int32 [batch][num_steps];
+ * relnorm: float64 [batch][num_steps]. Device pointers. */
+int bfd_fom_diagnostics(const bfd_fom_desc *d, const void *workspace, int32_t *its,
+                        double *relnorm, void *stream);
+
+/* Number of kernels launched by this library since load (for bench.py's gpu_launches). */
+uint64_t bfd_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Natural-layout operators shared by the PROM / HPROM paths and the tests.
+ * ------------------------------------------------------------------------------------------ */
+
+/* r = residual(w; wp) -- inviscid_burgers_res2D / _res2D_alt (:2544-2646).
+ * Also accumulates sum(r^2) into *norm2 (device, must be zeroed by the caller) when non-NULL. */
+int bfd_residual(int nx, int ny, const double *cx, const double *cxl, const double *cy,
+                 const double *cyd, const double *src, const double *lbc, const double *w,
+                 const double *wp, double *r, double *norm2, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BURGERS_B200_H */

@@ -1,0 +1,50 @@
+"""The C-ABI library builds for sm_100a, loads, and exports every symbol the header declares."""
+import ctypes
+import os
+import re
+
+from finitedifference_b200 import _build, _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_symbols():
+    text = open(os.path.join(ROOT, "include", "burgers_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(bfd_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_build_and_symbols():
+    path = _build.build()
+    assert os.path.exists(path)
+    lib = ctypes.CDLL(path)          # needs libcudart only, no GPU
+    declared = header_symbols()
+    assert declared, "no symbols parsed from the header"
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in include/burgers_b200.h but not exported"
+    assert sorted(_lib.SIGNATURES) == declared, "ctypes signatures out of sync with the header"
+    assert lib.bfd_abi_version() == 1
+
+
+def test_bad_arguments_are_reported_not_thrown():
+    lib = _lib.bind(_build.build())
+    d = _lib.FomDesc(0, 10, 1, 1, 100, 1, 1e-12)
+    assert lib.bfd_fom_workspace_bytes(ctypes.byref(d)) == 0
+    assert lib.bfd_fom_init(ctypes.byref(d), None, 0, None) == -1
+    d = _lib.FomDesc(10, 10, 1, 1, 100, 3, 1e-12)       # cells_per_lane must be 1 or 2
+    assert lib.bfd_fom_workspace_bytes(ctypes.byref(d)) == 0
+    d = _lib.FomDesc(750, 750, 1, 500, 100, 1, 1e-12)
+    nbytes = lib.bfd_fom_workspace_bytes(ctypes.byref(d))
+    assert 502 * 2 * 750 * 750 * 8 < nbytes < 1.15 * 502 * 2 * 750 * 750 * 8
+
+
+def test_no_cpu_fallback_without_gpu():
+    import pytest
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    import numpy as np
+    from finitedifference_b200 import hypernet2D as h
+    gx, gy = h.make_2D_grid(0, 100, 0, 100, 8, 8)
+    with pytest.raises(_lib.BurgersError):
+        h.inviscid_burgers_implicit2D(gx, gy, np.ones(128), 0.05, 1, [4.75, 0.02])
