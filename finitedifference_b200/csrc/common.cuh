@@ -80,8 +80,8 @@ __host__ __device__ inline size_t ssl_offset(const Ssl &L, int comp, int r, int 
 
 // Hand-off record between neighbouring strips: what the cell left of a strip's first column
 // contributes to the residual and to the forward substitution.
-//   {u, v, Fx = (u^2+up^2)/2, G = (u v + up vp)/2, du, dv, -, -}   64 bytes, 16-byte pieces
-constexpr int kEdgeDoubles = 8;
+//   {u, v, Fx = (u^2+up^2)/2, G = (u v + up vp)/2, du, dv}   48 bytes = three 16-byte pieces
+constexpr int kEdgeDoubles = 6;
 // Quiet-NaN with an unusual payload: "not written yet".  Arithmetic NaNs are canonical
 // (0x7ff8000000000000 / 0xfff8...), so a computed value never aliases it.
 constexpr unsigned long long kSentinelBits = 0x7ff8dead0b200b20ULL;

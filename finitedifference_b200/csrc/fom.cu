@@ -22,7 +22,7 @@
 // x_k == wp (first sweep of a step).  The last strip of a sample to finish applies the
 // reference's stopping rule on the device and sets up the sample's next sweep or next time
 // step, so samples progress independently and the host only keeps the launch queue full.
-#include "common.cuh"
+#include "wavefront.cuh"
 
 namespace bfd {
 
@@ -125,44 +125,18 @@ static FomArgs fom_args(const bfd_fom_desc *d, const FomLayout &L, void *ws) {
 
 namespace bfd {
 
-__device__ __forceinline__ double shfl_up1(double x) { return __shfl_up_sync(0xffffffffu, x, 1); }
-
-// 16-byte hand-off accesses: one transaction each on the GPU, so a pair is seen whole.
-#ifndef BFD_EMULATE
-__device__ __forceinline__ void ld_volatile2(const double *p, double &a, double &b) {
-    asm volatile("ld.volatile.global.v2.f64 {%0, %1}, [%2];" : "=d"(a), "=d"(b) : "l"(p) : "memory");
-}
-__device__ __forceinline__ void st_volatile2(double *p, double a, double b) {
-    asm volatile("st.volatile.global.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(a), "d"(b) : "memory");
-}
-#else   // emulation: second half first / first half last, so the checked half implies the other
-inline void ld_volatile2(const double *p, double &a, double &b) {
-    std::this_thread::yield();
-    unsigned long long x = __atomic_load_n((const unsigned long long *)p, __ATOMIC_ACQUIRE);
-    unsigned long long y = __atomic_load_n((const unsigned long long *)p + 1, __ATOMIC_ACQUIRE);
-    memcpy(&a, &x, 8); memcpy(&b, &y, 8);
-}
-inline void st_volatile2(double *p, double a, double b) {
-    unsigned long long x, y; memcpy(&x, &a, 8); memcpy(&y, &b, 8);
-    __atomic_store_n((unsigned long long *)p + 1, y, __ATOMIC_RELEASE);
-    __atomic_store_n((unsigned long long *)p, x, __ATOMIC_RELEASE);
-}
-#endif
-__device__ __forceinline__ bool is_sentinel(double x) {
-    return (unsigned long long)__double_as_longlong(x) == kSentinelBits;
-}
-
 // One Newton sweep of every still-active sample.  grid = ceil(batch*nstrips / WARPS) CTAs of
 // WARPS warps; warp <-> (sample m, strip j).  Virtual block ids come from a ticket so that a
 // strip's left neighbour (a smaller id) is always already resident when the strip waits on it.
 template <int CPL, int PF, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32) fom_sweep_kernel(const FomArgs a) {
     BFD_SHARED(unsigned, s_vb);
+    BFD_SHARED_ARRAY(double, s_edge, [WARPS][2][kEdgeSmemDoubles]);
     if (threadIdx.x == 0) s_vb = atomicInc(&a.glob->ticket, gridDim.x - 1);
     __syncthreads();
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nstrips = a.ssl.nstrips;
-    const int item = (int)s_vb * WARPS + (threadIdx.x >> 5);
+    const int item = (int)s_vb * WARPS + warp;
     if (item >= a.batch * nstrips) return;
     const int m = item / nstrips, j = item - m * nstrips;
     FomCtl *ctl = a.ctl + m;
@@ -198,11 +172,11 @@ __global__ void __launch_bounds__(WARPS * 32) fom_sweep_kernel(const FomArgs a) 
     const double *lbc = a.lbc + (size_t)m * ny;
 
     // hand-off records: read from the strip on the left, written for the strip on the right
-    double *edge_in = a.edge + (size_t)m * a.edge_stride_mu + (size_t)(j - 1) * ny * kEdgeDoubles;
-    double *edge_out = a.edge + (size_t)m * a.edge_stride_mu + (size_t)j * ny * kEdgeDoubles;
-    const bool consumer = (lane == 0 && j > 0);
-    const bool producer = (lane == 31 && j < nstrips - 1);
-    const double sentinel = __longlong_as_double((long long)kSentinelBits);
+    double *edge_m = a.edge + (size_t)m * a.edge_stride_mu;
+    EdgeReader ein;
+    EdgeWriter eout;
+    ein.init(edge_m + (size_t)(j > 0 ? j - 1 : 0) * ny * kEdgeDoubles, s_edge[warp][0], ny, lane, j > 0);
+    eout.init(edge_m + (size_t)j * ny * kEdgeDoubles, s_edge[warp][1], ny, lane, j < nstrips - 1);
 
     auto load = [&](int s, double (&u)[CPL], double (&v)[CPL], double (&up)[CPL], double (&vp)[CPL]) {
         const size_t o = (size_t)(s < last_row ? s : last_row) * (2 * W);
@@ -227,18 +201,10 @@ __global__ void __launch_bounds__(WARPS * 32) fom_sweep_kernel(const FomArgs a) 
 #pragma unroll
     for (int i = 0; i < PF; ++i) load(i, bu[i], bv[i], bup[i], bvp[i]);
 
-    // own cell of the previous step = upper neighbour (r-1, c) of this step
-    double pu[CPL], pv[CPL], pG[CPL], pH[CPL], pdu[CPL], pdv[CPL], pF_last = 0.0;
+    // own cells of the previous step = upper neighbours (r-1, c) of this step
+    Nbr prev[CPL];
 #pragma unroll
-    for (int q = 0; q < CPL; ++q) pu[q] = pv[q] = pG[q] = pH[q] = pdu[q] = pdv[q] = 0.0;
-
-    double e0 = 0, e1 = 0, e2 = 0, e3 = 0, e4 = 0, e5 = 0;  // pending hand-off record (consumer)
-    bool edge_dead = false;
-    if (consumer) {
-        ld_volatile2(edge_in + 0, e0, e1);
-        ld_volatile2(edge_in + 2, e2, e3);
-        ld_volatile2(edge_in + 4, e4, e5);
-    }
+    for (int q = 0; q < CPL; ++q) prev[q] = nbr_zero();
     double nrm = 0.0;
 
     for (int s0 = 0; s0 < nsteps; s0 += PF) {
@@ -255,40 +221,18 @@ __global__ void __launch_bounds__(WARPS * 32) fom_sweep_kernel(const FomArgs a) 
             }
             load(s + PF, bu[i], bv[i], bup[i], bvp[i]);
 
-            // left neighbour (r, c-1): lane-1's cell of the previous step
-            double Lu = shfl_up1(pu[CPL - 1]), Lv = shfl_up1(pv[CPL - 1]);
-            double LF = shfl_up1(pF_last), LG = shfl_up1(pG[CPL - 1]);
-            double Ldu = shfl_up1(pdu[CPL - 1]), Ldv = shfl_up1(pdv[CPL - 1]);
+            const int err = ein.step(s);
+            if (err && lane == 0) atomicExch(&a.glob->error, err);
+
+            // left neighbour (r, c-1): lane-1's last cell of the previous step
+            Nbr L;
+            L.u = shfl_up1(prev[CPL - 1].u); L.v = shfl_up1(prev[CPL - 1].v);
+            L.F = shfl_up1(prev[CPL - 1].F); L.G = shfl_up1(prev[CPL - 1].G);
+            L.du = shfl_up1(prev[CPL - 1].du); L.dv = shfl_up1(prev[CPL - 1].dv);
+            L.H = 0.0;
             if (lane == 0) {
-                Lu = Lv = LF = LG = Ldu = Ldv = 0.0;
-                if (consumer && s < ny) {
-                    if (!edge_dead) {
-                        unsigned spins = 0;
-                        while (is_sentinel(e0) || is_sentinel(e2) || is_sentinel(e4)) {
-                            double *rec = edge_in + (size_t)s * kEdgeDoubles;
-                            ld_volatile2(rec + 0, e0, e1);
-                            ld_volatile2(rec + 2, e2, e3);
-                            ld_volatile2(rec + 4, e4, e5);
-                            if (++spins > (1u << 24)) {
-                                edge_dead = true;
-                                atomicExch(&a.glob->error, BFD_ETIMEOUT);
-                                break;
-                            }
-                        }
-                    }
-                    if (!edge_dead) {
-                        Lu = e0; Lv = e1; LF = e2; LG = e3; Ldu = e4; Ldv = e5;
-                        double *rec = edge_in + (size_t)s * kEdgeDoubles;
-                        st_volatile2(rec + 0, sentinel, sentinel);   // re-arm for the next sweep
-                        st_volatile2(rec + 2, sentinel, sentinel);
-                        st_volatile2(rec + 4, sentinel, sentinel);
-                        if (s + 1 < ny) {                             // start fetching the next record
-                            ld_volatile2(rec + kEdgeDoubles + 0, e0, e1);
-                            ld_volatile2(rec + kEdgeDoubles + 2, e2, e3);
-                            ld_volatile2(rec + kEdgeDoubles + 4, e4, e5);
-                        }
-                    }
-                }
+                L = nbr_zero();
+                if (j > 0 && s < ny) ein.get(s, L);
             }
 
             const int r = s - lane;
@@ -300,32 +244,15 @@ __global__ void __launch_bounds__(WARPS * 32) fom_sweep_kernel(const FomArgs a) 
             double ou[CPL], ov[CPL];
 #pragma unroll
             for (int q = 0; q < CPL; ++q) {
-                const bool ok = rowok && colok[q];
-                double F = 0.5 * (u[q] * u[q]) + 0.5 * (up[q] * up[q]);   // hypernet2D.py:2619
-                double H = 0.5 * (v[q] * v[q]) + 0.5 * (vp[q] * vp[q]);   // :2620
-                double G = 0.5 * u[q] * v[q] + 0.5 * up[q] * vp[q];       // :2621
-                // :2637-2643
-                double ru = (u[q] - up[q]) + (cx[q] * F - cxl[q] * LF) + (cy * G - cyd * pG[q]) - srcq[q];
-                if (q == 0) ru -= lb;
-                const double rv = (v[q] - vp[q]) + (cy * H - cyd * pH[q]) + (cx[q] * G - cxl[q] * LG);
-                // r - A_L d_L - A_D d_D with the blocks of inviscid_burgers_exact_jac2D (:2719-2732)
-                const double bu_ = ru + cxl[q] * (Lu * Ldu) + 0.5 * cyd * (pv[q] * pdu[q] + pu[q] * pdv[q]);
-                const double bv_ = rv + 0.5 * cxl[q] * (Lv * Ldu + Lu * Ldv) + cyd * (pv[q] * pdv[q]);
-                const double d00 = 1.0 + cx[q] * u[q] + 0.5 * cy * v[q];
-                const double d01 = 0.5 * cy * u[q];
-                const double d10 = 0.5 * cx[q] * v[q];
-                const double d11 = 1.0 + cy * v[q] + 0.5 * cx[q] * u[q];
-                const double inv = 1.0 / (d00 * d11 - d01 * d10);
-                double du = (d11 * bu_ - d01 * bv_) * inv;
-                double dv = (d00 * bv_ - d10 * bu_) * inv;
-                double uu = u[q], vv = v[q];
-                if (!ok) { uu = vv = F = G = H = du = dv = 0.0; }
-                else nrm += ru * ru + rv * rv;
-                ou[q] = uu - du;
-                ov[q] = vv - dv;
-                Lu = uu; Lv = vv; LF = F; LG = G; Ldu = du; Ldv = dv;   // left neighbour of q+1
-                pu[q] = uu; pv[q] = vv; pG[q] = G; pH[q] = H; pdu[q] = du; pdv[q] = dv;
-                if (q == CPL - 1) pF_last = F;
+                double r2;
+                Nbr c = cell_update(u[q], v[q], up[q], vp[q], cx[q], cxl[q], cy, cyd, srcq[q],
+                                    q == 0 ? lb : 0.0, L, prev[q], r2);
+                if (rowok && colok[q]) nrm += r2;
+                else c = nbr_zero();          // outside the grid: contributes nothing, stays zero
+                ou[q] = c.u - c.du;
+                ov[q] = c.v - c.dv;
+                prev[q] = c;
+                L = c;                        // left neighbour of column q+1
             }
 
             double *o = xout + (size_t)s * (2 * W);
@@ -336,12 +263,7 @@ __global__ void __launch_bounds__(WARPS * 32) fom_sweep_kernel(const FomArgs a) 
                 *reinterpret_cast<double2 *>(o) = make_double2(ou[0], ou[1]);
                 *reinterpret_cast<double2 *>(o + W) = make_double2(ov[0], ov[1]);
             }
-            if (producer && rowok) {
-                double *rec = edge_out + (size_t)r * kEdgeDoubles;
-                st_volatile2(rec + 0, pu[CPL - 1], pv[CPL - 1]);
-                st_volatile2(rec + 2, pF_last, pG[CPL - 1]);
-                st_volatile2(rec + 4, pdu[CPL - 1], pdv[CPL - 1]);
-            }
+            eout.step(s - 31, prev[CPL - 1]);
         }
     }
 

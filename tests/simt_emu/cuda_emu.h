@@ -157,6 +157,16 @@ template <class T> static inline T __shfl_up_sync(unsigned, T v, int d) { return
 template <class T> static inline T __shfl_down_sync(unsigned, T v, int d) { return emu::shfl(v, emu::tls.lane + d); }
 template <class T> static inline T __shfl_xor_sync(unsigned, T v, int m) { return emu::shfl(v, emu::tls.lane ^ m); }
 template <class T> static inline T __shfl_sync(unsigned, T v, int l) { return emu::shfl(v, l); }
+static inline bool __all_sync(unsigned, bool p) {
+    // AND-reduce over the warp through the shuffle slots
+    emu::Warp *w = emu::tls.warp;
+    w->slot[emu::tls.lane] = p ? 1ull : 0ull;
+    w->bar.wait();
+    bool all = true;
+    for (int i = 0; i < w->bar.n; ++i) all = all && w->slot[i];
+    w->bar.wait();
+    return all;
+}
 static inline void __syncwarp(unsigned = 0xffffffffu) { emu::tls.warp->bar.wait(); }
 static inline void __syncthreads() { emu::tls.cta->bar.wait(); }
 static inline void __threadfence() { std::atomic_thread_fence(std::memory_order_seq_cst); }
