@@ -94,7 +94,8 @@ class ClockSampler:
 
 def algorithmic_bytes(its, cells):
     """48 B per cell-sweep (read x_k, read wp, write x_{k+1}); 32 B for the first sweep of a
-    step where x_0 == wp is read once.  its[m, t] = sweeps executed for sample m at step t."""
+    step where x_0 == wp is read once.  its[m, t] = residual evaluations (solves + 1) of sample m
+    at step t, as newton_raphson counts them."""
     its = np.asarray(its, dtype=np.int64)
     return int((cells * (32 + 48 * (its - 1))).sum())
 
@@ -146,8 +147,10 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--mu-per-gpu", type=int, default=int(os.environ.get("BFD_MU_PER_GPU", "16")))
-    ap.add_argument("--cells-per-lane", type=int, default=int(os.environ.get("BFD_CPL", "2")))
+    ap.add_argument("--mu-per-gpu", type=int, default=int(os.environ.get("BFD_MU_PER_GPU", "24")))
+    ap.add_argument("--chunk-steps", type=int, default=int(os.environ.get("BFD_CHUNK", "0")),
+                    help="time steps fused per launch (0 = library default)")
+    ap.add_argument("--non-strict", action="store_true", help="do not redo over-speculated steps")
     ap.add_argument("--num-steps", type=int, default=NUM_STEPS, help="time steps per trajectory (500 = the named config)")
     ap.add_argument("--grid", type=int, default=GRID_N)
     ap.add_argument("--e2e-mu", type=int, default=2)
@@ -177,14 +180,15 @@ def main():
     gx, gy = make_2D_grid(0, 100, 0, 100, n, n)
 
     # size the batch to the HBM actually free
-    one = _lib.FomDesc(n, n, 1, T, 100, args.cells_per_lane, 1e-12)
+    skw = dict(chunk_steps=args.chunk_steps, strict=not args.non_strict)
+    one = _lib.fom_desc(n, n, 1, T, chunk_steps=args.chunk_steps)
     per_mu = lib.bfd_fom_workspace_bytes(C.byref(one))
     free, _total = torch.cuda.mem_get_info(dev)
     B = max(1, min(args.mu_per_gpu, int(0.90 * free // per_mu)))
     mus = mu_lattice(B, rank, world)
     w0_dev = torch.ones(2 * cells, dtype=torch.float64, device=dev)
 
-    solver = FomSolver(gx, gy, DT, T, mus, device=dev, cells_per_lane=args.cells_per_lane)
+    solver = FomSolver(gx, gy, DT, T, mus, device=dev, **skw)
     ev = lambda: torch.cuda.Event(enable_timing=True)
 
     def one_step():
@@ -212,7 +216,8 @@ def main():
         total_ms = float(t.item())
         dist.barrier()
     its, rel = solver.diagnostics()
-    sweeps = solver.sweeps_launched
+    sweeps = solver.launches
+    redone = solver.steps_redone
     value = world * B * cells * T * args.steps / (total_ms * 1e-3)
 
     # roofline of the sweep kernel (the only kernel inside run()): algorithmic bytes / device time
@@ -225,10 +230,15 @@ def main():
     abytes = algorithmic_bytes(its, cells)
     achieved = abytes / (float(np.mean(run_ms)) * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "fom_sweep_kernel",
+                "traffic": None, "kernel": "fom_chunk_kernel",
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6.65 TB/s",
-                "algorithmic_bytes_per_step": abytes, "sweep_launches_per_step": sweeps,
-                "avg_launch_us": 1e3 * float(np.mean(run_ms)) / max(sweeps, 1)}
+                "algorithmic_bytes_per_step": abytes, "launches_per_step": sweeps,
+                "avg_launch_us": 1e3 * float(np.mean(run_ms)) / max(sweeps, 1),
+                "note": "algorithmic bytes = (48*solves + 32) B per cell-update (SURVEY 8d: one HBM pass per "
+                        "Newton sweep); the kernel fuses the sweeps of a step in registers, so its DRAM traffic "
+                        "is ~32 B per cell-update and frac may exceed 1: the binding unit is the FP64 pipe",
+                "fused_dram_bytes_model_per_step": int(32 * cells * T * B),
+                "steps_redone": redone}
 
     # end to end through the drop-in API: host w0 in, (2N, T+1) host snapshot arrays out
     del solver
@@ -240,7 +250,7 @@ def main():
     stage = torch.empty((2 * cells, T + 1), dtype=torch.float64, device=dev)
 
     def e2e_step():
-        s = FomSolver(gx, gy, DT, T, mus_e, device=dev, cells_per_lane=args.cells_per_lane)
+        s = FomSolver(gx, gy, DT, T, mus_e, device=dev, **skw)
         s.set_initial(w0_host.to(dev, non_blocking=True))
         s.run()
         for m in range(Be):
@@ -278,7 +288,8 @@ def main():
                 "config": {"workload": f"FOM parameter sweep, {n}x{n} grid, dt={DT}, {T} steps, "
                                        f"{B} mu per GPU (lattice over mu1 {MU1_RANGE} x mu2 {MU2_RANGE}), "
                                        "Newton rel tol 1e-12",
-                           "grid": n, "num_steps": T, "mu_per_gpu": B, "cells_per_lane": args.cells_per_lane,
+                           "grid": n, "num_steps": T, "mu_per_gpu": B, "chunk_steps": args.chunk_steps or 25,
+                           "strict": not args.non_strict,
                            "l2": f"working set {B * per_mu / 2**30:.1f} GiB of snapshots per GPU, far larger than L2; "
                                  "no flush needed", "newton_its_mean": float(its.mean()),
                            "max_relnorm": float(rel.max())},

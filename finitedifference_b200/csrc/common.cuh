@@ -10,7 +10,7 @@
 #else
 #include <cuda_runtime.h>
 #define BFD_SHARED(type, name) __shared__ type name
-#define BFD_SHARED_ARRAY(type, name, ...) __shared__ type name __VA_ARGS__
+#define BFD_SHARED_ARRAY(type, name, ...) __shared__ __align__(16) type name __VA_ARGS__
 #define BFD_LAUNCH(kernel, grid, block, smem, stream, ...) kernel<<<grid, block, smem, stream>>>(__VA_ARGS__)
 // kernels whose CTAs wait on one another: every CTA must be resident or ordered by ticket
 #define BFD_LAUNCH_CORESIDENT(kernel, grid, block, smem, stream, ...) \
@@ -78,10 +78,6 @@ __host__ __device__ inline size_t ssl_offset(const Ssl &L, int comp, int r, int 
     return ((size_t)(strip * L.slot_rows + r + l) * 2 + comp) * L.W + cc;
 }
 
-// Hand-off record between neighbouring strips: what the cell left of a strip's first column
-// contributes to the residual and to the forward substitution.
-//   {u, v, Fx = (u^2+up^2)/2, G = (u v + up vp)/2, du, dv}   48 bytes = three 16-byte pieces
-constexpr int kEdgeDoubles = 6;
 // Quiet-NaN with an unusual payload: "not written yet".  Arithmetic NaNs are canonical
 // (0x7ff8000000000000 / 0xfff8...), so a computed value never aliases it.
 constexpr unsigned long long kSentinelBits = 0x7ff8dead0b200b20ULL;

@@ -1,121 +1,160 @@
-// Full-order model: batched Newton sweeps as fused residual + block forward substitution.
+// Full-order model: batched trapezoidal time steps with all Newton sweeps of a step fused into
+// one pass of a register wavefront.
 //
 // Replaces, for the FOM path of the reference (BurgersFD_CleanFine/hypernet2D.py):
 //   inviscid_burgers_implicit2D :72-131, newton_raphson :1887-1933,
 //   inviscid_burgers_res2D_alt :2588-2646, inviscid_burgers_exact_jac2D :2703-2732 and the
 //   SuperLU spsolve at :1930.
 //
-// One Newton iteration J d = r, x <- x - d never builds J: with first-order upwind
-// differences the Jacobian is 2x2-block lower triangular (each cell couples to itself, its
-// left and its lower-row neighbour), so the solve is a block forward substitution
+// One Newton iteration J d = r, x <- x - d never builds J: with first-order upwind differences
+// the Jacobian is 2x2-block lower triangular (a cell couples to itself, its left and its
+// lower-row neighbour), so the solve is a block forward substitution
 //     D_p d_p = r_p - A_L d_L - A_D d_D
-// in which the cells of an anti-diagonal are independent.  A warp owns a strip of 32*CPL
-// columns and walks that wavefront: lane l is l rows behind lane 0, the left neighbour's
-// (u, v, fluxes, d) arrive by __shfl_up, the upper neighbour's are the lane's own previous
-// step.  States live in the skewed strip layout (common.cuh) so the anti-diagonal a warp
-// touches per step is one contiguous line of HBM.  Strips are chained left to right through
-// self-describing 64-byte records in global memory (no flags, no fences: a record is valid
-// when it no longer holds the sentinel; the consumer re-arms it).
+// in which the cells of an anti-diagonal are independent.  A warp owns a strip of 32 columns
+// and walks that wavefront down the rows: lane l is l rows behind lane 0, the left neighbour's
+// values arrive by __shfl_up, the upper neighbour's are the lane's own previous step.
 //
-// The sweep also accumulates ||r(x_k)||^2, so "residual norm, test, solve" of newton_raphson
-// costs one pass: 48 B per cell (read x_k 16, read wp 16, write x_{k+1} 16), 32 B when
-// x_k == wp (first sweep of a step).  The last strip of a sample to finish applies the
-// reference's stopping rule on the device and sets up the sample's next sweep or next time
-// step, so samples progress independently and the host only keeps the launch queue full.
+// Because EVERY dependency points up-wind, Newton iteration k+1 of a cell needs nothing but
+// iteration k of the same three cells.  The kernel therefore runs the K solves of a time step
+// as K "levels" of one software pipeline: at wavefront step s a lane works on level k of row
+// s - lane - k, all levels in the same step being independent of one another (instruction-level
+// parallelism for the FP64 pipe).  A time step costs one read of x_t (16 B/cell) and one write
+// of x_{t+1} (16 B/cell) instead of 48 B per Newton sweep, and several time steps are chained
+// inside one launch, so HBM and launch latency stop being the bound; the FP64 pipe is.
+//
+// Levels also accumulate ||r(x_k)||^2, k = 0..K, so newton_raphson's stopping rule is checked
+// for exactly the iterates the reference would test.  K is speculated (the previous step's
+// count); the last strip of a sample to finish a step validates the speculation on the device:
+// "converged at K" accepts the step, "converged earlier" redoes it with the right K (strict
+// mode), "not converged" continues it with further in-place sweeps.  Samples progress
+// independently; the host only keeps launches queued.
+//
+// States live in the skewed strip layout (common.cuh) so the anti-diagonal a warp touches per
+// step is one contiguous line of HBM.  Strips are chained left to right through
+// self-validating records in global memory (wavefront.cuh).
 #include "wavefront.cuh"
 
 namespace bfd {
 
+constexpr int kKMax = BFD_FOM_KMAX;
+constexpr int kNormSlots = kKMax + 1;
+
+enum StepStatus { kStepNone = 0, kStepOk = 1, kStepOkCap = 2, kStepEarly = 3, kStepNotConverged = 4 };
+
 struct FomCtl {            // one per mu sample, 64 bytes
-    int t;                 // time level being advanced (t -> t+1); == num_steps when finished
-    int k;                 // Newton sweep index inside the step
-    int in_slot;           // pool slot holding x_k
-    int out_slot;          // pool slot receiving x_{k+1}
-    int wp_slot;           // pool slot holding snapshot t
-    int slot_p, slot_q;    // the two work slots of this step (x_1 -> P, x_2 -> Q, x_3 -> P, ...)
-    int next_fresh;        // next never-used pool slot
-    unsigned arrive;       // strips of this sample that finished the current sweep
+    int t;                 // time level to advance next (t -> t+1); == num_steps when finished
+    int kbase;             // solves already applied to step t by earlier launches (continuation)
+    int k_first;           // solves for the first step of the next launch
+    int k_spec;            // solves speculated for the steps after it
+    int chunk;             // time steps the next launch attempts for this sample
+    unsigned arrive;       // strips of this sample that finished the current launch
+    int redone;            // steps redone or continued so far (statistics)
     int pad0;
-    double init_norm;      // ||r(x_0)|| of the current step
-    double pad1[2];
+    double init_norm;      // ||r(x_0)|| of step t, kept for continuation passes
+    double pad1[3];
 };
 static_assert(sizeof(FomCtl) == 64, "FomCtl must stay 64 bytes");
+
+struct StepRec {           // verdict on one time step of one launch
+    int status, kconv;
+    double rel, init;
+};
 
 struct FomGlobal {         // one per workspace, 64 bytes
     unsigned ticket;       // virtual block id dispenser (wraps every launch)
     int done;              // samples that completed all steps
     int error;             // BFD_E* raised on the device
-    int pad[13];
+    int redone;            // total steps redone / continued
+    int pad[12];
 };
 
 struct FomLayout {         // byte offsets inside the workspace
     Ssl ssl;
-    int batch, num_steps;
-    size_t off_global, off_ctl, off_snap_slot, off_its, off_relnorm, off_partial, off_edge,
+    int batch, num_steps, chunk;
+    size_t off_global, off_ctl, off_its, off_relnorm, off_steprec, off_arrive, off_partial, off_edge,
         off_pool, total;
-    size_t edge_stride_mu;   // doubles
-    size_t pool_stride_mu;   // doubles
+    size_t edge_stride_strip;  // doubles: one strip boundary, [chunk][ny][kRecDoubles]
+    size_t edge_stride_mu;     // doubles
+    size_t pool_stride_mu;     // doubles
 };
 
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-static FomLayout fom_layout(const bfd_fom_desc *d) {
-    FomLayout L;
-    L.ssl = make_ssl(d->nx, d->ny, d->cells_per_lane);
-    L.batch = d->batch;
-    L.num_steps = d->num_steps;
-    size_t o = 0;
-    L.off_global = o;    o = align_up(o + sizeof(FomGlobal), 256);
-    L.off_ctl = o;       o = align_up(o + sizeof(FomCtl) * d->batch, 256);
-    L.off_snap_slot = o; o = align_up(o + sizeof(int) * (size_t)d->batch * (d->num_steps + 1), 256);
-    L.off_its = o;       o = align_up(o + sizeof(int) * (size_t)d->batch * d->num_steps, 256);
-    L.off_relnorm = o;   o = align_up(o + sizeof(double) * (size_t)d->batch * d->num_steps, 256);
-    L.off_partial = o;   o = align_up(o + sizeof(double) * (size_t)d->batch * L.ssl.nstrips, 256);
-    L.edge_stride_mu = (size_t)L.ssl.nstrips * d->ny * kEdgeDoubles;
-    L.off_edge = o;      o = align_up(o + sizeof(double) * L.edge_stride_mu * d->batch, 256);
-    L.pool_stride_mu = L.ssl.state_doubles * (size_t)(d->num_steps + 2);
-    L.off_pool = o;      o = align_up(o + sizeof(double) * L.pool_stride_mu * d->batch, 256);
-    L.total = o;
-    return L;
+static int desc_chunk(const bfd_fom_desc *d) { return d->chunk_steps > 0 ? d->chunk_steps : 25; }
+static int desc_hint(const bfd_fom_desc *d) {
+    int h = d->newton_hint > 0 ? d->newton_hint : 4;
+    if (h > d->max_its) h = d->max_its;
+    return h;
 }
 
 static int check_desc(const bfd_fom_desc *d) {
     if (!d || d->nx < 1 || d->ny < 1 || d->batch < 1 || d->num_steps < 0 || d->max_its < 1) return BFD_EINVAL;
-    if (d->cells_per_lane != 1 && d->cells_per_lane != 2) return BFD_EINVAL;
+    if (d->chunk_steps < 0 || d->chunk_steps > BFD_FOM_MAX_CHUNK) return BFD_EINVAL;
+    if (d->newton_hint < 0 || d->newton_hint > kKMax) return BFD_EINVAL;
+    if (!(d->rel_tol < 1.0)) return BFD_EINVAL;
     return BFD_OK;
 }
 
-// Arguments of the sweep kernel (passed by value).
+static FomLayout fom_layout(const bfd_fom_desc *d) {
+    FomLayout L;
+    L.ssl = make_ssl(d->nx, d->ny, 1);
+    L.batch = d->batch;
+    L.num_steps = d->num_steps;
+    L.chunk = desc_chunk(d);
+    const size_t B = (size_t)d->batch, S = (size_t)L.chunk, ns = (size_t)L.ssl.nstrips;
+    size_t o = 0;
+    L.off_global = o;   o = align_up(o + sizeof(FomGlobal), 256);
+    L.off_ctl = o;      o = align_up(o + sizeof(FomCtl) * B, 256);
+    L.off_its = o;      o = align_up(o + sizeof(int) * B * d->num_steps, 256);
+    L.off_relnorm = o;  o = align_up(o + sizeof(double) * B * d->num_steps, 256);
+    L.off_steprec = o;  o = align_up(o + sizeof(StepRec) * B * S, 256);
+    L.off_arrive = o;   o = align_up(o + sizeof(unsigned) * B * S, 256);
+    L.off_partial = o;  o = align_up(o + sizeof(double) * B * S * ns * kNormSlots, 256);
+    L.edge_stride_strip = S * (size_t)d->ny * kRecDoubles;
+    L.edge_stride_mu = L.edge_stride_strip * (ns > 1 ? ns - 1 : 0);
+    L.off_edge = o;     o = align_up(o + sizeof(double) * L.edge_stride_mu * B, 256);
+    L.pool_stride_mu = L.ssl.state_doubles * (size_t)(d->num_steps + 1);
+    L.off_pool = o;     o = align_up(o + sizeof(double) * L.pool_stride_mu * B, 256);
+    L.total = o;
+    return L;
+}
+
+// Arguments of the kernels (passed by value).
 struct FomArgs {
     Ssl ssl;
-    int batch, num_steps, max_its;
+    int batch, num_steps, max_its, chunk, strict, uniform_y, hint;
     double rel_tol;
     const double *cx, *cxl, *cy, *cyd, *src, *lbc;
     FomGlobal *glob;
     FomCtl *ctl;
-    int *snap_slot;     // [batch][num_steps+1]
     int *its;           // [batch][num_steps]
     double *relnorm;    // [batch][num_steps]
-    double *partial;    // [batch][nstrips]
-    double *edge;       // [batch][nstrips][ny][kEdgeDoubles]
-    double *pool;       // [batch][num_steps+2][state]
-    size_t edge_stride_mu, pool_stride_mu;
+    StepRec *steprec;   // [batch][chunk]
+    unsigned *arrive;   // [batch][chunk]
+    double *partial;    // [batch][chunk][nstrips][kNormSlots]
+    double *edge;       // [batch][nstrips-1][chunk][ny][kRecDoubles]
+    double *pool;       // [batch][num_steps+1][state]   snapshot t of sample m in slot t
+    size_t edge_stride_strip, edge_stride_mu, pool_stride_mu;
 };
 
 static FomArgs fom_args(const bfd_fom_desc *d, const FomLayout &L, void *ws) {
     char *b = (char *)ws;
     FomArgs a;
     a.ssl = L.ssl;
-    a.batch = d->batch; a.num_steps = d->num_steps; a.max_its = d->max_its; a.rel_tol = d->rel_tol;
+    a.batch = d->batch; a.num_steps = d->num_steps; a.max_its = d->max_its; a.chunk = L.chunk;
+    a.strict = d->strict; a.uniform_y = d->uniform_y; a.hint = desc_hint(d);
+    a.rel_tol = d->rel_tol;
     a.cx = a.cxl = a.cy = a.cyd = a.src = a.lbc = nullptr;
     a.glob = (FomGlobal *)(b + L.off_global);
     a.ctl = (FomCtl *)(b + L.off_ctl);
-    a.snap_slot = (int *)(b + L.off_snap_slot);
     a.its = (int *)(b + L.off_its);
     a.relnorm = (double *)(b + L.off_relnorm);
+    a.steprec = (StepRec *)(b + L.off_steprec);
+    a.arrive = (unsigned *)(b + L.off_arrive);
     a.partial = (double *)(b + L.off_partial);
     a.edge = (double *)(b + L.off_edge);
     a.pool = (double *)(b + L.off_pool);
+    a.edge_stride_strip = L.edge_stride_strip;
     a.edge_stride_mu = L.edge_stride_mu;
     a.pool_stride_mu = L.pool_stride_mu;
     return a;
@@ -125,185 +164,210 @@ static FomArgs fom_args(const bfd_fom_desc *d, const FomLayout &L, void *ws) {
 
 namespace bfd {
 
-// One Newton sweep of every still-active sample.  grid = ceil(batch*nstrips / WARPS) CTAs of
-// WARPS warps; warp <-> (sample m, strip j).  Virtual block ids come from a ticket so that a
-// strip's left neighbour (a smaller id) is always already resident when the strip waits on it.
-template <int CPL, int PF, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32) fom_sweep_kernel(const FomArgs a) {
-    BFD_SHARED(unsigned, s_vb);
-    BFD_SHARED_ARRAY(double, s_edge, [WARPS][2][kEdgeSmemDoubles]);
-    if (threadIdx.x == 0) s_vb = atomicInc(&a.glob->ticket, gridDim.x - 1);
-    __syncthreads();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int nstrips = a.ssl.nstrips;
-    const int item = (int)s_vb * WARPS + warp;
-    if (item >= a.batch * nstrips) return;
-    const int m = item / nstrips, j = item - m * nstrips;
-    FomCtl *ctl = a.ctl + m;
-    const int t = ctl->t;
-    if (t >= a.num_steps) return;  // this sample has finished its trajectory
+// What one warp needs to run one time step of its strip.
+struct StepIo {
+    const double *xin;    // level-0 iterate: snapshot t, or the partly converged x of slot t+1 (CONT)
+    const double *xwp;    // snapshot t
+    double *xout;         // slot t+1 (all three already offset to this strip and lane)
+    double *edge_in;      // hand-off records of the strip on the left for this time step
+    double *edge_out;     // ... and the ones this strip produces
+    double *ring_in, *ring_out;   // shared memory of this warp
+    double *partial;      // [kNormSlots] squared residual norms of this (sample, step, strip)
+    const double *lbc;    // [ny] inlet term of this sample
+    const double *cy, *cyd;
+    int ny, strip, nstrips, lane;
+    double cx, cxl, src;  // column constants of this lane
+    bool colok, inlet;
+    int *error;
+};
 
-    constexpr int W = 32 * CPL;
-    const int nx = a.ssl.nx, ny = a.ssl.ny;
-    const int in_slot = ctl->in_slot, wp_slot = ctl->wp_slot, out_slot = ctl->out_slot;
-    const bool first = (in_slot == wp_slot);  // x_0 == wp: read the state once
-    const size_t sd = a.ssl.state_doubles;
-    const size_t strip_off = (size_t)j * a.ssl.strip_stride + (size_t)lane * CPL;
-    const double *pool_m = a.pool + (size_t)m * a.pool_stride_mu;
-    const double *xin = pool_m + (size_t)in_slot * sd + strip_off;
-    const double *xwp = pool_m + (size_t)wp_slot * sd + strip_off;
-    double *xout = a.pool + (size_t)m * a.pool_stride_mu + (size_t)out_slot * sd + strip_off;
-    const int last_row = a.ssl.slot_rows - 1;
-    const int nsteps = ny + kSkew;
+struct Level {            // what a cell hands to its right (L) and lower (D) neighbours at one level
+    double Fh, Gh, Hh;    // current-iterate flux parts u^2/2, uv/2, v^2/2
+    double pu, pm, pvv;   // u*du, v*du + u*dv, v*dv
+};
 
-    // per-lane column constants
-    double cx[CPL], cxl[CPL], srcq[CPL];
-    bool colok[CPL];
-#pragma unroll
-    for (int q = 0; q < CPL; ++q) {
-        const int c = j * W + lane * CPL + q;
-        colok[q] = c < nx;
-        const int cc = colok[q] ? c : nx - 1;
-        cx[q] = a.cx[cc];
-        cxl[q] = a.cxl[cc];
-        srcq[q] = a.src[(size_t)m * nx + cc];
-    }
-    const bool inlet = (j == 0 && lane == 0);
-    const double *lbc = a.lbc + (size_t)m * ny;
+// One trapezoidal time step of one strip: K fused Newton solves plus the residual of x_K.
+//   K     solves applied in this pass (levels 0..K-1 solve, level K evaluates ||r(x_K)||)
+//   CONT  continuation pass: the level-0 iterate differs from the previous snapshot
+//   UNI   cy / cyd are the same for every row (kept in registers)
+// Residual in the form used here (hypernet2D.py:2619-2643 regrouped): with Fh = u^2/2,
+// Gh = uv/2, Hh = v^2/2 of the iterate and Fp, Gp, Hp of the previous snapshot,
+//   ru = [u + cx Fh + cy Gh - cxl Fh_L - cyd Gh_D] + Au,  Au = -up + cx Fp + cy Gp - cxl Fp_L - cyd Gp_D - src - lbc
+//   rv = [v + cy Hh + cx Gh - cyd Hh_D - cxl Gh_L] + Av,  Av = -vp + cy Hp + cx Gp - cyd Hp_D - cxl Gp_L
+// Au, Av do not change between Newton levels and ride along the level pipeline.
+template <int K, bool CONT, bool UNI>
+__device__ __noinline__ void sweep_step(const StepIo &io) {
+    constexpr int NPR = 2 * K + 1 + (CONT ? 1 : 0);
+    constexpr int PF = 4;
+    constexpr int W = 32;
+    const int lane = io.lane, ny = io.ny;
+    const int last_row = ny + kSkew - 1;   // last slot-row holding cells
+    const int nsteps = ny + kSkew + K;
 
-    // hand-off records: read from the strip on the left, written for the strip on the right
-    double *edge_m = a.edge + (size_t)m * a.edge_stride_mu;
-    EdgeReader ein;
-    EdgeWriter eout;
-    ein.init(edge_m + (size_t)(j > 0 ? j - 1 : 0) * ny * kEdgeDoubles, s_edge[warp][0], ny, lane, j > 0);
-    eout.init(edge_m + (size_t)j * ny * kEdgeDoubles, s_edge[warp][1], ny, lane, j < nstrips - 1);
+    EdgeIn<NPR> ein;
+    EdgeOut<NPR> eout;
+    ein.init(io.edge_in, io.ring_in, ny, lane, io.strip > 0);
+    eout.init(io.edge_out, io.ring_out, ny, lane, io.strip < io.nstrips - 1);
+    const bool from_edge = (lane == 0) && io.strip > 0;
+    const bool to_edge = (lane == 31) && io.strip < io.nstrips - 1;
 
-    auto load = [&](int s, double (&u)[CPL], double (&v)[CPL], double (&up)[CPL], double (&vp)[CPL]) {
+    const double cx = io.cx, cxl = io.cxl, hcx = 0.5 * io.cx, hcxl = 0.5 * io.cxl, ncxl = -io.cxl;
+    const double src = io.src;
+    double cyU = 0.0, cydU = 0.0;
+    if (UNI) { cyU = __ldg(io.cy + (ny > 1 ? 1 : 0)); cydU = __ldg(io.cyd + (ny > 1 ? 1 : 0)); }
+
+    // register prefetch ring of the level-0 input, rows s .. s+PF-1
+    double bu[PF], bv[PF], bup[PF], bvp[PF];
+    auto load = [&](int s, int i) {
         const size_t o = (size_t)(s < last_row ? s : last_row) * (2 * W);
-        if constexpr (CPL == 1) {
-            u[0] = __ldg(xin + o);
-            v[0] = __ldg(xin + o + W);
-            if (!first) { up[0] = __ldg(xwp + o); vp[0] = __ldg(xwp + o + W); }
-        } else {
-            const double2 a0 = __ldg(reinterpret_cast<const double2 *>(xin + o));
-            const double2 a1 = __ldg(reinterpret_cast<const double2 *>(xin + o + W));
-            u[0] = a0.x; u[1] = a0.y; v[0] = a1.x; v[1] = a1.y;
-            if (!first) {
-                const double2 b0 = __ldg(reinterpret_cast<const double2 *>(xwp + o));
-                const double2 b1 = __ldg(reinterpret_cast<const double2 *>(xwp + o + W));
-                up[0] = b0.x; up[1] = b0.y; vp[0] = b1.x; vp[1] = b1.y;
-            }
-        }
+        bu[i] = io.xin[o];
+        bv[i] = io.xin[o + W];
+        if (CONT) { bup[i] = io.xwp[o]; bvp[i] = io.xwp[o + W]; }
+        else { bup[i] = 0.0; bvp[i] = 0.0; }
     };
-
-    // prefetch ring (registers): rows s .. s+PF-1
-    double bu[PF][CPL], bv[PF][CPL], bup[PF][CPL], bvp[PF][CPL];
 #pragma unroll
-    for (int i = 0; i < PF; ++i) load(i, bu[i], bv[i], bup[i], bvp[i]);
+    for (int i = 0; i < PF; ++i) load(i, i);
 
-    // own cells of the previous step = upper neighbours (r-1, c) of this step
-    Nbr prev[CPL];
+    Level prev[K];            // own cell of the previous step at each level = upper neighbour now
+    double pFh = 0.0, pGh = 0.0, pHh = 0.0;   // level K (residual only)
+    double qFp = 0.0, qGp = 0.0, qHp = 0.0;   // previous-snapshot flux parts of the previous row (CONT)
 #pragma unroll
-    for (int q = 0; q < CPL; ++q) prev[q] = nbr_zero();
-    double nrm = 0.0;
+    for (int k = 0; k < K; ++k) prev[k] = Level{0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    double xu[K + 1], xv[K + 1], Au[K + 1], Av[K + 1], nrm[K + 1];
+#pragma unroll
+    for (int k = 0; k <= K; ++k) { xu[k] = xv[k] = Au[k] = Av[k] = 0.0; nrm[k] = 0.0; }
 
     for (int s0 = 0; s0 < nsteps; s0 += PF) {
 #pragma unroll
         for (int i = 0; i < PF; ++i) {
             const int s = s0 + i;
-            if (s >= nsteps) break;  // warp-uniform
-            double u[CPL], v[CPL], up[CPL], vp[CPL];
-#pragma unroll
-            for (int q = 0; q < CPL; ++q) {
-                u[q] = bu[i][q]; v[q] = bv[i][q];
-                up[q] = first ? u[q] : bup[i][q];
-                vp[q] = first ? v[q] : bvp[i][q];
+            if (s >= nsteps) break;   // warp-uniform
+            {
+                const int err = ein.open(s);
+                if (err && lane == 0) atomicExch(io.error, err);
             }
-            load(s + PF, bu[i], bv[i], bup[i], bvp[i]);
+            xu[0] = bu[i]; xv[0] = bv[i];
+            const double up = CONT ? bup[i] : xu[0], vp = CONT ? bvp[i] : xv[0];
+            load(s + PF, i);
 
-            const int err = ein.step(s);
-            if (err && lane == 0) atomicExch(&a.glob->error, err);
-
-            // left neighbour (r, c-1): lane-1's last cell of the previous step
-            Nbr L;
-            L.u = shfl_up1(prev[CPL - 1].u); L.v = shfl_up1(prev[CPL - 1].v);
-            L.F = shfl_up1(prev[CPL - 1].F); L.G = shfl_up1(prev[CPL - 1].G);
-            L.du = shfl_up1(prev[CPL - 1].du); L.dv = shfl_up1(prev[CPL - 1].dv);
-            L.H = 0.0;
+            // left neighbours (r, c-1): lane-1's cells of the previous step, every level
+            double LF[K + 1], LG[K + 1], Lpu[K], Lpm[K], LFp = 0.0, LGp = 0.0;
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                LF[k] = shfl_up1(prev[k].Fh); LG[k] = shfl_up1(prev[k].Gh);
+                Lpu[k] = shfl_up1(prev[k].pu); Lpm[k] = shfl_up1(prev[k].pm);
+            }
+            LF[K] = shfl_up1(pFh); LG[K] = shfl_up1(pGh);
+            if (CONT) { LFp = shfl_up1(qFp); LGp = shfl_up1(qGp); }
             if (lane == 0) {
-                L = nbr_zero();
-                if (j > 0 && s < ny) ein.get(s, L);
-            }
-
-            const int r = s - lane;
-            const bool rowok = (unsigned)r < (unsigned)ny;
-            const int rr = rowok ? r : 0;
-            const double cy = __ldg(a.cy + rr), cyd = __ldg(a.cyd + rr);
-            const double lb = (inlet && rowok) ? __ldg(lbc + rr) : 0.0;
-
-            double ou[CPL], ov[CPL];
 #pragma unroll
-            for (int q = 0; q < CPL; ++q) {
-                double r2;
-                Nbr c = cell_update(u[q], v[q], up[q], vp[q], cx[q], cxl[q], cy, cyd, srcq[q],
-                                    q == 0 ? lb : 0.0, L, prev[q], r2);
-                if (rowok && colok[q]) nrm += r2;
-                else c = nbr_zero();          // outside the grid: contributes nothing, stays zero
-                ou[q] = c.u - c.du;
-                ov[q] = c.v - c.dv;
-                prev[q] = c;
-                L = c;                        // left neighbour of column q+1
+                for (int k = 0; k <= K; ++k) {
+                    const int rk = s - k;
+                    const bool take = from_edge && (unsigned)rk < (unsigned)ny;
+                    const double *rec = ein.row(take ? rk : 0);
+                    LF[k] = take ? rec[4 * k] : 0.0;
+                    LG[k] = take ? rec[4 * k + 1] : 0.0;
+                    if (k < K) {
+                        Lpu[k] = take ? rec[4 * k + 2] : 0.0;
+                        Lpm[k] = take ? rec[4 * k + 3] : 0.0;
+                    }
+                    if (CONT && k == 0) {
+                        LFp = take ? rec[4 * K + 2] : 0.0;
+                        LGp = take ? rec[4 * K + 3] : 0.0;
+                    }
+                }
             }
 
-            double *o = xout + (size_t)s * (2 * W);
-            if constexpr (CPL == 1) {
-                o[0] = ou[0];
-                o[W] = ov[0];
-            } else {
-                *reinterpret_cast<double2 *>(o) = make_double2(ou[0], ou[1]);
-                *reinterpret_cast<double2 *>(o + W) = make_double2(ov[0], ov[1]);
+            // levels in descending order: level k+1 consumes xu[k+1], Au[k+1] before level k
+            // replaces them with the values for the next step
+#pragma unroll
+            for (int k = K; k >= 0; --k) {
+                const int rk = s - lane - k;
+                const bool rowok = (unsigned)rk < (unsigned)ny;
+                const bool valid = rowok && io.colok;
+                const bool top = (rk <= 0);      // no upper neighbour (row -1 is not a cell)
+                double cy, cyd;
+                if (UNI) { cy = cyU; cyd = cydU; }
+                else { const int rr = rowok ? rk : 0; cy = __ldg(io.cy + rr); cyd = __ldg(io.cyd + rr); }
+                const double hcy = 0.5 * cy, hcyd = 0.5 * cyd, ncyd = -cyd;
+                double *orec = eout.row(rowok ? rk : 0);
+                const bool put = to_edge && rowok;
+
+                if (k == 0) {
+                    // previous-snapshot parts and the level-independent terms Au, Av
+                    const double hup = 0.5 * up, hvp = 0.5 * vp;
+                    const double Fp = hup * up, Gp = hup * vp, Hp = hvp * vp;
+                    const double DGp = top ? 0.0 : (CONT ? qGp : prev[0].Gh);
+                    const double DHp = top ? 0.0 : (CONT ? qHp : prev[0].Hh);
+                    const double lFp = CONT ? LFp : LF[0], lGp = CONT ? LGp : LG[0];
+                    const double lb = (io.inlet && rowok) ? __ldg(io.lbc + rk) : 0.0;
+                    double au = fma(cx, Fp, -up);
+                    au = fma(cy, Gp, au); au = fma(ncxl, lFp, au); au = fma(ncyd, DGp, au);
+                    au = (au - src) - lb;
+                    double av = fma(cy, Hp, -vp);
+                    av = fma(cx, Gp, av); av = fma(ncyd, DHp, av); av = fma(ncxl, lGp, av);
+                    Au[0] = au; Av[0] = av;
+                    if (CONT) {
+                        qFp = Fp; qGp = Gp; qHp = Hp;
+                        if (put) { orec[4 * K + 2] = Fp; orec[4 * K + 3] = Gp; }
+                    }
+                }
+
+                const double u = xu[k], v = xv[k];
+                const double hu = 0.5 * u, hv = 0.5 * v;
+                const double Fh = hu * u, Gh = hu * v, Hh = hv * v;
+                double DG, DH;
+                if (k < K) { DG = top ? 0.0 : prev[k].Gh; DH = top ? 0.0 : prev[k].Hh; }
+                else { DG = top ? 0.0 : pGh; DH = top ? 0.0 : pHh; }
+                double ru = Au[k] + u;
+                ru = fma(cx, Fh, ru); ru = fma(cy, Gh, ru); ru = fma(ncxl, LF[k], ru); ru = fma(ncyd, DG, ru);
+                double rv = Av[k] + v;
+                rv = fma(cy, Hh, rv); rv = fma(cx, Gh, rv); rv = fma(ncyd, DH, rv); rv = fma(ncxl, LG[k], rv);
+                const double r2 = fma(rv, rv, ru * ru);
+                nrm[k] += valid ? r2 : 0.0;
+
+                if (k < K) {
+                    const double Dpm = top ? 0.0 : prev[k].pm, Dpvv = top ? 0.0 : prev[k].pvv;
+                    const double bu_ = fma(hcyd, Dpm, fma(cxl, Lpu[k], ru));
+                    const double bv_ = fma(cyd, Dpvv, fma(hcxl, Lpm[k], rv));
+                    const double d00 = fma(cx, u, fma(hcy, v, 1.0));
+                    const double d11 = fma(cy, v, fma(hcx, u, 1.0));
+                    const double d01 = hcy * u, d10 = hcx * v;
+                    const double inv = rcp_fast(fma(d00, d11, -(d01 * d10)));
+                    const double du = fma(d11, bu_, -(d01 * bv_)) * inv;
+                    const double dv = fma(d00, bv_, -(d10 * bu_)) * inv;
+                    Level c;
+                    c.Fh = Fh; c.Gh = Gh; c.Hh = Hh;
+                    c.pu = u * du; c.pm = fma(v, du, u * dv); c.pvv = v * dv;
+                    prev[k] = c;
+                    xu[k + 1] = u - du; xv[k + 1] = v - dv;
+                    Au[k + 1] = Au[k]; Av[k + 1] = Av[k];
+                    if (put) { orec[4 * k] = Fh; orec[4 * k + 1] = Gh; orec[4 * k + 2] = c.pu; orec[4 * k + 3] = c.pm; }
+                    if (k == K - 1) {
+                        // x_K of row rk: slot-row (rk + lane) of the output state
+                        const int so = s - (K - 1);
+                        if (so >= 0 && so <= last_row) {
+                            double *o = io.xout + (size_t)so * (2 * W);
+                            o[0] = valid ? xu[K] : 0.0;
+                            o[W] = valid ? xv[K] : 0.0;
+                        }
+                    }
+                } else {
+                    pFh = Fh; pGh = Gh; pHh = Hh;
+                    if (put) { orec[4 * K] = Fh; orec[4 * K + 1] = Gh; }
+                }
             }
-            eout.step(s - 31, prev[CPL - 1]);
+            eout.close(s - kSkew - K);
         }
     }
 
-    // ||r||^2 of this strip, fixed reduction order (deterministic iteration counts)
+    // ||r(x_k)||^2 of this strip, fixed reduction order (deterministic iteration counts)
 #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) nrm += __shfl_xor_sync(0xffffffffu, nrm, off);
-    if (lane != 0) return;
-    a.partial[(size_t)m * nstrips + j] = nrm;
-    __threadfence();
-    if (atomicInc(&ctl->arrive, (unsigned)nstrips - 1) != (unsigned)nstrips - 1) return;
-    __threadfence();
-
-    // Last strip of this sample: newton_raphson's bookkeeping (hypernet2D.py:1907-1930).
-    double sum = 0.0;
-    const volatile double *part = a.partial + (size_t)m * nstrips;
-    for (int i = 0; i < nstrips; ++i) sum += part[i];
-    const double resnorm = sqrt(sum);
-    const int k = ctl->k;
-    double init = ctl->init_norm;
-    if (k == 0) { init = resnorm; ctl->init_norm = resnorm; }   // x_0 == wp: init_norm == resnorms[0]
-    const double rel = resnorm / init;
-    const bool conv = rel < a.rel_tol;                           // test precedes the solve (:1919)
-    const int P = ctl->slot_p, Q = ctl->slot_q;
-    if (conv || k + 1 >= a.max_its) {
-        // converged: the un-updated iterate x_k is the answer; cap reached: x_{k+1} is
-        const int fin = conv ? in_slot : out_slot;
-        const int other = (fin == P) ? Q : P;   // fin == wp_slot (test passed at k == 0) leaves P, Q free
-        a.snap_slot[(size_t)m * (a.num_steps + 1) + t + 1] = fin;
-        a.its[(size_t)m * a.num_steps + t] = k + 1;              // == len(resnorms)
-        a.relnorm[(size_t)m * a.num_steps + t] = rel;
-        const int fresh = ctl->next_fresh;
-        ctl->t = t + 1; ctl->k = 0;
-        ctl->wp_slot = fin; ctl->in_slot = fin;
-        ctl->slot_p = other; ctl->slot_q = fresh; ctl->next_fresh = fresh + 1;
-        ctl->out_slot = other;
-        if (t + 1 == a.num_steps) atomicAdd(&a.glob->done, 1);
-    } else {
-        ctl->k = k + 1;
-        ctl->in_slot = out_slot;
-        ctl->out_slot = (out_slot == P) ? Q : P;
+    for (int k = 0; k <= K; ++k) {
+        double x = nrm[k];
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) x += __shfl_xor_sync(0xffffffffu, x, off);
+        if (lane == 0) io.partial[k] = x;
     }
 }
 
@@ -311,7 +375,164 @@ __global__ void __launch_bounds__(WARPS * 32) fom_sweep_kernel(const FomArgs a) 
 
 namespace bfd {
 
-// natural (u|v, row-major) -> skewed strip layout, for every sample's slot 0; also resets control
+// newton_raphson's stopping rule (hypernet2D.py:1907-1930) applied to the residual norms one
+// pass produced: rn[k] = ||r(x_{kb+k})||, k = 0..K.  Run by the last strip to finish the step.
+__device__ void validate_step(const FomArgs &a, int m, int i, int kb, int K, double init_prev) {
+    const int ns = a.ssl.nstrips;
+    const volatile double *part = a.partial + (size_t)(m * a.chunk + i) * ns * kNormSlots;
+    double rn[kNormSlots];
+    for (int k = 0; k <= K; ++k) {
+        double sum = 0.0;
+        for (int j = 0; j < ns; ++j) sum += part[(size_t)j * kNormSlots + k];
+        rn[k] = sqrt(sum);
+    }
+    StepRec rec;
+    rec.init = kb ? init_prev : rn[0];          // init_norm = ||r(x_0)||, x_0 = wp (:1907)
+    rec.status = kStepNone; rec.kconv = K; rec.rel = 0.0;
+    for (int k = 0; k < K; ++k) {               // the test precedes each solve (:1915-1921)
+        const double rel = rn[k] / rec.init;
+        if (rel < a.rel_tol) { rec.status = kStepEarly; rec.kconv = k; rec.rel = rel; break; }
+    }
+    if (rec.status == kStepNone) {
+        if (kb + K >= a.max_its) {              // cap: max_its solves applied, no further test
+            rec.status = kStepOkCap; rec.rel = rn[K - 1] / rec.init;
+        } else {
+            rec.rel = rn[K] / rec.init;
+            rec.status = rec.rel < a.rel_tol ? kStepOk : kStepNotConverged;
+        }
+    }
+    a.steprec[(size_t)m * a.chunk + i] = rec;
+}
+
+__device__ __forceinline__ int clampk(int k) { return k < 1 ? 1 : (k > kKMax ? kKMax : k); }
+
+// Turn the verdicts of a launch into the sample's next state.  Run by the last strip of the
+// sample to finish the launch.
+__device__ void commit_chunk(const FomArgs &a, int m, int t0, int n, int kbase, int k_first, int k_spec) {
+    FomCtl *ctl = a.ctl + m;
+    int t = t0, knext = k_spec, redo = 0;
+    int new_kbase = 0, new_kfirst = k_first;
+    bool stop = false;
+    for (int i = 0; i < n && !stop; ++i) {
+        const StepRec rec = a.steprec[(size_t)m * a.chunk + i];
+        const int kb = i ? 0 : kbase;
+        int K = i ? k_spec : k_first;
+        if (K > a.max_its - kb) K = a.max_its - kb;
+        int *its = a.its + (size_t)m * a.num_steps + t;
+        double *rel = a.relnorm + (size_t)m * a.num_steps + t;
+        switch (rec.status) {
+        case kStepOk:     *its = kb + K + 1; *rel = rec.rel; knext = kb + K; ++t; break;   // == len(resnorms)
+        case kStepOkCap:  *its = a.max_its;  *rel = rec.rel; knext = kb + K; ++t; break;
+        case kStepEarly:
+            if (!a.strict || rec.kconv == 0) {   // keep the further-converged iterate
+                *its = kb + K + 1; *rel = rec.rel; knext = kb + rec.kconv; ++t;
+            } else {                              // the reference returns x_kconv: redo with that count
+                new_kbase = 0; new_kfirst = rec.kconv; stop = true; ++redo;
+            }
+            break;
+        default:                                  // not converged: further sweeps in place
+            new_kbase = kb + K; new_kfirst = 1; ctl->init_norm = rec.init; stop = true; ++redo;
+            break;
+        }
+    }
+    if (!stop) {
+        ctl->kbase = 0; ctl->k_first = clampk(knext); ctl->k_spec = clampk(knext); ctl->chunk = a.chunk;
+    } else {
+        ctl->kbase = new_kbase; ctl->k_first = new_kfirst; ctl->chunk = 1;
+    }
+    ctl->t = t;
+    if (redo) { ctl->redone += redo; atomicAdd(&a.glob->redone, redo); }
+    if (t >= a.num_steps) atomicAdd(&a.glob->done, 1);
+}
+
+// Up to `chunk` time steps of every unfinished sample.  One warp per CTA <-> (sample m, strip j);
+// virtual ids come from a ticket so that a strip's left neighbour (a smaller id) is always
+// already running when the strip waits on it.
+template <bool UNI>
+__global__ void __launch_bounds__(32) fom_chunk_kernel(const FomArgs a) {
+    BFD_SHARED_ARRAY(double, s_in, [kInRing * kRecDoubles]);
+    BFD_SHARED_ARRAY(double, s_out, [kOutRing * kRecDoubles]);
+    const int lane = threadIdx.x;
+    unsigned vb = 0;
+    if (lane == 0) vb = atomicInc(&a.glob->ticket, gridDim.x - 1);
+    vb = __shfl_sync(0xffffffffu, vb, 0);
+    const int nstrips = a.ssl.nstrips;
+    const int item = (int)vb;
+    if (item >= a.batch * nstrips) return;
+    const int m = item / nstrips, j = item - m * nstrips;
+    FomCtl *ctl = a.ctl + m;
+    const int t0 = ctl->t;
+    if (t0 >= a.num_steps) return;   // this sample has finished its trajectory
+    const int kbase = ctl->kbase, k_first = ctl->k_first, k_spec = ctl->k_spec;
+    const double init_prev = ctl->init_norm;
+    int n = ctl->chunk;
+    if (n > a.num_steps - t0) n = a.num_steps - t0;
+
+    const int nx = a.ssl.nx, ny = a.ssl.ny;
+    const size_t sd = a.ssl.state_doubles;
+    const size_t strip_off = (size_t)j * a.ssl.strip_stride + (size_t)lane;
+    double *pool_m = a.pool + (size_t)m * a.pool_stride_mu + strip_off;
+    double *edge_m = a.edge + (size_t)m * a.edge_stride_mu;
+
+    StepIo io;
+    io.ring_in = s_in; io.ring_out = s_out;
+    io.lbc = a.lbc + (size_t)m * ny;
+    io.cy = a.cy; io.cyd = a.cyd;
+    io.ny = ny; io.strip = j; io.nstrips = nstrips; io.lane = lane;
+    const int c = j * 32 + lane;
+    io.colok = c < nx;
+    const int cc = io.colok ? c : nx - 1;
+    io.cx = a.cx[cc]; io.cxl = a.cxl[cc]; io.src = a.src[(size_t)m * nx + cc];
+    io.inlet = (j == 0 && lane == 0);
+    io.error = &a.glob->error;
+
+    for (int i = 0; i < n; ++i) {
+        const int t = t0 + i;
+        const int kb = i ? 0 : kbase;
+        int K = i ? k_spec : k_first;
+        if (K > a.max_its - kb) K = a.max_its - kb;
+        io.xwp = pool_m + (size_t)t * sd;
+        io.xout = pool_m + (size_t)(t + 1) * sd;
+        io.xin = kb ? io.xout : io.xwp;
+        const size_t eoff = (size_t)i * ny * kRecDoubles;
+        io.edge_in = edge_m + (size_t)(j > 0 ? j - 1 : 0) * a.edge_stride_strip + eoff;
+        io.edge_out = edge_m + (size_t)(j < nstrips - 1 ? j : 0) * a.edge_stride_strip + eoff;
+        io.partial = a.partial + ((size_t)(m * a.chunk + i) * nstrips + j) * kNormSlots;
+        if (kb) {
+            sweep_step<1, true, UNI>(io);
+        } else {
+            switch (K) {
+            case 1: sweep_step<1, false, UNI>(io); break;
+            case 2: sweep_step<2, false, UNI>(io); break;
+            case 3: sweep_step<3, false, UNI>(io); break;
+            case 4: sweep_step<4, false, UNI>(io); break;
+            case 5: sweep_step<5, false, UNI>(io); break;
+            default: sweep_step<6, false, UNI>(io); break;
+            }
+        }
+        __syncwarp();
+        if (lane == 0) {
+            __threadfence();
+            if (atomicInc(&a.arrive[(size_t)m * a.chunk + i], (unsigned)nstrips - 1) == (unsigned)nstrips - 1) {
+                __threadfence();
+                validate_step(a, m, i, kb, kb ? 1 : K, init_prev);
+            }
+        }
+    }
+    if (lane == 0) {
+        __threadfence();
+        if (atomicInc(&ctl->arrive, (unsigned)nstrips - 1) == (unsigned)nstrips - 1) {
+            __threadfence();
+            commit_chunk(a, m, t0, n, kbase, k_first, k_spec);
+        }
+    }
+}
+
+}  // namespace bfd
+
+namespace bfd {
+
+// natural (u|v, row-major) -> skewed strip layout, into every sample's slot 0
 __global__ void fom_import_kernel(const FomArgs a, const double *w0, size_t w0_stride) {
     const Ssl &L = a.ssl;
     const size_t per_state = L.state_doubles;
@@ -320,6 +541,7 @@ __global__ void fom_import_kernel(const FomArgs a, const double *w0, size_t w0_s
          i += (size_t)gridDim.x * blockDim.x) {
         const int m = (int)(i / per_state);
         size_t o = i - (size_t)m * per_state;
+        const size_t o_state = o;
         const int strip = (int)(o / L.strip_stride);
         o -= (size_t)strip * L.strip_stride;
         const int s = (int)(o / (2 * L.W));
@@ -329,24 +551,33 @@ __global__ void fom_import_kernel(const FomArgs a, const double *w0, size_t w0_s
         double val = 0.0;
         if (r >= 0 && r < L.ny && c < L.nx)
             val = w0[(size_t)m * w0_stride + (size_t)comp * L.nx * L.ny + (size_t)r * L.nx + c];
-        a.pool[(size_t)m * a.pool_stride_mu + o + (size_t)strip * L.strip_stride] = val;
+        a.pool[(size_t)m * a.pool_stride_mu + o_state] = val;
     }
 }
 
+// arm the hand-off records and reset the per-sample control blocks
 __global__ void fom_reset_kernel(const FomArgs a) {
     const size_t n_edge = a.edge_stride_mu * a.batch;
     const double sentinel = __longlong_as_double((long long)kSentinelBits);
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n_edge;
          i += (size_t)gridDim.x * blockDim.x)
         a.edge[i] = sentinel;
+    const size_t n_arrive = (size_t)a.batch * a.chunk;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n_arrive;
+         i += (size_t)gridDim.x * blockDim.x)
+        a.arrive[i] = 0u;
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (g == 0) { a.glob->ticket = 0; a.glob->done = (a.num_steps == 0) ? a.batch : 0; a.glob->error = 0; }
+    if (g == 0) {
+        a.glob->ticket = 0; a.glob->done = (a.num_steps == 0) ? a.batch : 0; a.glob->error = 0;
+        a.glob->redone = 0;
+    }
     if (g < a.batch) {
         FomCtl c;
-        c.t = 0; c.k = 0; c.in_slot = 0; c.wp_slot = 0; c.slot_p = 1; c.slot_q = 2; c.out_slot = 1;
-        c.next_fresh = 3; c.arrive = 0; c.pad0 = 0; c.init_norm = 0.0; c.pad1[0] = c.pad1[1] = 0.0;
+        c.t = 0; c.kbase = 0; c.k_first = a.hint; c.k_spec = a.hint;
+        c.chunk = 1;      // the first launch probes the solve count on one step
+        c.arrive = 0; c.redone = 0; c.pad0 = 0; c.init_norm = 0.0;
+        c.pad1[0] = c.pad1[1] = c.pad1[2] = 0.0;
         a.ctl[g] = c;
-        a.snap_slot[(size_t)g * (a.num_steps + 1)] = 0;
     }
 }
 
@@ -359,7 +590,6 @@ __global__ void fom_export_kernel(const FomArgs a, int m, int t0, int t1, int la
     const int strip = blockIdx.y, s = blockIdx.x;      // one slot-row (u and v) per CTA column
     const int nt = t1 - t0;
     const size_t N = (size_t)L.nx * L.ny;
-    const int *slots = a.snap_slot + (size_t)m * (a.num_steps + 1);
     const double *pool_m = a.pool + (size_t)m * a.pool_stride_mu;
     for (int comp = 0; comp < 2; ++comp) {
         for (int cc0 = 0; cc0 < L.W; cc0 += 32) {
@@ -368,7 +598,7 @@ __global__ void fom_export_kernel(const FomArgs a, int m, int t0, int t1, int la
                 for (int ty = threadIdx.y; ty < 32; ty += blockDim.y) {
                     const int t = tb + ty;
                     if (t < nt) {
-                        const size_t o = (size_t)slots[t0 + t] * L.state_doubles +
+                        const size_t o = (size_t)(t0 + t) * L.state_doubles +
                                          ((size_t)(strip * L.slot_rows + s) * 2 + comp) * L.W + cc0 + threadIdx.x;
                         tile[ty][threadIdx.x] = pool_m[o];
                     }
@@ -413,7 +643,7 @@ extern "C" int bfd_fom_init(const bfd_fom_desc *d, void *ws, size_t ws_bytes, vo
     const FomLayout L = fom_layout(d);
     if (ws_bytes < L.total) return BFD_EWORKSPACE;
     const FomArgs a = fom_args(d, L, ws);
-    BFD_LAUNCH(fom_reset_kernel, BFD_GRID(296), 256, 0, (cudaStream_t)stream, a);
+    BFD_LAUNCH(fom_reset_kernel, BFD_GRID(592), 256, 0, (cudaStream_t)stream, a);
     BFD_LAUNCHED();
     return BFD_OK;
 }
@@ -428,13 +658,13 @@ extern "C" int bfd_fom_set_initial(const bfd_fom_desc *d, void *ws, const double
     return BFD_OK;
 }
 
-template <int CPL>
-static int launch_sweep(const FomArgs &a, cudaStream_t st) {
-    constexpr int WARPS = 4, PF = 4;
-    const int items = a.batch * a.ssl.nstrips;
-    const int grid = (items + WARPS - 1) / WARPS;
-    auto kernel = fom_sweep_kernel<CPL, PF, WARPS>;
-    BFD_LAUNCH_CORESIDENT(kernel, grid, WARPS * 32, 0, st, a);
+static int launch_chunk(const FomArgs &a, cudaStream_t st) {
+    const int grid = a.batch * a.ssl.nstrips;
+    if (a.uniform_y) {
+        BFD_LAUNCH_CORESIDENT(fom_chunk_kernel<true>, grid, 32, 0, st, a);
+    } else {
+        BFD_LAUNCH_CORESIDENT(fom_chunk_kernel<false>, grid, 32, 0, st, a);
+    }
     BFD_LAUNCHED();
     return BFD_OK;
 }
@@ -448,12 +678,12 @@ extern "C" int bfd_fom_run(const bfd_fom_desc *d, void *ws, const bfd_fom_coef *
     a.src = coef->src; a.lbc = coef->lbc;
     cudaStream_t st = (cudaStream_t)stream;
     volatile int *h = (volatile int *)h_pinned;
-    h[0] = 0; h[1] = 0; h[2] = 0;
+    h[0] = 0; h[1] = 0; h[2] = 0; h[3] = 0;
     if (d->num_steps == 0) { h[0] = d->batch; return BFD_OK; }
 
-    // Samples advance independently on the device; the host only keeps sweeps queued and polls
-    // the "samples finished" counter one batch of launches behind, so the GPU never idles on it.
-    // A sweep launched after everything finished exits at once.
+    // Samples advance independently on the device; the host keeps two launches queued and looks
+    // at the "samples finished" counter of the launch before them, so the GPU never idles on
+    // the poll.  A launch issued after everything finished exits at once.
     cudaEvent_t ev[2];
     BFD_CUDA(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming));
     BFD_CUDA(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
@@ -461,19 +691,16 @@ extern "C" int bfd_fom_run(const bfd_fom_desc *d, void *ws, const bfd_fom_coef *
     const long long hard_cap = (long long)d->num_steps * d->max_its + 8;
     long long launched = 0;
     int rc = BFD_OK, pending = 0, slot = 0;
-    const int chunk = 8;
     bool finished = false;
     while (!finished && rc == BFD_OK) {
-        for (int i = 0; i < chunk && rc == BFD_OK; ++i) {
-            rc = (d->cells_per_lane == 1) ? launch_sweep<1>(a, st) : launch_sweep<2>(a, st);
-            ++launched;
-        }
+        rc = launch_chunk(a, st);
+        ++launched;
         if (rc != BFD_OK) break;
         cudaError_t e = cudaMemcpyAsync(h_poll + 2 * slot, &a.glob->done, 2 * sizeof(int),
                                         cudaMemcpyDeviceToHost, st);
         if (e == cudaSuccess) e = cudaEventRecord(ev[slot], st);
         if (e != cudaSuccess) { rc = record_cuda_error(e, "fom poll"); break; }
-        if (pending) {   // look at the poll issued one chunk ago
+        if (pending) {   // look at the poll issued one launch ago
             const int prev = slot ^ 1;
             e = cudaEventSynchronize(ev[prev]);
             if (e != cudaSuccess) { rc = record_cuda_error(e, "fom poll sync"); break; }
@@ -481,17 +708,17 @@ extern "C" int bfd_fom_run(const bfd_fom_desc *d, void *ws, const bfd_fom_coef *
         }
         pending = 1;
         slot ^= 1;
-        if (launched > hard_cap + 2 * chunk) { rc = BFD_ENOTCONVERGED; break; }
+        if (launched > hard_cap) { rc = BFD_ENOTCONVERGED; break; }
     }
     cudaError_t e = cudaStreamSynchronize(st);
     if (e != cudaSuccess && rc == BFD_OK) rc = record_cuda_error(e, "fom run sync");
     cudaEventDestroy(ev[0]);
     cudaEventDestroy(ev[1]);
     if (rc == BFD_OK) {
-        int fin[2] = {0, 0};
-        e = cudaMemcpy(fin, &a.glob->done, sizeof(fin), cudaMemcpyDeviceToHost);
+        int fin[4] = {0, 0, 0, 0};
+        e = cudaMemcpy(fin, &a.glob->done, 3 * sizeof(int), cudaMemcpyDeviceToHost);
         if (e != cudaSuccess) return record_cuda_error(e, "fom final status");
-        h[0] = fin[0]; h[1] = fin[1]; h[2] = (int)launched;
+        h[0] = fin[0]; h[1] = fin[1]; h[2] = (int)launched; h[3] = fin[2];
         if (fin[1] != 0) rc = fin[1];
         else if (fin[0] < d->batch) rc = BFD_ENOTCONVERGED;
     }

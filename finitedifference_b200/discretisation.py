@@ -50,3 +50,13 @@ def parameter_terms(grid_x, grid_y, dt, mus):
     den = dx if dx.size == ny else np.full(ny, dx[0])
     lbc = np.stack([0.5 * dt * mu[0] ** 2 / den for mu in mus])
     return np.ascontiguousarray(src), np.ascontiguousarray(lbc)
+
+
+def is_uniform(cy, cyd, rtol=1e-12):
+    """True when the y coefficients are one value to ``rtol`` (``make_2D_grid`` grids are:
+    linspace spacing varies by a few ulp), so the kernels may hold them in a register."""
+    cy = np.asarray(cy); cyd = np.asarray(cyd)
+    if cy.size < 2:
+        return True
+    ref = cy[1]
+    return bool(np.all(np.abs(cy - ref) <= rtol * abs(ref)) and np.all(np.abs(cyd[1:] - ref) <= rtol * abs(ref)))

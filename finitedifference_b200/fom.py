@@ -13,7 +13,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from .discretisation import parameter_terms, stencil_coefficients
+from .discretisation import is_uniform, parameter_terms, stencil_coefficients
 
 
 def _require_cuda(device=None) -> torch.device:
@@ -35,8 +35,8 @@ class FomSolver:
     Snapshots stay resident in HBM (skewed strip layout, csrc/common.cuh) until exported.
     """
 
-    def __init__(self, grid_x, grid_y, dt, num_steps, mus, device=None, cells_per_lane=1,
-                 max_its=100, rel_tol=1e-12):
+    def __init__(self, grid_x, grid_y, dt, num_steps, mus, device=None, max_its=100, rel_tol=1e-12,
+                 strict=True, chunk_steps=0, newton_hint=0):
         self.lib = _lib.get_lib()
         self.device = _require_cuda(device)
         self.grid_x = np.asarray(grid_x, dtype=np.float64)
@@ -44,20 +44,22 @@ class FomSolver:
         self.mus = np.atleast_2d(np.asarray(mus, dtype=np.float64))
         self.nx, self.ny = self.grid_x.size - 1, self.grid_y.size - 1
         self.batch, self.num_steps, self.dt = self.mus.shape[0], int(num_steps), float(dt)
-        self.desc = _lib.FomDesc(self.nx, self.ny, self.batch, self.num_steps, int(max_its),
-                                 int(cells_per_lane), float(rel_tol))
+        cx, cxl, cy, cyd = stencil_coefficients(self.grid_x, self.grid_y, self.dt)
+        self.uniform_y = is_uniform(cy, cyd)
+        self.desc = _lib.fom_desc(self.nx, self.ny, self.batch, self.num_steps, max_its, rel_tol,
+                                  chunk_steps, newton_hint, strict, self.uniform_y)
         nbytes = self.lib.bfd_fom_workspace_bytes(C.byref(self.desc))
         if nbytes == 0:
             raise _lib.BurgersError("invalid FOM description")
         self.workspace_bytes = nbytes
         with torch.cuda.device(self.device):
             self.ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
-            cx, cxl, cy, cyd = stencil_coefficients(self.grid_x, self.grid_y, self.dt)
             src, lbc = parameter_terms(self.grid_x, self.grid_y, self.dt, self.mus)
             self._coef_t = [_dev(a, self.device) for a in (cx, cxl, cy, cyd, src, lbc)]
             self.coef = _lib.FomCoef(*[t.data_ptr() for t in self._coef_t])
             self._pinned = torch.zeros(16, dtype=torch.int32).pin_memory()
-        self.sweeps_launched = 0
+        self.launches = 0
+        self.steps_redone = 0
         self._ready = False
 
     # -- helpers ---------------------------------------------------------------------------
@@ -97,7 +99,8 @@ class FomSolver:
         with torch.cuda.device(self.device):
             rc = self.lib.bfd_fom_run(C.byref(self.desc), self.ws.data_ptr(), C.byref(self.coef),
                                       self._pinned.data_ptr(), self._stream())
-        self.sweeps_launched = int(self._pinned[2])
+        self.launches = int(self._pinned[2])
+        self.steps_redone = int(self._pinned[3])
         self._check(rc, "bfd_fom_run")
         self._ready = False
 

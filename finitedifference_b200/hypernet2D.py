@@ -8,7 +8,7 @@ never mutated; outputs are fresh NumPy arrays.  The work runs in hand-written sm
 behind the C ABI of include/burgers_b200.h; without the built extension or without a CUDA
 device every solver here raises -- there is no CPU path.
 
-Extra, keyword-only arguments (device, cells_per_lane, ...) default to the reference's
+Extra, keyword-only arguments (device, strict, ...) default to the reference's
 behaviour.
 """
 from __future__ import annotations
@@ -29,7 +29,7 @@ __all__ = [
 
 
 def inviscid_burgers_implicit2D(grid_x, grid_y, w0, dt, num_steps, mu, *, device=None,
-                                cells_per_lane=1, return_info=False):
+                                strict=True, return_info=False, **solver_kw):
     """Full-order trajectory; reference hypernet2D.py:72-131.
 
     Returns ``snaps`` of shape ``(2N, num_steps+1)``, float64, C order: column ``i`` is the
@@ -37,26 +37,27 @@ def inviscid_burgers_implicit2D(grid_x, grid_y, w0, dt, num_steps, mu, *, device
     (at most 100 iterations) exactly as ``newton_raphson`` decides it.  ``return_info=True``
     also returns ``{"newton_its": ..., "relnorm": ...}`` per step.
     """
-    solver = FomSolver(grid_x, grid_y, dt, num_steps, [list(mu)[:2]], device=device,
-                       cells_per_lane=cells_per_lane)
+    solver = FomSolver(grid_x, grid_y, dt, num_steps, [list(mu)[:2]], device=device, strict=strict,
+                       **solver_kw)
     solver.set_initial(np.asarray(w0, dtype=np.float64).ravel())
     solver.run()
     snaps = solver.snapshots(0)
     if return_info:
         its, rel = solver.diagnostics()
-        return snaps, {"newton_its": its[0], "relnorm": rel[0], "sweeps": solver.sweeps_launched}
+        return snaps, {"newton_its": its[0], "relnorm": rel[0], "launches": solver.launches,
+                       "steps_redone": solver.steps_redone}
     return snaps
 
 
 def inviscid_burgers_implicit2D_batch(grid_x, grid_y, w0, dt, num_steps, mus, *, device=None,
-                                      cells_per_lane=1):
+                                      strict=True, **solver_kw):
     """Parameter sweep: the FOM for every ``mu`` in ``mus`` advanced together on one GPU.
 
     Not in the reference (which loops ``load_or_compute_snaps`` over mu serially,
     run_prom.py:59-71); returns the ready-to-export ``FomSolver`` so that callers choose
     between ``snapshots(m)`` (host) and ``snapshots_device(m)`` (HBM-resident).
     """
-    solver = FomSolver(grid_x, grid_y, dt, num_steps, mus, device=device, cells_per_lane=cells_per_lane)
+    solver = FomSolver(grid_x, grid_y, dt, num_steps, mus, device=device, strict=strict, **solver_kw)
     solver.set_initial(w0)
     solver.run()
     return solver

@@ -49,13 +49,22 @@ const char *bfd_last_cuda_error(void);
  *   src[batch][nx] = dt*0.02*exp(mu2*xc)   source term             (:2625)
  *   lbc[batch][ny] = 0.5*dt*mu1^2/dx       inlet ghost flux, applied at c == 0 (:2628-2631)
  * ------------------------------------------------------------------------------------------ */
+#define BFD_FOM_KMAX 6         /* Newton solves fused into one pass over a time step */
+#define BFD_FOM_MAX_CHUNK 64   /* time steps advanced by one launch */
+
 typedef struct bfd_fom_desc {
     int32_t nx, ny;          /* cells in x (fast axis) and y */
     int32_t batch;           /* number of mu samples advanced together */
     int32_t num_steps;       /* T; T+1 snapshots are kept per mu */
     int32_t max_its;         /* Newton cap; the reference passes 100 (:123) */
-    int32_t cells_per_lane;  /* 1 or 2 : columns owned by one lane of the wavefront */
-    double rel_tol;          /* relnorm_cutoff; the reference passes 1e-12 (:123) */
+    int32_t chunk_steps;     /* time steps per launch, 1..BFD_FOM_MAX_CHUNK; 0 = default (25) */
+    int32_t newton_hint;     /* first guess of the Newton solves per step, 1..BFD_FOM_KMAX; 0 = 4 */
+    int32_t strict;          /* 1: iteration counts and iterates exactly as newton_raphson decides
+                                them (a step whose speculated solve count was too high is redone);
+                                0: such a step keeps its further-converged iterate */
+    int32_t uniform_y;       /* 1: cy[r] and cyd[r>0] are one value (held in a register) */
+    int32_t reserved;
+    double rel_tol;          /* relnorm_cutoff, < 1; the reference passes 1e-12 (:123) */
 } bfd_fom_desc;
 
 /* Device pointers to the discretisation inputs listed above. */
@@ -75,7 +84,8 @@ int bfd_fom_set_initial(const bfd_fom_desc *d, void *workspace, const double *w0
 
 /* Advance every sample num_steps steps (Newton to rel_tol each step); returns when done.
  * h_pinned: >= 64 bytes of page-locked host memory used to poll completion.
- * On return h_pinned[0..2] (int32) = {samples finished, device error code, sweeps launched}. */
+ * On return h_pinned[0..3] (int32) = {samples finished, device error code, kernels launched,
+ * time steps that were redone or continued because the speculated solve count was wrong}. */
 int bfd_fom_run(const bfd_fom_desc *d, void *workspace, const bfd_fom_coef *coef, void *h_pinned,
                 void *stream);
 

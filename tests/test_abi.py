@@ -23,19 +23,19 @@ def test_build_and_symbols():
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in include/burgers_b200.h but not exported"
     assert sorted(_lib.SIGNATURES) == declared, "ctypes signatures out of sync with the header"
-    assert lib.bfd_abi_version() == 1
+    assert lib.bfd_abi_version() == 2
 
 
 def test_bad_arguments_are_reported_not_thrown():
     lib = _lib.bind(_build.build())
-    d = _lib.FomDesc(0, 10, 1, 1, 100, 1, 1e-12)
+    d = _lib.fom_desc(0, 10, 1, 1)
     assert lib.bfd_fom_workspace_bytes(ctypes.byref(d)) == 0
     assert lib.bfd_fom_init(ctypes.byref(d), None, 0, None) == -1
-    d = _lib.FomDesc(10, 10, 1, 1, 100, 3, 1e-12)       # cells_per_lane must be 1 or 2
-    assert lib.bfd_fom_workspace_bytes(ctypes.byref(d)) == 0
-    d = _lib.FomDesc(750, 750, 1, 500, 100, 1, 1e-12)
+    for bad in (dict(newton_hint=_lib.FOM_KMAX + 1), dict(chunk_steps=_lib.FOM_MAX_CHUNK + 1), dict(rel_tol=1.0)):
+        assert lib.bfd_fom_workspace_bytes(ctypes.byref(_lib.fom_desc(10, 10, 1, 1, **bad))) == 0
+    d = _lib.fom_desc(750, 750, 1, 500)
     nbytes = lib.bfd_fom_workspace_bytes(ctypes.byref(d))
-    assert 502 * 2 * 750 * 750 * 8 < nbytes < 1.15 * 502 * 2 * 750 * 750 * 8
+    assert 501 * 2 * 750 * 750 * 8 < nbytes < 1.15 * 501 * 2 * 750 * 750 * 8
 
 
 def test_no_cpu_fallback_without_gpu():

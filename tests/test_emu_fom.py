@@ -16,17 +16,22 @@ def rel_err(a, b):
     return (np.linalg.norm(a - b, axis=0) / np.linalg.norm(b, axis=0)).max()
 
 
-@pytest.mark.parametrize("nx,ny,cpl,mus", [
-    (16, 16, 1, [[4.75, 0.02]]),
-    (40, 40, 2, [[5.19, 0.026], [4.3, 0.03]]),     # two strips at CPL=1 width, batch of two
-    (70, 33, 2, [[5.0, 0.02]]),                    # non-square, ragged last strip
+@pytest.mark.parametrize("nx,ny,mus,kw", [
+    (16, 16, [[4.75, 0.02]], {}),
+    (40, 40, [[5.19, 0.026], [4.3, 0.03]], dict(chunk_steps=2)),   # two strips, batch of two
+    (70, 33, [[5.0, 0.02]], dict(uniform_y=False)),               # non-square, ragged last strip, cy[] path
+    (33, 20, [[5.0, 0.02]], dict(newton_hint=1, chunk_steps=1)),   # under-speculated: continuation passes
+    (20, 20, [[4.4, 0.016]], dict(newton_hint=6)),                 # over-speculated: the step is redone
 ])
-def test_emulated_fom_matches_oracle(lib, nx, ny, cpl, mus):
+def test_emulated_fom_matches_oracle(lib, nx, ny, mus, kw):
     gx, gy = orc.make_2D_grid(0, 100, 0, 100, nx, ny)
     w0 = np.ones(2 * nx * ny)
-    snaps, its, rel = E.fom_run(lib, gx, gy, w0, 0.05, 2, mus, cpl=cpl)
+    stats = {}
+    snaps, its, rel = E.fom_run(lib, gx, gy, w0, 0.05, 3, mus, stats=stats, **kw)
+    if "newton_hint" in kw:
+        assert stats["redone"] >= 1
     for m, mu in enumerate(mus):
-        ref, hist = orc.fom_trajectory(gx, gy, w0, 0.05, 2, mu, return_info=True)
+        ref, hist = orc.fom_trajectory(gx, gy, w0, 0.05, 3, mu, return_info=True)
         assert its[m].tolist() == [len(h) for h in hist]
         assert rel_err(snaps[m], ref) < 1e-13
         assert np.all(rel[m] < 1e-12)
@@ -39,6 +44,21 @@ def test_emulated_fom_golden(lib, golden):
     snaps, its, _ = E.fom_run(lib, gx, gy, np.ones(2 * n * n), float(g["dt"]), 6, [list(g["mu"])])
     assert its[0].tolist() == list(g["newton_its"][:6])
     assert rel_err(snaps[0], g["snaps"][:, :7]) < 1e-13
+
+
+def test_emulated_non_strict_keeps_converged_iterate(lib):
+    """strict=False never redoes an over-speculated step: the iterate is the further-converged
+    x_K, still a root of the step to the Newton tolerance and within 1e-10 of the reference."""
+    n = 20
+    gx, gy = orc.make_2D_grid(0, 100, 0, 100, n, n)
+    w0 = np.ones(2 * n * n)
+    stats = {}
+    snaps, its, rel = E.fom_run(lib, gx, gy, w0, 0.05, 3, [[4.75, 0.02]], newton_hint=5, strict=False,
+                                stats=stats)
+    ref = orc.fom_trajectory(gx, gy, w0, 0.05, 3, [4.75, 0.02])
+    assert stats["redone"] == 0
+    assert rel_err(snaps[0], ref) < 1e-12
+    assert np.all(rel[0] < 1e-12)
 
 
 def test_emulated_max_its_cap(lib):
