@@ -52,6 +52,7 @@ SIGNATURES = {
     "bfd_fom_run": (C.c_int, [C.POINTER(FomDesc), _P, C.POINTER(FomCoef), _P, _P]),
     "bfd_fom_export": (C.c_int, [C.POINTER(FomDesc), _P, C.c_int, C.c_int, C.c_int, C.c_int,
                                  C.c_size_t, _P, _P]),
+    "bfd_fom_trace": (C.c_int, [C.POINTER(FomDesc), _P, _P, _P]),
     "bfd_fom_diagnostics": (C.c_int, [C.POINTER(FomDesc), _P, _P, _P, _P]),
     "bfd_residual": (C.c_int, [C.c_int, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
 }

@@ -71,7 +71,7 @@ struct FomGlobal {         // one per workspace, 64 bytes
 struct FomLayout {         // byte offsets inside the workspace
     Ssl ssl;
     int batch, num_steps, chunk;
-    size_t off_global, off_ctl, off_its, off_relnorm, off_steprec, off_arrive, off_partial, off_edge,
+    size_t off_global, off_ctl, off_its, off_relnorm, off_steprec, off_arrive, off_partial, off_trace, off_edge,
         off_pool, total;
     size_t edge_stride_strip;  // doubles: one strip boundary, [chunk][ny][kRecDoubles]
     size_t edge_stride_mu;     // doubles
@@ -110,6 +110,7 @@ static FomLayout fom_layout(const bfd_fom_desc *d) {
     L.off_steprec = o;  o = align_up(o + sizeof(StepRec) * B * S, 256);
     L.off_arrive = o;   o = align_up(o + sizeof(unsigned) * B * S, 256);
     L.off_partial = o;  o = align_up(o + sizeof(double) * B * S * ns * kNormSlots, 256);
+    L.off_trace = o;    o = align_up(o + sizeof(unsigned long long) * B * S * ns * 2, 256);
     L.edge_stride_strip = S * (size_t)d->ny * kRecDoubles;
     L.edge_stride_mu = L.edge_stride_strip * (ns > 1 ? ns - 1 : 0);
     L.off_edge = o;     o = align_up(o + sizeof(double) * L.edge_stride_mu * B, 256);
@@ -132,6 +133,7 @@ struct FomArgs {
     StepRec *steprec;   // [batch][chunk]
     unsigned *arrive;   // [batch][chunk]
     double *partial;    // [batch][chunk][nstrips][kNormSlots]
+    unsigned long long *trace;   // [batch][chunk][nstrips][2] globaltimer at the start / end of a strip's time step
     double *edge;       // [batch][nstrips-1][chunk][ny][kRecDoubles]
     double *pool;       // [batch][num_steps+1][state]   snapshot t of sample m in slot t
     size_t edge_stride_strip, edge_stride_mu, pool_stride_mu;
@@ -152,6 +154,7 @@ static FomArgs fom_args(const bfd_fom_desc *d, const FomLayout &L, void *ws) {
     a.steprec = (StepRec *)(b + L.off_steprec);
     a.arrive = (unsigned *)(b + L.off_arrive);
     a.partial = (double *)(b + L.off_partial);
+    a.trace = (unsigned long long *)(b + L.off_trace);
     a.edge = (double *)(b + L.off_edge);
     a.pool = (double *)(b + L.off_pool);
     a.edge_stride_strip = L.edge_stride_strip;
@@ -196,7 +199,7 @@ struct Level {            // what a cell hands to its right (L) and lower (D) ne
 //   rv = [v + cy Hh + cx Gh - cyd Hh_D - cxl Gh_L] + Av,  Av = -vp + cy Hp + cx Gp - cyd Hp_D - cxl Gp_L
 // Au, Av do not change between Newton levels and ride along the level pipeline.
 template <int K, bool CONT, bool UNI>
-__device__ __noinline__ void sweep_step(const StepIo &io) {
+__device__ __forceinline__ void sweep_step(const StepIo &io) {
     constexpr int NPR = 2 * K + 1 + (CONT ? 1 : 0);
     constexpr int PF = 4;
     constexpr int W = 32;
@@ -461,11 +464,16 @@ __global__ void __launch_bounds__(32) fom_chunk_kernel(const FomArgs a) {
     if (item >= a.batch * nstrips) return;
     const int m = item / nstrips, j = item - m * nstrips;
     FomCtl *ctl = a.ctl + m;
-    const int t0 = ctl->t;
+    // control words are read by lane 0 and broadcast: the compiler then knows they are
+    // warp-uniform and keeps the shuffles of the sweep free of convergence bookkeeping
+    int c_t = 0, c_kbase = 0, c_kfirst = 0, c_kspec = 0, c_chunk = 0;
+    if (lane == 0) { c_t = ctl->t; c_kbase = ctl->kbase; c_kfirst = ctl->k_first; c_kspec = ctl->k_spec; c_chunk = ctl->chunk; }
+    const int t0 = __shfl_sync(0xffffffffu, c_t, 0);
     if (t0 >= a.num_steps) return;   // this sample has finished its trajectory
-    const int kbase = ctl->kbase, k_first = ctl->k_first, k_spec = ctl->k_spec;
+    const int kbase = __shfl_sync(0xffffffffu, c_kbase, 0), k_first = __shfl_sync(0xffffffffu, c_kfirst, 0),
+              k_spec = __shfl_sync(0xffffffffu, c_kspec, 0);
     const double init_prev = ctl->init_norm;
-    int n = ctl->chunk;
+    int n = __shfl_sync(0xffffffffu, c_chunk, 0);
     if (n > a.num_steps - t0) n = a.num_steps - t0;
 
     const int nx = a.ssl.nx, ny = a.ssl.ny;
@@ -498,6 +506,8 @@ __global__ void __launch_bounds__(32) fom_chunk_kernel(const FomArgs a) {
         io.edge_in = edge_m + (size_t)(j > 0 ? j - 1 : 0) * a.edge_stride_strip + eoff;
         io.edge_out = edge_m + (size_t)(j < nstrips - 1 ? j : 0) * a.edge_stride_strip + eoff;
         io.partial = a.partial + ((size_t)(m * a.chunk + i) * nstrips + j) * kNormSlots;
+        unsigned long long *tr = a.trace + ((size_t)(m * a.chunk + i) * nstrips + j) * 2;
+        if (lane == 0) tr[0] = global_timer_ns();
         if (kb) {
             sweep_step<1, true, UNI>(io);
         } else {
@@ -512,6 +522,7 @@ __global__ void __launch_bounds__(32) fom_chunk_kernel(const FomArgs a) {
         }
         __syncwarp();
         if (lane == 0) {
+            tr[1] = global_timer_ns();
             __threadfence();
             if (atomicInc(&a.arrive[(size_t)m * a.chunk + i], (unsigned)nstrips - 1) == (unsigned)nstrips - 1) {
                 __threadfence();
@@ -736,6 +747,15 @@ extern "C" int bfd_fom_export(const bfd_fom_desc *d, const void *ws, int mu_inde
     dim3 grid(d->ny + kSkew, L.ssl.nstrips), block(32, 8);
     BFD_LAUNCH(fom_export_kernel, grid, block, 0, (cudaStream_t)stream, a, mu_index, t0, t1, layout, ld, out);
     BFD_LAUNCHED();
+    return BFD_OK;
+}
+
+extern "C" int bfd_fom_trace(const bfd_fom_desc *d, const void *ws, uint64_t *out, void *stream) {
+    if (check_desc(d) != BFD_OK || !ws || !out) return BFD_EINVAL;
+    const FomLayout L = fom_layout(d);
+    const FomArgs a = fom_args(d, L, const_cast<void *>(ws));
+    const size_t n = (size_t)d->batch * L.chunk * L.ssl.nstrips * 2;
+    BFD_CUDA(cudaMemcpyAsync(out, a.trace, n * sizeof(uint64_t), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
     return BFD_OK;
 }
 

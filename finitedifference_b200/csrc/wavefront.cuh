@@ -34,6 +34,11 @@ __device__ __forceinline__ double rcp_fast(double x) {
     return fma(r, e, r);
 }
 __device__ __forceinline__ void spin_pause() { __nanosleep(20); }
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
 #else
 inline void ld_volatile2(const double *p, double &a, double &b) {
     std::this_thread::yield();
@@ -50,6 +55,7 @@ inline void cp_async16(double *dst, const double *src) { ld_volatile2(src, dst[0
 inline void cp_async_wait_all() {}
 inline double rcp_fast(double x) { return 1.0 / x; }
 inline void spin_pause() { std::this_thread::yield(); }
+inline unsigned long long global_timer_ns() { return 0; }
 #endif
 
 __device__ __forceinline__ bool is_sentinel(double x) {
@@ -100,30 +106,49 @@ struct EdgeIn {
         }
     }
     // Whole warp, every step; works when step `s` opens a block.  Returns BFD_ETIMEOUT once if
-    // the producer never showed up (the block then reads as zeros).
+    // the producer never showed up (the block then reads as zeros).  Every branch is
+    // warp-uniform (votes), so the caller's shuffles stay convergent.
     __device__ __forceinline__ int open(int s) {
         if (!active || s >= ny || (s % kEdgeBlock) != 0) return 0;
         int err = 0;
         cp_async_wait_all();
+        double p0[kIters], p1[kIters];
+        bool mine[kIters];
 #pragma unroll
         for (int it = 0; it < kIters; ++it) {
             const int q = lane + 32 * it, row = s + q / NPR, piece = q % NPR;
-            if (q < kEdgeBlock * NPR && row < ny) {
-                double *slot = ring + (row % kInRing) * kRecDoubles + 2 * piece;
-                double *src = g + (size_t)row * kRecDoubles + 2 * piece;
-                double p0 = slot[0], p1 = slot[1];
-                unsigned spins = 0;
-                while (!dead && (is_sentinel(p0) || is_sentinel(p1))) {
-                    if (++spins > kSpinLimit) { dead = true; err = BFD_ETIMEOUT; break; }
-                    if (spins > 4) spin_pause();
-                    ld_volatile2(src, p0, p1);
+            mine[it] = q < kEdgeBlock * NPR && row < ny;
+            const double *slot = ring + ((mine[it] ? row : s) % kInRing) * kRecDoubles + 2 * (mine[it] ? piece : 0);
+            p0[it] = slot[0]; p1[it] = slot[1];
+        }
+        if (!dead) {
+            unsigned spins = 0;
+            for (;;) {
+                bool ok = true;
+#pragma unroll
+                for (int it = 0; it < kIters; ++it)
+                    ok = ok && (!mine[it] || !(is_sentinel(p0[it]) || is_sentinel(p1[it])));
+                if (__all_sync(0xffffffffu, ok)) break;
+                if (++spins > kSpinLimit) { dead = true; err = BFD_ETIMEOUT; break; }
+                if (spins > 2) spin_pause();
+#pragma unroll
+                for (int it = 0; it < kIters; ++it) {
+                    const int q = lane + 32 * it, row = s + q / NPR, piece = q % NPR;
+                    if (mine[it] && (is_sentinel(p0[it]) || is_sentinel(p1[it])))
+                        ld_volatile2(g + (size_t)row * kRecDoubles + 2 * piece, p0[it], p1[it]);
                 }
-                if (dead) { p0 = 0.0; p1 = 0.0; }
-                else st_volatile2(src, sentinel_value(), sentinel_value());   // re-arm
-                slot[0] = p0; slot[1] = p1;
             }
         }
-        dead = !__all_sync(0xffffffffu, !dead);
+#pragma unroll
+        for (int it = 0; it < kIters; ++it) {
+            const int q = lane + 32 * it, row = s + q / NPR, piece = q % NPR;
+            if (mine[it]) {
+                double *slot = ring + (row % kInRing) * kRecDoubles + 2 * piece;
+                slot[0] = dead ? 0.0 : p0[it];
+                slot[1] = dead ? 0.0 : p1[it];
+                if (!dead) st_volatile2(g + (size_t)row * kRecDoubles + 2 * piece, sentinel_value(), sentinel_value());   // re-arm
+            }
+        }
         __syncwarp();
         if (!dead && s + kEdgeBlock < ny) prefetch(s + kEdgeBlock);
         return err;

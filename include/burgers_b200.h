@@ -101,6 +101,12 @@ int bfd_fom_export(const bfd_fom_desc *d, const void *workspace, int mu_index, i
 int bfd_fom_diagnostics(const bfd_fom_desc *d, const void *workspace, int32_t *its,
                         double *relnorm, void *stream);
 
+/* Pipeline trace of the most recent launches: for every (sample, time step of the launch,
+ * strip) the %globaltimer (ns) at which the strip started and finished that time step.
+ * out: uint64 [batch][chunk_steps][nstrips][2], device pointer; nstrips = ceil(nx/32).  Entries
+ * of steps a launch did not run keep older values.  Profiling aid (see profiles/). */
+int bfd_fom_trace(const bfd_fom_desc *d, const void *workspace, uint64_t *out, void *stream);
+
 /* Number of kernels launched by this library since load (for bench.py's gpu_launches). */
 uint64_t bfd_launch_count(void);
 
