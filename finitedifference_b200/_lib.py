@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "_burgers_b200.so")
+LIB_PATH = os.environ.get("BFD_LIB") or os.path.join(HERE, "_burgers_b200.so")   # BFD_LIB: profiling variants
 
 BFD_OK = 0
 ERRORS = {-1: "BFD_EINVAL", -2: "BFD_ECUDA", -3: "BFD_EWORKSPACE", -4: "BFD_ETIMEOUT",

@@ -167,14 +167,26 @@ static FomArgs fom_args(const bfd_fom_desc *d, const FomLayout &L, void *ws) {
 
 namespace bfd {
 
-// What one warp needs to run one time step of its strip.
+#ifndef BFD_WARPS
+#define BFD_WARPS 4
+#endif
+constexpr int kWarpsPerStrip = BFD_WARPS;     // warps sharing the Newton levels of one strip
+constexpr int kHandValues = 6;                 // x (2), Au, Av, and cy, cyd of the row on non-uniform grids
+constexpr int kHandDoubles = 2 * kHandValues * 32;   // one level hand-off between two warps: [2 buffers][values][32 lanes]
+constexpr int kPfDepth = 6;                    // rows of level-0 input in flight (cp.async ring in shared memory)
+constexpr int kPfValues = 7;                   // u, v, up, vp (CONT), lbc (inlet lane), cy, cyd (non-uniform grids)
+constexpr int kPfDoubles = kPfDepth * kPfValues * 32;
+
+// What one warp needs to run its levels of one time step of its strip.
 struct StepIo {
     const double *xin;    // level-0 iterate: snapshot t, or the partly converged x of slot t+1 (CONT)
     const double *xwp;    // snapshot t
     double *xout;         // slot t+1 (all three already offset to this strip and lane)
     double *edge_in;      // hand-off records of the strip on the left for this time step
     double *edge_out;     // ... and the ones this strip produces
-    double *ring_in, *ring_out;   // shared memory of this warp
+    double *ring_in, *ring_out;   // shared memory of this CTA
+    double *hand;         // shared memory: level hand-off between the warps of the CTA
+    double *pf;           // shared memory: prefetch ring of the level-0 input [kPfDepth][kPfValues][32]
     double *partial;      // [kNormSlots] squared residual norms of this (sample, step, strip)
     const double *lbc;    // [ny] inlet term of this sample
     const double *cy, *cyd;
@@ -189,8 +201,10 @@ struct Level {            // what a cell hands to its right (L) and lower (D) ne
     double pu, pm, pvv;   // u*du, v*du + u*dv, v*dv
 };
 
-// One trapezoidal time step of one strip: K fused Newton solves plus the residual of x_K.
-//   K     solves applied in this pass (levels 0..K-1 solve, level K evaluates ||r(x_K)||)
+// Levels LO..HI-1 of one trapezoidal time step of one strip.  A time step is K fused Newton
+// solves (levels 0..K-1) plus the residual of x_K (level K); the levels are split between the
+// warps of the CTA, which pass the iterate from level HI-1 to level HI through shared memory
+// and meet at one CTA barrier per wavefront step.
 //   CONT  continuation pass: the level-0 iterate differs from the previous snapshot
 //   UNI   cy / cyd are the same for every row (kept in registers)
 // Residual in the form used here (hypernet2D.py:2619-2643 regrouped): with Fh = u^2/2,
@@ -198,10 +212,11 @@ struct Level {            // what a cell hands to its right (L) and lower (D) ne
 //   ru = [u + cx Fh + cy Gh - cxl Fh_L - cyd Gh_D] + Au,  Au = -up + cx Fp + cy Gp - cxl Fp_L - cyd Gp_D - src - lbc
 //   rv = [v + cy Hh + cx Gh - cyd Hh_D - cxl Gh_L] + Av,  Av = -vp + cy Hp + cx Gp - cyd Hp_D - cxl Gp_L
 // Au, Av do not change between Newton levels and ride along the level pipeline.
-template <int K, bool CONT, bool UNI>
-__device__ __forceinline__ void sweep_step(const StepIo &io) {
+template <int K, int LO, int HI, bool CONT, bool UNI>
+__device__ __forceinline__ void sweep_part(const StepIo &io) {
     constexpr int NPR = 2 * K + 1 + (CONT ? 1 : 0);
-    constexpr int PF = 4;
+    constexpr bool FIRST = (LO == 0), LAST = (HI == K + 1);
+    constexpr int NL = HI - LO;              // levels of this warp
     constexpr int W = 32;
     const int lane = io.lane, ny = io.ny;
     const int last_row = ny + kSkew - 1;   // last slot-row holding cells
@@ -209,7 +224,7 @@ __device__ __forceinline__ void sweep_step(const StepIo &io) {
 
     EdgeIn<NPR> ein;
     EdgeOut<NPR> eout;
-    ein.init(io.edge_in, io.ring_in, ny, lane, io.strip > 0);
+    ein.init(io.edge_in, io.ring_in, ny, lane, io.strip > 0, FIRST);
     eout.init(io.edge_out, io.ring_out, ny, lane, io.strip < io.nstrips - 1);
     const bool from_edge = (lane == 0) && io.strip > 0;
     const bool to_edge = (lane == 31) && io.strip < io.nstrips - 1;
@@ -219,52 +234,75 @@ __device__ __forceinline__ void sweep_step(const StepIo &io) {
     double cyU = 0.0, cydU = 0.0;
     if (UNI) { cyU = __ldg(io.cy + (ny > 1 ? 1 : 0)); cydU = __ldg(io.cyd + (ny > 1 ? 1 : 0)); }
 
-    // register prefetch ring of the level-0 input, rows s .. s+PF-1
-    double bu[PF], bv[PF], bup[PF], bvp[PF];
-    auto load = [&](int s, int i) {
-        const size_t o = (size_t)(s < last_row ? s : last_row) * (2 * W);
-        bu[i] = io.xin[o];
-        bv[i] = io.xin[o + W];
-        if (CONT) { bup[i] = io.xwp[o]; bvp[i] = io.xwp[o + W]; }
-        else { bup[i] = 0.0; bvp[i] = 0.0; }
+    // Level-0 input, prefetched kPfDepth-1 rows ahead into shared memory with cp.async (first
+    // warp only; each lane copies and later reads its own 8-byte elements).  One commit group
+    // per wavefront step, so "all but the newest kPfDepth-2 groups" is exactly "row s has
+    // landed" -- unlike register prefetching, where every LDG shares one counting scoreboard
+    // and the first use of the oldest load also waits for the newest.
+    auto pf_slot = [&](int row) { return io.pf + (size_t)(row % kPfDepth) * (kPfValues * 32) + lane; };
+    auto pf_issue = [&](int row) {
+        const int r = row < last_row ? row : last_row;
+        const size_t o = (size_t)r * (2 * W);
+        double *d = pf_slot(row);
+        cp_async8(d, io.xin + o);
+        cp_async8(d + 32, io.xin + o + W);
+        if (CONT) { cp_async8(d + 64, io.xwp + o); cp_async8(d + 96, io.xwp + o + W); }
+        const int rc = r - lane < 0 ? 0 : (r - lane >= ny ? ny - 1 : r - lane);   // grid row of this lane's cell
+        if (io.inlet) cp_async8(d + 128, io.lbc + rc);
+        if (!UNI) { cp_async8(d + 160, io.cy + rc); cp_async8(d + 192, io.cyd + rc); }
     };
+    if (FIRST) {
 #pragma unroll
-    for (int i = 0; i < PF; ++i) load(i, i);
+        for (int i = 0; i < kPfDepth - 1; ++i) { pf_issue(i); cp_async_commit(); }
+    }
 
-    Level prev[K];            // own cell of the previous step at each level = upper neighbour now
-    double pFh = 0.0, pGh = 0.0, pHh = 0.0;   // level K (residual only)
+    Level prev[K + 1];        // own cell of the previous step at each level = upper neighbour now
     double qFp = 0.0, qGp = 0.0, qHp = 0.0;   // previous-snapshot flux parts of the previous row (CONT)
 #pragma unroll
-    for (int k = 0; k < K; ++k) prev[k] = Level{0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-    double xu[K + 1], xv[K + 1], Au[K + 1], Av[K + 1], nrm[K + 1];
+    for (int k = 0; k <= K; ++k) prev[k] = Level{0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    double xu[K + 2], xv[K + 2], Au[K + 2], Av[K + 2], Cy[K + 2], Cyd[K + 2], nrm[K + 1];
 #pragma unroll
-    for (int k = 0; k <= K; ++k) { xu[k] = xv[k] = Au[k] = Av[k] = 0.0; nrm[k] = 0.0; }
+    for (int k = 0; k <= K + 1; ++k) { xu[k] = xv[k] = Au[k] = Av[k] = 0.0; Cy[k] = cyU; Cyd[k] = cydU; }
+#pragma unroll
+    for (int k = 0; k <= K; ++k) nrm[k] = 0.0;
+    double *hand_in = io.hand - kHandDoubles;    // written by the previous warp of the CTA
+    double *hand_out = io.hand;
 
-    for (int s0 = 0; s0 < nsteps; s0 += PF) {
-#pragma unroll
-        for (int i = 0; i < PF; ++i) {
-            const int s = s0 + i;
-            if (s >= nsteps) break;   // warp-uniform
-            {
+    for (int s = 0; s < nsteps; ++s) {
+        {
+            double up = 0.0, vp = 0.0, lb = 0.0;
+            if (FIRST) {
+                cp_async_wait_pending<kPfDepth - 2>();      // row s (and any hand-off block due) has landed
                 const int err = ein.open(s);
                 if (err && lane == 0) atomicExch(io.error, err);
+                const double *d = pf_slot(s);
+                xu[0] = d[0]; xv[0] = d[32];
+                up = CONT ? d[64] : xu[0]; vp = CONT ? d[96] : xv[0];
+                if (io.inlet) lb = d[128];
+                if (!UNI) { Cy[0] = d[160]; Cyd[0] = d[192]; }
+#ifndef BFD_X_NOLOAD
+                pf_issue(s + kPfDepth - 1);                 // refills the slot read one step ago
+#endif
+                cp_async_commit();
+            } else {
+                // x_LO and the level-independent terms of row s - lane - LO, produced by the
+                // previous warp one step ago
+                const double *h = hand_in + ((s + 1) & 1) * (kHandValues * 32) + lane;
+                xu[LO] = h[0]; xv[LO] = h[32]; Au[LO] = h[64]; Av[LO] = h[96];
+                if (!UNI) { Cy[LO] = h[128]; Cyd[LO] = h[160]; }
             }
-            xu[0] = bu[i]; xv[0] = bv[i];
-            const double up = CONT ? bup[i] : xu[0], vp = CONT ? bvp[i] : xv[0];
-            load(s + PF, i);
 
-            // left neighbours (r, c-1): lane-1's cells of the previous step, every level
-            double LF[K + 1], LG[K + 1], Lpu[K], Lpm[K], LFp = 0.0, LGp = 0.0;
+            // left neighbours (r, c-1): lane-1's cells of the previous step, own levels
+            double LF[K + 1], LG[K + 1], Lpu[K + 1], Lpm[K + 1], LFp = 0.0, LGp = 0.0;
 #pragma unroll
-            for (int k = 0; k < K; ++k) {
+            for (int k = LO; k < HI; ++k) {
                 LF[k] = shfl_up1(prev[k].Fh); LG[k] = shfl_up1(prev[k].Gh);
-                Lpu[k] = shfl_up1(prev[k].pu); Lpm[k] = shfl_up1(prev[k].pm);
+                if (k < K) { Lpu[k] = shfl_up1(prev[k].pu); Lpm[k] = shfl_up1(prev[k].pm); }
             }
-            LF[K] = shfl_up1(pFh); LG[K] = shfl_up1(pGh);
-            if (CONT) { LFp = shfl_up1(qFp); LGp = shfl_up1(qGp); }
+            if (CONT && FIRST) { LFp = shfl_up1(qFp); LGp = shfl_up1(qGp); }
             if (lane == 0) {
 #pragma unroll
-                for (int k = 0; k <= K; ++k) {
+                for (int k = LO; k < HI; ++k) {
                     const int rk = s - k;
                     const bool take = from_edge && (unsigned)rk < (unsigned)ny;
                     const double *rec = ein.row(take ? rk : 0);
@@ -284,14 +322,12 @@ __device__ __forceinline__ void sweep_step(const StepIo &io) {
             // levels in descending order: level k+1 consumes xu[k+1], Au[k+1] before level k
             // replaces them with the values for the next step
 #pragma unroll
-            for (int k = K; k >= 0; --k) {
+            for (int k = HI - 1; k >= LO; --k) {
                 const int rk = s - lane - k;
                 const bool rowok = (unsigned)rk < (unsigned)ny;
                 const bool valid = rowok && io.colok;
                 const bool top = (rk <= 0);      // no upper neighbour (row -1 is not a cell)
-                double cy, cyd;
-                if (UNI) { cy = cyU; cyd = cydU; }
-                else { const int rr = rowok ? rk : 0; cy = __ldg(io.cy + rr); cyd = __ldg(io.cyd + rr); }
+                const double cy = UNI ? cyU : Cy[k], cyd = UNI ? cydU : Cyd[k];
                 const double hcy = 0.5 * cy, hcyd = 0.5 * cyd, ncyd = -cyd;
                 double *orec = eout.row(rowok ? rk : 0);
                 const bool put = to_edge && rowok;
@@ -303,7 +339,6 @@ __device__ __forceinline__ void sweep_step(const StepIo &io) {
                     const double DGp = top ? 0.0 : (CONT ? qGp : prev[0].Gh);
                     const double DHp = top ? 0.0 : (CONT ? qHp : prev[0].Hh);
                     const double lFp = CONT ? LFp : LF[0], lGp = CONT ? LGp : LG[0];
-                    const double lb = (io.inlet && rowok) ? __ldg(io.lbc + rk) : 0.0;
                     double au = fma(cx, Fp, -up);
                     au = fma(cy, Gp, au); au = fma(ncxl, lFp, au); au = fma(ncyd, DGp, au);
                     au = (au - src) - lb;
@@ -319,9 +354,7 @@ __device__ __forceinline__ void sweep_step(const StepIo &io) {
                 const double u = xu[k], v = xv[k];
                 const double hu = 0.5 * u, hv = 0.5 * v;
                 const double Fh = hu * u, Gh = hu * v, Hh = hv * v;
-                double DG, DH;
-                if (k < K) { DG = top ? 0.0 : prev[k].Gh; DH = top ? 0.0 : prev[k].Hh; }
-                else { DG = top ? 0.0 : pGh; DH = top ? 0.0 : pHh; }
+                const double DG = top ? 0.0 : prev[k].Gh, DH = top ? 0.0 : prev[k].Hh;
                 double ru = Au[k] + u;
                 ru = fma(cx, Fh, ru); ru = fma(cy, Gh, ru); ru = fma(ncxl, LF[k], ru); ru = fma(ncyd, DG, ru);
                 double rv = Av[k] + v;
@@ -345,32 +378,86 @@ __device__ __forceinline__ void sweep_step(const StepIo &io) {
                     prev[k] = c;
                     xu[k + 1] = u - du; xv[k + 1] = v - dv;
                     Au[k + 1] = Au[k]; Av[k + 1] = Av[k];
+                    if (!UNI) { Cy[k + 1] = Cy[k]; Cyd[k + 1] = Cyd[k]; }
                     if (put) { orec[4 * k] = Fh; orec[4 * k + 1] = Gh; orec[4 * k + 2] = c.pu; orec[4 * k + 3] = c.pm; }
                     if (k == K - 1) {
                         // x_K of row rk: slot-row (rk + lane) of the output state
                         const int so = s - (K - 1);
+#ifdef BFD_X_NOSTORE
+                        if (so == 0) {
+#else
                         if (so >= 0 && so <= last_row) {
+#endif
                             double *o = io.xout + (size_t)so * (2 * W);
                             o[0] = valid ? xu[K] : 0.0;
                             o[W] = valid ? xv[K] : 0.0;
                         }
                     }
                 } else {
-                    pFh = Fh; pGh = Gh; pHh = Hh;
+                    prev[K].Fh = Fh; prev[K].Gh = Gh; prev[K].Hh = Hh;
                     if (put) { orec[4 * K] = Fh; orec[4 * K + 1] = Gh; }
                 }
             }
-            eout.close(s - kSkew - K);
+            if (!LAST) {
+                double *h = hand_out + (s & 1) * (kHandValues * 32) + lane;
+                h[0] = xu[HI]; h[32] = xv[HI]; h[64] = Au[HI]; h[96] = Av[HI];
+                if (!UNI) { h[128] = Cy[HI]; h[160] = Cyd[HI]; }
+            }
+#ifndef BFD_X_NOEDGEOUT
+            if (LAST) eout.close(s - kSkew - K);
+#endif
+#ifndef BFD_X_NOBAR
+            if (kWarpsPerStrip > 1) __syncthreads();
+#endif
         }
     }
 
     // ||r(x_k)||^2 of this strip, fixed reduction order (deterministic iteration counts)
 #pragma unroll
-    for (int k = 0; k <= K; ++k) {
+    for (int k = LO; k < HI; ++k) {
         double x = nrm[k];
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) x += __shfl_xor_sync(0xffffffffu, x, off);
         if (lane == 0) io.partial[k] = x;
+    }
+    (void)NL;
+}
+
+// A warp with no level in this pass only keeps the CTA's barrier count.
+template <int K>
+__device__ __forceinline__ void idle_part(const StepIo &io) {
+    const int nsteps = io.ny + kSkew + K;
+    for (int s = 0; s < nsteps; ++s) __syncthreads();
+}
+
+// First level of warp w when the K+1 levels of a pass (K solves + the residual of x_K) are
+// split between kWarpsPerStrip = 4 warps; warp w runs levels [part(K, w), part(K, w+1)).
+// Balanced by FP64 work: level 0 also forms Au, Av (57 ops), a solve level is 46, the
+// residual level 17.
+__host__ __device__ constexpr int part(int K, int w) {
+    if (kWarpsPerStrip == 1) return w == 0 ? 0 : K + 1;
+    if (kWarpsPerStrip == 2) return w == 0 ? 0 : (w == 1 ? (K + 1) / 2 : K + 1);
+    if (K + 1 <= 4) return w < K + 1 ? w : K + 1;
+    if (K == 4) return w == 0 ? 0 : w == 1 ? 1 : w == 2 ? 2 : w == 3 ? 3 : 5;
+    if (K == 5) return w == 0 ? 0 : w == 1 ? 1 : w == 2 ? 3 : w == 3 ? 4 : 6;
+    return w == 0 ? 0 : w == 1 ? 1 : w == 2 ? 3 : w == 3 ? 5 : 7;     // K == 6
+}
+
+template <int K, int WARP, bool CONT, bool UNI>
+__device__ __forceinline__ void sweep_warp(const StepIo &io) {
+    constexpr int LO = part(K, WARP), HI = part(K, WARP + 1);
+    if constexpr (LO < HI) sweep_part<K, LO, HI, CONT, UNI>(io);
+    else idle_part<K>(io);
+}
+
+// The K+1 levels of a time step split between the warps of the CTA.
+template <int K, bool CONT, bool UNI>
+__device__ __forceinline__ void sweep_step(const StepIo &io, int warp) {
+    if (warp == 0) sweep_warp<K, 0, CONT, UNI>(io);
+    if constexpr (kWarpsPerStrip > 1) { if (warp == 1) sweep_warp<K, 1, CONT, UNI>(io); }
+    if constexpr (kWarpsPerStrip > 2) {
+        if (warp == 2) sweep_warp<K, 2, CONT, UNI>(io);
+        if (warp == 3) sweep_warp<K, 3, CONT, UNI>(io);
     }
 }
 
@@ -448,33 +535,42 @@ __device__ void commit_chunk(const FomArgs &a, int m, int t0, int n, int kbase, 
     if (t >= a.num_steps) atomicAdd(&a.glob->done, 1);
 }
 
-// Up to `chunk` time steps of every unfinished sample.  One warp per CTA <-> (sample m, strip j);
-// virtual ids come from a ticket so that a strip's left neighbour (a smaller id) is always
-// already running when the strip waits on it.
+// Up to `chunk` time steps of every unfinished sample.  One CTA of kWarpsPerStrip warps <->
+// (sample m, strip j); virtual ids come from a ticket so that a strip's left neighbour (a
+// smaller id) is always already running when the strip waits on it.
 template <bool UNI>
-__global__ void __launch_bounds__(32) fom_chunk_kernel(const FomArgs a) {
+__global__ void __launch_bounds__(32 * kWarpsPerStrip, kWarpsPerStrip == 4 ? 4 : 6) fom_chunk_kernel(const FomArgs a) {
     BFD_SHARED_ARRAY(double, s_in, [kInRing * kRecDoubles]);
     BFD_SHARED_ARRAY(double, s_out, [kOutRing * kRecDoubles]);
-    const int lane = threadIdx.x;
-    unsigned vb = 0;
-    if (lane == 0) vb = atomicInc(&a.glob->ticket, gridDim.x - 1);
-    vb = __shfl_sync(0xffffffffu, vb, 0);
+    BFD_SHARED_ARRAY(double, s_hand, [kWarpsPerStrip * kHandDoubles]);
+    BFD_SHARED_ARRAY(double, s_pf, [kPfDoubles]);
+    BFD_SHARED_ARRAY(int, s_ctl, [8]);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nstrips = a.ssl.nstrips;
-    const int item = (int)vb;
-    if (item >= a.batch * nstrips) return;
+    for (int i = threadIdx.x; i < kWarpsPerStrip * kHandDoubles; i += blockDim.x) s_hand[i] = 0.0;
+    if (threadIdx.x == 0) {
+        const int item = (int)atomicInc(&a.glob->ticket, gridDim.x - 1);
+        s_ctl[0] = item;
+        s_ctl[1] = a.num_steps;      // t: "finished" unless the item is real
+        if (item < a.batch * nstrips) {
+            const FomCtl *c = a.ctl + item / nstrips;
+            s_ctl[1] = c->t; s_ctl[2] = c->kbase; s_ctl[3] = c->k_first; s_ctl[4] = c->k_spec; s_ctl[5] = c->chunk;
+        }
+    }
+    __syncthreads();
+    // control words are broadcast by shuffle: the compiler then knows they are warp-uniform
+    // and keeps the shuffles of the sweep free of convergence bookkeeping
+    int w = (lane < 8) ? s_ctl[lane] : 0;
+    const int item = __shfl_sync(0xffffffffu, w, 0);
+    const int t0 = __shfl_sync(0xffffffffu, w, 1);
+    if (t0 >= a.num_steps) return;   // nothing to do, or this sample has finished its trajectory
+    const int kbase = __shfl_sync(0xffffffffu, w, 2), k_first = __shfl_sync(0xffffffffu, w, 3),
+              k_spec = __shfl_sync(0xffffffffu, w, 4);
+    int n = __shfl_sync(0xffffffffu, w, 5);
+    if (n > a.num_steps - t0) n = a.num_steps - t0;
     const int m = item / nstrips, j = item - m * nstrips;
     FomCtl *ctl = a.ctl + m;
-    // control words are read by lane 0 and broadcast: the compiler then knows they are
-    // warp-uniform and keeps the shuffles of the sweep free of convergence bookkeeping
-    int c_t = 0, c_kbase = 0, c_kfirst = 0, c_kspec = 0, c_chunk = 0;
-    if (lane == 0) { c_t = ctl->t; c_kbase = ctl->kbase; c_kfirst = ctl->k_first; c_kspec = ctl->k_spec; c_chunk = ctl->chunk; }
-    const int t0 = __shfl_sync(0xffffffffu, c_t, 0);
-    if (t0 >= a.num_steps) return;   // this sample has finished its trajectory
-    const int kbase = __shfl_sync(0xffffffffu, c_kbase, 0), k_first = __shfl_sync(0xffffffffu, c_kfirst, 0),
-              k_spec = __shfl_sync(0xffffffffu, c_kspec, 0);
     const double init_prev = ctl->init_norm;
-    int n = __shfl_sync(0xffffffffu, c_chunk, 0);
-    if (n > a.num_steps - t0) n = a.num_steps - t0;
 
     const int nx = a.ssl.nx, ny = a.ssl.ny;
     const size_t sd = a.ssl.state_doubles;
@@ -484,6 +580,8 @@ __global__ void __launch_bounds__(32) fom_chunk_kernel(const FomArgs a) {
 
     StepIo io;
     io.ring_in = s_in; io.ring_out = s_out;
+    io.hand = s_hand + warp * kHandDoubles;
+    io.pf = s_pf;
     io.lbc = a.lbc + (size_t)m * ny;
     io.cy = a.cy; io.cyd = a.cyd;
     io.ny = ny; io.strip = j; io.nstrips = nstrips; io.lane = lane;
@@ -507,21 +605,21 @@ __global__ void __launch_bounds__(32) fom_chunk_kernel(const FomArgs a) {
         io.edge_out = edge_m + (size_t)(j < nstrips - 1 ? j : 0) * a.edge_stride_strip + eoff;
         io.partial = a.partial + ((size_t)(m * a.chunk + i) * nstrips + j) * kNormSlots;
         unsigned long long *tr = a.trace + ((size_t)(m * a.chunk + i) * nstrips + j) * 2;
-        if (lane == 0) tr[0] = global_timer_ns();
+        if (threadIdx.x == 0) tr[0] = global_timer_ns();
         if (kb) {
-            sweep_step<1, true, UNI>(io);
+            sweep_step<1, true, UNI>(io, warp);
         } else {
             switch (K) {
-            case 1: sweep_step<1, false, UNI>(io); break;
-            case 2: sweep_step<2, false, UNI>(io); break;
-            case 3: sweep_step<3, false, UNI>(io); break;
-            case 4: sweep_step<4, false, UNI>(io); break;
-            case 5: sweep_step<5, false, UNI>(io); break;
-            default: sweep_step<6, false, UNI>(io); break;
+            case 1: sweep_step<1, false, UNI>(io, warp); break;
+            case 2: sweep_step<2, false, UNI>(io, warp); break;
+            case 3: sweep_step<3, false, UNI>(io, warp); break;
+            case 4: sweep_step<4, false, UNI>(io, warp); break;
+            case 5: sweep_step<5, false, UNI>(io, warp); break;
+            default: sweep_step<6, false, UNI>(io, warp); break;
             }
         }
-        __syncwarp();
-        if (lane == 0) {
+        __syncthreads();       // both warps have published their norms
+        if (threadIdx.x == 0) {
             tr[1] = global_timer_ns();
             __threadfence();
             if (atomicInc(&a.arrive[(size_t)m * a.chunk + i], (unsigned)nstrips - 1) == (unsigned)nstrips - 1) {
@@ -530,7 +628,7 @@ __global__ void __launch_bounds__(32) fom_chunk_kernel(const FomArgs a) {
             }
         }
     }
-    if (lane == 0) {
+    if (threadIdx.x == 0) {
         __threadfence();
         if (atomicInc(&ctl->arrive, (unsigned)nstrips - 1) == (unsigned)nstrips - 1) {
             __threadfence();
@@ -672,9 +770,9 @@ extern "C" int bfd_fom_set_initial(const bfd_fom_desc *d, void *ws, const double
 static int launch_chunk(const FomArgs &a, cudaStream_t st) {
     const int grid = a.batch * a.ssl.nstrips;
     if (a.uniform_y) {
-        BFD_LAUNCH_CORESIDENT(fom_chunk_kernel<true>, grid, 32, 0, st, a);
+        BFD_LAUNCH_CORESIDENT(fom_chunk_kernel<true>, grid, 32 * kWarpsPerStrip, 0, st, a);
     } else {
-        BFD_LAUNCH_CORESIDENT(fom_chunk_kernel<false>, grid, 32, 0, st, a);
+        BFD_LAUNCH_CORESIDENT(fom_chunk_kernel<false>, grid, 32 * kWarpsPerStrip, 0, st, a);
     }
     BFD_LAUNCHED();
     return BFD_OK;

@@ -20,8 +20,16 @@ __device__ __forceinline__ void cp_async16(double *smem_dst, const double *gsrc)
     const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gsrc) : "memory");
 }
-__device__ __forceinline__ void cp_async_wait_all() {
-    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+// 8 bytes global -> shared (each lane copies its own element)
+__device__ __forceinline__ void cp_async8(double *smem_dst, const double *gsrc) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+// wait until at most N of this thread's committed groups are still in flight
+template <int N>
+__device__ __forceinline__ void cp_async_wait_pending() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 // 1/x for x of order one: 20-bit seed + two Newton steps (relative error ~1e-16; the Newton
 // correction it scales tolerates far more).  5 FP64-pipe instructions instead of ~10.
@@ -52,7 +60,9 @@ inline void st_volatile2(double *p, double a, double b) {
     __atomic_store_n((unsigned long long *)p, x, __ATOMIC_RELEASE);
 }
 inline void cp_async16(double *dst, const double *src) { ld_volatile2(src, dst[0], dst[1]); }
-inline void cp_async_wait_all() {}
+inline void cp_async8(double *dst, const double *src) { *dst = *src; }
+inline void cp_async_commit() {}
+template <int N> inline void cp_async_wait_pending() {}
 inline double rcp_fast(double x) { return 1.0 / x; }
 inline void spin_pause() { std::this_thread::yield(); }
 inline unsigned long long global_timer_ns() { return 0; }
@@ -72,7 +82,8 @@ __device__ __forceinline__ double sentinel_value() { return __longlong_as_double
 //     piece 2K+1 = (Fp, Gp)          previous-time-level flux parts (continuation passes only)
 // Rows travel in blocks of kEdgeBlock: the producer collects them in shared memory and the
 // warp flushes a block with coalesced 16-byte volatile stores; the consumer warp copies a block
-// into its shared-memory ring one block ahead (cp.async), checks it when the block opens and
+// into its shared-memory ring one block ahead (cp.async, in the caller's per-step commit
+// groups: the caller waits for the group before open()), checks it when the block opens and
 // spins on whatever had not arrived.  No flags, no fences: a piece is valid once neither of its
 // doubles is the sentinel (the buffer starts armed and the consumer re-arms what it has taken,
 // ready for the next launch).
@@ -92,9 +103,10 @@ struct EdgeIn {
     int ny, lane;
     bool active, dead;
 
-    __device__ __forceinline__ void init(double *g_, double *ring_, int ny_, int lane_, bool active_) {
+    // `opener`: this warp is the one that calls open() (the others only read rows)
+    __device__ __forceinline__ void init(double *g_, double *ring_, int ny_, int lane_, bool active_, bool opener) {
         g = g_; ring = ring_; ny = ny_; lane = lane_; active = active_; dead = false;
-        if (active) prefetch(0);
+        if (active && opener) prefetch(0);
     }
     // start copying the block whose first row is row0 into the ring
     __device__ __forceinline__ void prefetch(int row0) {
@@ -111,7 +123,6 @@ struct EdgeIn {
     __device__ __forceinline__ int open(int s) {
         if (!active || s >= ny || (s % kEdgeBlock) != 0) return 0;
         int err = 0;
-        cp_async_wait_all();
         double p0[kIters], p1[kIters];
         bool mine[kIters];
 #pragma unroll
