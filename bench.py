@@ -288,7 +288,7 @@ def main():
                 "config": {"workload": f"FOM parameter sweep, {n}x{n} grid, dt={DT}, {T} steps, "
                                        f"{B} mu per GPU (lattice over mu1 {MU1_RANGE} x mu2 {MU2_RANGE}), "
                                        "Newton rel tol 1e-12",
-                           "grid": n, "num_steps": T, "mu_per_gpu": B, "chunk_steps": args.chunk_steps or 25,
+                           "grid": n, "num_steps": T, "mu_per_gpu": B, "chunk_steps": args.chunk_steps or 50,
                            "strict": not args.non_strict,
                            "l2": f"working set {B * per_mu / 2**30:.1f} GiB of snapshots per GPU, far larger than L2; "
                                  "no flush needed", "newton_its_mean": float(its.mean()),

@@ -39,6 +39,7 @@ namespace bfd {
 constexpr int kKMax = BFD_FOM_KMAX;
 constexpr int kNormSlots = kKMax + 1;
 
+constexpr unsigned kGateStop = 1u << 16;   // BFD_FOM_MAX_CHUNK attempts fit below
 enum StepStatus { kStepNone = 0, kStepOk = 1, kStepOkCap = 2, kStepEarly = 3, kStepNotConverged = 4 };
 
 struct FomCtl {            // one per mu sample, 64 bytes
@@ -46,10 +47,10 @@ struct FomCtl {            // one per mu sample, 64 bytes
     int kbase;             // solves already applied to step t by earlier launches (continuation)
     int k_first;           // solves for the first step of the next launch
     int k_spec;            // solves speculated for the steps after it
-    int chunk;             // time steps the next launch attempts for this sample
-    unsigned arrive;       // strips of this sample that finished the current launch
+    unsigned gate;         // kGateStop | highest attempt any strip of the sample has started
+    unsigned arrive;       // strips of this sample that finished the current segment
     int redone;            // steps redone or continued so far (statistics)
-    int pad0;
+    unsigned epoch;        // bumped by every commit: strips waiting to restart watch it
     double init_norm;      // ||r(x_0)|| of step t, kept for continuation passes
     double pad1[3];
 };
@@ -80,7 +81,7 @@ struct FomLayout {         // byte offsets inside the workspace
 
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-static int desc_chunk(const bfd_fom_desc *d) { return d->chunk_steps > 0 ? d->chunk_steps : 25; }
+static int desc_chunk(const bfd_fom_desc *d) { return d->chunk_steps > 0 ? d->chunk_steps : 50; }
 static int desc_hint(const bfd_fom_desc *d) {
     int h = d->newton_hint > 0 ? d->newton_hint : 4;
     if (h > d->max_its) h = d->max_its;
@@ -110,7 +111,7 @@ static FomLayout fom_layout(const bfd_fom_desc *d) {
     L.off_steprec = o;  o = align_up(o + sizeof(StepRec) * B * S, 256);
     L.off_arrive = o;   o = align_up(o + sizeof(unsigned) * B * S, 256);
     L.off_partial = o;  o = align_up(o + sizeof(double) * B * S * ns * kNormSlots, 256);
-    L.off_trace = o;    o = align_up(o + sizeof(unsigned long long) * B * S * ns * 2, 256);
+    L.off_trace = o;    o = align_up(o + sizeof(unsigned long long) * B * S * ns * 3, 256);
     L.edge_stride_strip = S * (size_t)d->ny * kRecDoubles;
     L.edge_stride_mu = L.edge_stride_strip * (ns > 1 ? ns - 1 : 0);
     L.off_edge = o;     o = align_up(o + sizeof(double) * L.edge_stride_mu * B, 256);
@@ -133,7 +134,7 @@ struct FomArgs {
     StepRec *steprec;   // [batch][chunk]
     unsigned *arrive;   // [batch][chunk]
     double *partial;    // [batch][chunk][nstrips][kNormSlots]
-    unsigned long long *trace;   // [batch][chunk][nstrips][2] globaltimer at the start / end of a strip's time step
+    unsigned long long *trace;   // [batch][chunk][nstrips][3] globaltimer at the start / end of a strip's time step, hand-off misses << 32 | spins
     double *edge;       // [batch][nstrips-1][chunk][ny][kRecDoubles]
     double *pool;       // [batch][num_steps+1][state]   snapshot t of sample m in slot t
     size_t edge_stride_strip, edge_stride_mu, pool_stride_mu;
@@ -167,15 +168,26 @@ static FomArgs fom_args(const bfd_fom_desc *d, const FomLayout &L, void *ws) {
 
 namespace bfd {
 
+#ifndef BFD_MINB
+#define BFD_MINB 4
+#endif
 #ifndef BFD_WARPS
 #define BFD_WARPS 4
 #endif
 constexpr int kWarpsPerStrip = BFD_WARPS;     // warps sharing the Newton levels of one strip
-constexpr int kHandValues = 6;                 // x (2), Au, Av, and cy, cyd of the row on non-uniform grids
-constexpr int kHandDoubles = 2 * kHandValues * 32;   // one level hand-off between two warps: [2 buffers][values][32 lanes]
-constexpr int kPfDepth = 6;                    // rows of level-0 input in flight (cp.async ring in shared memory)
+
+// Shared memory of one CTA (byte sizes).  Everything a lane exchanges is a 16-byte pair, laid
+// out [pair][lane] so that 128-bit accesses of a quarter warp are conflict-free.
+constexpr int kPairRow = 32 * 16;              // one pair for each lane
+constexpr int kHandBytes = 2 * 3 * kPairRow;   // level hand-off between two warps: [2 buffers][(xu,xv),(Au,Av),(cy,cyd)][lane]
+constexpr int kHandIfaces = kWarpsPerStrip > 1 ? kWarpsPerStrip - 1 : 1;
+constexpr int kXchgLevels = kKMax + 2;         // levels 0..K, plus (Fp, Gp) of continuation passes
+constexpr int kXchgBytes = kXchgLevels * 2 * 2 * kPairRow;   // left-neighbour exchange: [level][2 buffers][(Fh,Gh),(pu,pm)][lane]
+constexpr int kPfDepth = 6;                    // rows of level-0 input in flight (cp.async ring)
 constexpr int kPfValues = 7;                   // u, v, up, vp (CONT), lbc (inlet lane), cy, cyd (non-uniform grids)
-constexpr int kPfDoubles = kPfDepth * kPfValues * 32;
+constexpr int kPfBytes = kPfDepth * kPfValues * 32 * 8;
+
+template <bool B> struct BoolTag { static constexpr bool value = B; };
 
 // What one warp needs to run its levels of one time step of its strip.
 struct StepIo {
@@ -184,9 +196,10 @@ struct StepIo {
     double *xout;         // slot t+1 (all three already offset to this strip and lane)
     double *edge_in;      // hand-off records of the strip on the left for this time step
     double *edge_out;     // ... and the ones this strip produces
-    double *ring_in, *ring_out;   // shared memory of this CTA
-    double *hand;         // shared memory: level hand-off between the warps of the CTA
-    double *pf;           // shared memory: prefetch ring of the level-0 input [kPfDepth][kPfValues][32]
+    saddr ring_in, ring_out;   // shared memory of this CTA (shared-window addresses)
+    saddr hand;           // level hand-off written by this warp (the previous warp's is kHandBytes below)
+    saddr pf;             // prefetch ring of the level-0 input [kPfDepth][kPfValues][32]
+    saddr xchg;           // left-neighbour exchange
     double *partial;      // [kNormSlots] squared residual norms of this (sample, step, strip)
     const double *lbc;    // [ny] inlet term of this sample
     const double *cy, *cyd;
@@ -194,11 +207,12 @@ struct StepIo {
     double cx, cxl, src;  // column constants of this lane
     bool colok, inlet;
     int *error;
+    unsigned long long *stats;   // hand-off wait statistics of this (sample, step, strip)
 };
 
-struct Level {            // what a cell hands to its right (L) and lower (D) neighbours at one level
-    double Fh, Gh, Hh;    // current-iterate flux parts u^2/2, uv/2, v^2/2
-    double pu, pm, pvv;   // u*du, v*du + u*dv, v*dv
+struct Level {            // what a cell keeps for its lower neighbour (D) at one level
+    double Gh, Hh;        // current-iterate flux parts uv/2, v^2/2
+    double pm, pvv;       // v*du + u*dv, v*dv
 };
 
 // Levels LO..HI-1 of one trapezoidal time step of one strip.  A time step is K fused Newton
@@ -212,205 +226,179 @@ struct Level {            // what a cell hands to its right (L) and lower (D) ne
 //   ru = [u + cx Fh + cy Gh - cxl Fh_L - cyd Gh_D] + Au,  Au = -up + cx Fp + cy Gp - cxl Fp_L - cyd Gp_D - src - lbc
 //   rv = [v + cy Hh + cx Gh - cyd Hh_D - cxl Gh_L] + Av,  Av = -vp + cy Hp + cx Gp - cyd Hp_D - cxl Gp_L
 // Au, Av do not change between Newton levels and ride along the level pipeline.
+//
+// Neighbours: the upper cell (r-1, c) is the lane's own previous step (registers).  The left
+// cell (r, c-1) is lane-1's previous step: every lane publishes (Fh, Gh) and (u du, v du + u dv)
+// of each level in a double-buffered shared-memory exchange and reads its left neighbour's one
+// step later; lane 0 reads the same pairs from the hand-off record of the strip on its left
+// instead (only the ADDRESS differs), and lane 31 also files them in the record for the strip
+// on its right.
 template <int K, int LO, int HI, bool CONT, bool UNI>
 __device__ __forceinline__ void sweep_part(const StepIo &io) {
     constexpr int NPR = 2 * K + 1 + (CONT ? 1 : 0);
     constexpr bool FIRST = (LO == 0), LAST = (HI == K + 1);
-    constexpr int NL = HI - LO;              // levels of this warp
     constexpr int W = 32;
     const int lane = io.lane, ny = io.ny;
     const int last_row = ny + kSkew - 1;   // last slot-row holding cells
     const int nsteps = ny + kSkew + K;
 
-    EdgeIn<NPR> ein;
-    EdgeOut<NPR> eout;
-    ein.init(io.edge_in, io.ring_in, ny, lane, io.strip > 0, FIRST);
-    eout.init(io.edge_out, io.ring_out, ny, lane, io.strip < io.nstrips - 1);
     const bool from_edge = (lane == 0) && io.strip > 0;
     const bool to_edge = (lane == 31) && io.strip < io.nstrips - 1;
+    const bool colok = io.colok;
 
     const double cx = io.cx, cxl = io.cxl, hcx = 0.5 * io.cx, hcxl = 0.5 * io.cxl, ncxl = -io.cxl;
     const double src = io.src;
     double cyU = 0.0, cydU = 0.0;
     if (UNI) { cyU = __ldg(io.cy + (ny > 1 ? 1 : 0)); cydU = __ldg(io.cyd + (ny > 1 ? 1 : 0)); }
 
-    // Level-0 input, prefetched kPfDepth-1 rows ahead into shared memory with cp.async (first
-    // warp only; each lane copies and later reads its own 8-byte elements).  One commit group
-    // per wavefront step, so "all but the newest kPfDepth-2 groups" is exactly "row s has
-    // landed" -- unlike register prefetching, where every LDG shares one counting scoreboard
-    // and the first use of the oldest load also waits for the newest.
-    auto pf_slot = [&](int row) { return io.pf + (size_t)(row % kPfDepth) * (kPfValues * 32) + lane; };
-    auto pf_issue = [&](int row) {
-        const int r = row < last_row ? row : last_row;
-        const size_t o = (size_t)r * (2 * W);
-        double *d = pf_slot(row);
-        cp_async8(d, io.xin + o);
-        cp_async8(d + 32, io.xin + o + W);
-        if (CONT) { cp_async8(d + 64, io.xwp + o); cp_async8(d + 96, io.xwp + o + W); }
-        const int rc = r - lane < 0 ? 0 : (r - lane >= ny ? ny - 1 : r - lane);   // grid row of this lane's cell
-        if (io.inlet) cp_async8(d + 128, io.lbc + rc);
-        if (!UNI) { cp_async8(d + 160, io.cy + rc); cp_async8(d + 192, io.cyd + rc); }
-    };
-    if (FIRST) {
-#pragma unroll
-        for (int i = 0; i < kPfDepth - 1; ++i) { pf_issue(i); cp_async_commit(); }
-    }
+    // level-0 input: rows land in the shared-memory ring one step ahead (dma_part)
+    const saddr pf_lane = io.pf + (saddr)(lane * 8);
+    auto pf_slot = [&](int row) { return pf_lane + (saddr)((row % kPfDepth) * (kPfValues * 256)); };
+    auto in_slot = [&](int row, int piece) { return io.ring_in + (saddr)((row % kInRing) * kRecBytes + piece * 16); };
+    auto out_slot = [&](int row, int piece) { return io.ring_out + (saddr)((row % kOutRing) * kRecBytes + piece * 16); };
 
     Level prev[K + 1];        // own cell of the previous step at each level = upper neighbour now
-    double qFp = 0.0, qGp = 0.0, qHp = 0.0;   // previous-snapshot flux parts of the previous row (CONT)
+    double qGp = 0.0, qHp = 0.0;   // previous-snapshot flux parts of the previous row (CONT)
 #pragma unroll
-    for (int k = 0; k <= K; ++k) prev[k] = Level{0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    for (int k = 0; k <= K; ++k) prev[k] = Level{0.0, 0.0, 0.0, 0.0};
     double xu[K + 2], xv[K + 2], Au[K + 2], Av[K + 2], Cy[K + 2], Cyd[K + 2], nrm[K + 1];
 #pragma unroll
     for (int k = 0; k <= K + 1; ++k) { xu[k] = xv[k] = Au[k] = Av[k] = 0.0; Cy[k] = cyU; Cyd[k] = cydU; }
 #pragma unroll
     for (int k = 0; k <= K; ++k) nrm[k] = 0.0;
-    double *hand_in = io.hand - kHandDoubles;    // written by the previous warp of the CTA
-    double *hand_out = io.hand;
+    const saddr hand_in = io.hand - (saddr)kHandBytes + (saddr)(lane * 16);   // written by the previous warp
+    const saddr hand_out = io.hand + (saddr)(lane * 16);
+    const saddr xc_own = io.xchg + (saddr)(lane * 16);                         // this lane's pairs
+    const saddr xc_left = io.xchg + (saddr)((lane > 0 ? lane - 1 : 0) * 16);  // the left lane's
+    auto xc_level = [](int k, int buf) { return (saddr)((k * 2 + buf) * 2 * kPairRow); };
 
-    for (int s = 0; s < nsteps; ++s) {
-        {
-            double up = 0.0, vp = 0.0, lb = 0.0;
-            if (FIRST) {
-                cp_async_wait_pending<kPfDepth - 2>();      // row s (and any hand-off block due) has landed
-                const int err = ein.open(s);
-                if (err && lane == 0) atomicExch(io.error, err);
-                const double *d = pf_slot(s);
-                xu[0] = d[0]; xv[0] = d[32];
-                up = CONT ? d[64] : xu[0]; vp = CONT ? d[96] : xv[0];
-                if (io.inlet) lb = d[128];
-                if (!UNI) { Cy[0] = d[160]; Cyd[0] = d[192]; }
-#ifndef BFD_X_NOLOAD
-                pf_issue(s + kPfDepth - 1);                 // refills the slot read one step ago
-#endif
-                cp_async_commit();
-            } else {
-                // x_LO and the level-independent terms of row s - lane - LO, produced by the
-                // previous warp one step ago
-                const double *h = hand_in + ((s + 1) & 1) * (kHandValues * 32) + lane;
-                xu[LO] = h[0]; xv[LO] = h[32]; Au[LO] = h[64]; Av[LO] = h[96];
-                if (!UNI) { Cy[LO] = h[128]; Cyd[LO] = h[160]; }
-            }
-
-            // left neighbours (r, c-1): lane-1's cells of the previous step, own levels
-            double LF[K + 1], LG[K + 1], Lpu[K + 1], Lpm[K + 1], LFp = 0.0, LGp = 0.0;
-#pragma unroll
-            for (int k = LO; k < HI; ++k) {
-                LF[k] = shfl_up1(prev[k].Fh); LG[k] = shfl_up1(prev[k].Gh);
-                if (k < K) { Lpu[k] = shfl_up1(prev[k].pu); Lpm[k] = shfl_up1(prev[k].pm); }
-            }
-            if (CONT && FIRST) { LFp = shfl_up1(qFp); LGp = shfl_up1(qGp); }
-            if (lane == 0) {
-#pragma unroll
-                for (int k = LO; k < HI; ++k) {
-                    const int rk = s - k;
-                    const bool take = from_edge && (unsigned)rk < (unsigned)ny;
-                    const double *rec = ein.row(take ? rk : 0);
-                    LF[k] = take ? rec[4 * k] : 0.0;
-                    LG[k] = take ? rec[4 * k + 1] : 0.0;
-                    if (k < K) {
-                        Lpu[k] = take ? rec[4 * k + 2] : 0.0;
-                        Lpm[k] = take ? rec[4 * k + 3] : 0.0;
-                    }
-                    if (CONT && k == 0) {
-                        LFp = take ? rec[4 * K + 2] : 0.0;
-                        LGp = take ? rec[4 * K + 3] : 0.0;
-                    }
-                }
-            }
-
-            // levels in descending order: level k+1 consumes xu[k+1], Au[k+1] before level k
-            // replaces them with the values for the next step
-#pragma unroll
-            for (int k = HI - 1; k >= LO; --k) {
-                const int rk = s - lane - k;
-                const bool rowok = (unsigned)rk < (unsigned)ny;
-                const bool valid = rowok && io.colok;
-                const bool top = (rk <= 0);      // no upper neighbour (row -1 is not a cell)
-                const double cy = UNI ? cyU : Cy[k], cyd = UNI ? cydU : Cyd[k];
-                const double hcy = 0.5 * cy, hcyd = 0.5 * cyd, ncyd = -cyd;
-                double *orec = eout.row(rowok ? rk : 0);
-                const bool put = to_edge && rowok;
-
-                if (k == 0) {
-                    // previous-snapshot parts and the level-independent terms Au, Av
-                    const double hup = 0.5 * up, hvp = 0.5 * vp;
-                    const double Fp = hup * up, Gp = hup * vp, Hp = hvp * vp;
-                    const double DGp = top ? 0.0 : (CONT ? qGp : prev[0].Gh);
-                    const double DHp = top ? 0.0 : (CONT ? qHp : prev[0].Hh);
-                    const double lFp = CONT ? LFp : LF[0], lGp = CONT ? LGp : LG[0];
-                    double au = fma(cx, Fp, -up);
-                    au = fma(cy, Gp, au); au = fma(ncxl, lFp, au); au = fma(ncyd, DGp, au);
-                    au = (au - src) - lb;
-                    double av = fma(cy, Hp, -vp);
-                    av = fma(cx, Gp, av); av = fma(ncyd, DHp, av); av = fma(ncxl, lGp, av);
-                    Au[0] = au; Av[0] = av;
-                    if (CONT) {
-                        qFp = Fp; qGp = Gp; qHp = Hp;
-                        if (put) { orec[4 * K + 2] = Fp; orec[4 * K + 3] = Gp; }
-                    }
-                }
-
-                const double u = xu[k], v = xv[k];
-                const double hu = 0.5 * u, hv = 0.5 * v;
-                const double Fh = hu * u, Gh = hu * v, Hh = hv * v;
-                const double DG = top ? 0.0 : prev[k].Gh, DH = top ? 0.0 : prev[k].Hh;
-                double ru = Au[k] + u;
-                ru = fma(cx, Fh, ru); ru = fma(cy, Gh, ru); ru = fma(ncxl, LF[k], ru); ru = fma(ncyd, DG, ru);
-                double rv = Av[k] + v;
-                rv = fma(cy, Hh, rv); rv = fma(cx, Gh, rv); rv = fma(ncyd, DH, rv); rv = fma(ncxl, LG[k], rv);
-                const double r2 = fma(rv, rv, ru * ru);
-                nrm[k] += valid ? r2 : 0.0;
-
-                if (k < K) {
-                    const double Dpm = top ? 0.0 : prev[k].pm, Dpvv = top ? 0.0 : prev[k].pvv;
-                    const double bu_ = fma(hcyd, Dpm, fma(cxl, Lpu[k], ru));
-                    const double bv_ = fma(cyd, Dpvv, fma(hcxl, Lpm[k], rv));
-                    const double d00 = fma(cx, u, fma(hcy, v, 1.0));
-                    const double d11 = fma(cy, v, fma(hcx, u, 1.0));
-                    const double d01 = hcy * u, d10 = hcx * v;
-                    const double inv = rcp_fast(fma(d00, d11, -(d01 * d10)));
-                    const double du = fma(d11, bu_, -(d01 * bv_)) * inv;
-                    const double dv = fma(d00, bv_, -(d10 * bu_)) * inv;
-                    Level c;
-                    c.Fh = Fh; c.Gh = Gh; c.Hh = Hh;
-                    c.pu = u * du; c.pm = fma(v, du, u * dv); c.pvv = v * dv;
-                    prev[k] = c;
-                    xu[k + 1] = u - du; xv[k + 1] = v - dv;
-                    Au[k + 1] = Au[k]; Av[k + 1] = Av[k];
-                    if (!UNI) { Cy[k + 1] = Cy[k]; Cyd[k + 1] = Cyd[k]; }
-                    if (put) { orec[4 * k] = Fh; orec[4 * k + 1] = Gh; orec[4 * k + 2] = c.pu; orec[4 * k + 3] = c.pm; }
-                    if (k == K - 1) {
-                        // x_K of row rk: slot-row (rk + lane) of the output state
-                        const int so = s - (K - 1);
-#ifdef BFD_X_NOSTORE
-                        if (so == 0) {
-#else
-                        if (so >= 0 && so <= last_row) {
-#endif
-                            double *o = io.xout + (size_t)so * (2 * W);
-                            o[0] = valid ? xu[K] : 0.0;
-                            o[W] = valid ? xv[K] : 0.0;
-                        }
-                    }
-                } else {
-                    prev[K].Fh = Fh; prev[K].Gh = Gh; prev[K].Hh = Hh;
-                    if (put) { orec[4 * K] = Fh; orec[4 * K + 1] = Gh; }
-                }
-            }
-            if (!LAST) {
-                double *h = hand_out + (s & 1) * (kHandValues * 32) + lane;
-                h[0] = xu[HI]; h[32] = xv[HI]; h[64] = Au[HI]; h[96] = Av[HI];
-                if (!UNI) { h[128] = Cy[HI]; h[160] = Cyd[HI]; }
-            }
-#ifndef BFD_X_NOEDGEOUT
-            if (LAST) eout.close(s - kSkew - K);
-#endif
-#ifndef BFD_X_NOBAR
-            if (kWarpsPerStrip > 1) __syncthreads();
-#endif
+    // One wavefront step.  EP ("edge phase"): some lane's row is outside the grid at some level
+    // (first 32+K and last 31+K steps); the main phase runs without row masks.
+    auto body = [&](const int s, auto ep) {
+        constexpr bool EP = decltype(ep)::value;
+        const int rbuf = (s + 1) & 1, wbuf = s & 1;      // exchange buffers: written last step / this step
+        double up = 0.0, vp = 0.0, lb = 0.0;
+        if (FIRST) {
+            const saddr d = pf_slot(s);
+            xu[0] = lds(d); xv[0] = lds(d + 256);
+            up = CONT ? lds(d + 512) : xu[0]; vp = CONT ? lds(d + 768) : xv[0];
+            if (io.inlet) lb = lds(d + 1024);
+            if (!UNI) { Cy[0] = lds(d + 1280); Cyd[0] = lds(d + 1536); }
+        } else {
+            // x_LO and the level-independent terms of row s - lane - LO, from the previous warp
+            const saddr h = hand_in + (saddr)(rbuf * 3 * kPairRow);
+            lds2(h, xu[LO], xv[LO]);
+            lds2(h + kPairRow, Au[LO], Av[LO]);
+            if (!UNI) lds2(h + 2 * kPairRow, Cy[LO], Cyd[LO]);
         }
-    }
+
+        // levels in descending order: level k+1 consumes xu[k+1], Au[k+1] before level k
+        // replaces them with the values for the next step
+#pragma unroll
+        for (int k = HI - 1; k >= LO; --k) {
+            const int rk = s - lane - k;
+            const bool rowok = EP ? (unsigned)rk < (unsigned)ny : true;
+            const bool valid = rowok && colok;
+            const bool top = EP ? (rk <= 0) : false;   // no upper neighbour (row -1 is not a cell)
+            const double cy = UNI ? cyU : Cy[k], cyd = UNI ? cydU : Cyd[k];
+            const double hcy = 0.5 * cy, hcyd = 0.5 * cyd, ncyd = -cyd;
+            const bool put = to_edge && rowok;
+            const int rrow = rowok ? rk : 0;           // row for record addresses (lanes 0 and 31)
+
+            // left neighbour (r, c-1): lane-1's pairs of the previous step, or the record
+            const bool take = from_edge && rowok;
+            const saddr la = take ? in_slot(rrow, 2 * k) : xc_left + xc_level(k, rbuf);
+            double LF, LG, Lpu = 0.0, Lpm = 0.0;
+            lds2(la, LF, LG);
+            if (k < K) lds2(la + (take ? 16 : kPairRow), Lpu, Lpm);
+
+            if (k == 0) {
+                // previous-snapshot parts and the level-independent terms Au, Av
+                const double hup = 0.5 * up, hvp = 0.5 * vp;
+                const double Fp = hup * up, Gp = hup * vp, Hp = hvp * vp;
+                double DGp = CONT ? qGp : prev[0].Gh, DHp = CONT ? qHp : prev[0].Hh;
+                if (EP) { DGp = top ? 0.0 : DGp; DHp = top ? 0.0 : DHp; }
+                double lFp = LF, lGp = LG;
+                if (CONT) {
+                    const saddr lp = take ? in_slot(rrow, 2 * K + 1) : xc_left + xc_level(K + 1, rbuf);
+                    lds2(lp, lFp, lGp);
+                }
+                double au = fma(cx, Fp, -up);
+                au = fma(cy, Gp, au); au = fma(ncxl, lFp, au); au = fma(ncyd, DGp, au);
+                au = (au - src) - lb;
+                double av = fma(cy, Hp, -vp);
+                av = fma(cx, Gp, av); av = fma(ncyd, DHp, av); av = fma(ncxl, lGp, av);
+                Au[0] = au; Av[0] = av;
+                if (CONT) {
+                    qGp = Gp; qHp = Hp;
+                    sts2(xc_own + xc_level(K + 1, wbuf), Fp, Gp);
+                    if (put) sts2(out_slot(rrow, 2 * K + 1), Fp, Gp);
+                }
+            }
+
+            const double u = xu[k], v = xv[k];
+            const double hu = 0.5 * u, hv = 0.5 * v;
+            const double Fh = hu * u, Gh = hu * v, Hh = hv * v;
+            double DG = prev[k].Gh, DH = prev[k].Hh;
+            if (EP) { DG = top ? 0.0 : DG; DH = top ? 0.0 : DH; }
+            double ru = Au[k] + u;
+            ru = fma(cx, Fh, ru); ru = fma(cy, Gh, ru); ru = fma(ncxl, LF, ru); ru = fma(ncyd, DG, ru);
+            double rv = Av[k] + v;
+            rv = fma(cy, Hh, rv); rv = fma(cx, Gh, rv); rv = fma(ncyd, DH, rv); rv = fma(ncxl, LG, rv);
+            const double r2 = fma(rv, rv, ru * ru);
+            nrm[k] += valid ? r2 : 0.0;
+            sts2(xc_own + xc_level(k, wbuf), Fh, Gh);
+            if (put) sts2(out_slot(rrow, 2 * k), Fh, Gh);
+            prev[k].Gh = Gh; prev[k].Hh = Hh;
+
+            if (k < K) {
+                double Dpm = prev[k].pm, Dpvv = prev[k].pvv;
+                if (EP) { Dpm = top ? 0.0 : Dpm; Dpvv = top ? 0.0 : Dpvv; }
+                const double bu_ = fma(hcyd, Dpm, fma(cxl, Lpu, ru));
+                const double bv_ = fma(cyd, Dpvv, fma(hcxl, Lpm, rv));
+                const double d00 = fma(cx, u, fma(hcy, v, 1.0));
+                const double d11 = fma(cy, v, fma(hcx, u, 1.0));
+                const double d01 = hcy * u, d10 = hcx * v;
+                const double inv = rcp_fast(fma(d00, d11, -(d01 * d10)));
+                const double du = fma(d11, bu_, -(d01 * bv_)) * inv;
+                const double dv = fma(d00, bv_, -(d10 * bu_)) * inv;
+                const double pu = u * du, pm = fma(v, du, u * dv);
+                prev[k].pm = pm; prev[k].pvv = v * dv;
+                sts2(xc_own + xc_level(k, wbuf) + kPairRow, pu, pm);
+                if (put) sts2(out_slot(rrow, 2 * k + 1), pu, pm);
+                xu[k + 1] = u - du; xv[k + 1] = v - dv;
+                Au[k + 1] = Au[k]; Av[k + 1] = Av[k];
+                if (!UNI) { Cy[k + 1] = Cy[k]; Cyd[k + 1] = Cyd[k]; }
+                if (k == K - 1) {
+                    // x_K of row rk: slot-row (rk + lane) of the output state
+                    const int so = s - (K - 1);
+#ifdef BFD_X_NOSTORE
+                    if (so == 0) {
+#else
+                    if (!EP || (so >= 0 && so <= last_row)) {
+#endif
+                        double *o = io.xout + (size_t)so * (2 * W);
+                        o[0] = valid ? xu[K] : 0.0;
+                        o[W] = valid ? xv[K] : 0.0;
+                    }
+                }
+            }
+        }
+        if (!LAST) {
+            const saddr h = hand_out + (saddr)(wbuf * 3 * kPairRow);
+            sts2(h, xu[HI], xv[HI]);
+            sts2(h + kPairRow, Au[HI], Av[HI]);
+            if (!UNI) sts2(h + 2 * kPairRow, Cy[HI], Cyd[HI]);
+        }
+        __syncthreads();
+    };
+
+    __syncthreads();      // row 0 and the first hand-off block are in shared memory (dma_part)
+    int s = 0;
+    const int head_end = nsteps < kSkew + K + 1 ? nsteps : kSkew + K + 1;
+    for (; s < head_end; ++s) body(s, BoolTag<true>{});
+    for (; s < ny; ++s) body(s, BoolTag<false>{});     // 0 < row < ny for every lane and level
+    for (; s < nsteps; ++s) body(s, BoolTag<true>{});
 
     // ||r(x_k)||^2 of this strip, fixed reduction order (deterministic iteration counts)
 #pragma unroll
@@ -420,14 +408,65 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
         for (int off = 16; off > 0; off >>= 1) x += __shfl_xor_sync(0xffffffffu, x, off);
         if (lane == 0) io.partial[k] = x;
     }
-    (void)NL;
 }
 
 // A warp with no level in this pass only keeps the CTA's barrier count.
 template <int K>
 __device__ __forceinline__ void idle_part(const StepIo &io) {
     const int nsteps = io.ny + kSkew + K;
+    __syncthreads();
     for (int s = 0; s < nsteps; ++s) __syncthreads();
+    (void)io;
+}
+
+// The data-movement warp of the CTA: keeps the level-0 input ring kPfDepth-1 rows ahead with
+// cp.async, brings the hand-off blocks of the strip on the left into the shared-memory ring
+// one step before the compute warps need them (spinning there, off their critical path, if the
+// producer is late), and flushes finished blocks of this strip's records to global memory.
+// It meets the compute warps at the same per-step barrier.
+template <int K, bool CONT, bool UNI>
+__device__ __forceinline__ void dma_part(const StepIo &io) {
+    constexpr int NPR = 2 * K + 1 + (CONT ? 1 : 0);
+    constexpr int W = 32;
+    const int lane = io.lane, ny = io.ny;
+    const int last_row = ny + kSkew - 1;
+    const int nsteps = ny + kSkew + K;
+    EdgeIn<NPR> ein;
+    EdgeOut<NPR> eout;
+    ein.init(io.edge_in, io.ring_in, ny, lane, io.strip > 0);
+    eout.init(io.edge_out, io.ring_out, ny, lane, io.strip < io.nstrips - 1);
+    const saddr pf_lane = io.pf + (saddr)(lane * 8);
+    auto pf_issue = [&](int row) {
+        const int r = row < last_row ? row : last_row;
+        const size_t o = (size_t)r * (2 * W);
+        const saddr d = pf_lane + (saddr)((row % kPfDepth) * (kPfValues * 256));
+        cp_async8(d, io.xin + o);
+        cp_async8(d + 256, io.xin + o + W);
+        if (CONT) { cp_async8(d + 512, io.xwp + o); cp_async8(d + 768, io.xwp + o + W); }
+        const int rc = r - lane < 0 ? 0 : (r - lane >= ny ? ny - 1 : r - lane);   // grid row of this lane's cell
+        if (io.inlet) cp_async8(d + 1024, io.lbc + rc);
+        if (!UNI) { cp_async8(d + 1280, io.cy + rc); cp_async8(d + 1536, io.cyd + rc); }
+    };
+    // One commit group per step: "all but the newest kPfDepth-2 groups" = "the row of the next
+    // step, and the hand-off block prefetched 8 steps ago, have landed".
+#pragma unroll
+    for (int i = 0; i < kPfDepth - 1; ++i) { pf_issue(i); cp_async_commit(); }
+    cp_async_wait_pending<kPfDepth - 2>();
+    int err = ein.open(0);
+    __syncthreads();
+    for (int s = 0; s < nsteps; ++s) {
+        pf_issue(s + kPfDepth - 1);          // refills the slot read one step ago
+        cp_async_commit();
+        cp_async_wait_pending<kPfDepth - 2>();   // row s+1 has landed
+        err |= ein.open(s + 1);              // block starting at row s+1, if that opens one
+        eout.close(s - 1 - kSkew - K);       // row whose last level finished in the previous step
+        __syncthreads();
+    }
+    eout.close(nsteps - 1 - kSkew - K);
+    if (lane == 0) {
+        if (err) atomicExch(io.error, err);
+        if (io.stats) *io.stats = ((unsigned long long)ein.misses << 32) | ein.spins_total;
+    }
 }
 
 // First level of warp w when the K+1 levels of a pass (K solves + the residual of x_K) are
@@ -459,6 +498,7 @@ __device__ __forceinline__ void sweep_step(const StepIo &io, int warp) {
         if (warp == 2) sweep_warp<K, 2, CONT, UNI>(io);
         if (warp == 3) sweep_warp<K, 3, CONT, UNI>(io);
     }
+    if (warp == kWarpsPerStrip) dma_part<K, CONT, UNI>(io);
 }
 
 }  // namespace bfd
@@ -467,7 +507,8 @@ namespace bfd {
 
 // newton_raphson's stopping rule (hypernet2D.py:1907-1930) applied to the residual norms one
 // pass produced: rn[k] = ||r(x_{kb+k})||, k = 0..K.  Run by the last strip to finish the step.
-__device__ void validate_step(const FomArgs &a, int m, int i, int kb, int K, double init_prev) {
+// Returns true when the speculated solve count was wrong and the sample must stop and restart.
+__device__ bool validate_step(const FomArgs &a, int m, int i, int kb, int K, double init_prev) {
     const int ns = a.ssl.nstrips;
     const volatile double *part = a.partial + (size_t)(m * a.chunk + i) * ns * kNormSlots;
     double rn[kNormSlots];
@@ -492,21 +533,23 @@ __device__ void validate_step(const FomArgs &a, int m, int i, int kb, int K, dou
         }
     }
     a.steprec[(size_t)m * a.chunk + i] = rec;
+    return rec.status == kStepNotConverged || (rec.status == kStepEarly && a.strict && rec.kconv > 0);
 }
 
 __device__ __forceinline__ int clampk(int k) { return k < 1 ? 1 : (k > kKMax ? kKMax : k); }
 
-// Turn the verdicts of a launch into the sample's next state.  Run by the last strip of the
-// sample to finish the launch.
-__device__ void commit_chunk(const FomArgs &a, int m, int t0, int n, int kbase, int k_first, int k_spec) {
+// Turn the verdicts of a segment (attempts i0 .. i0+n-1 of this launch, time steps t0 ..) into
+// the sample's next state.  Run by the last strip of the sample to finish the segment.
+__device__ void commit_segment(const FomArgs &a, int m, int t0, int i0, int n, int kbase, int k_first, int k_spec) {
     FomCtl *ctl = a.ctl + m;
+    if (n <= 0) return;
     int t = t0, knext = k_spec, redo = 0;
     int new_kbase = 0, new_kfirst = k_first;
     bool stop = false;
-    for (int i = 0; i < n && !stop; ++i) {
-        const StepRec rec = a.steprec[(size_t)m * a.chunk + i];
-        const int kb = i ? 0 : kbase;
-        int K = i ? k_spec : k_first;
+    for (int ii = 0; ii < n && !stop; ++ii) {
+        const StepRec rec = a.steprec[(size_t)m * a.chunk + i0 + ii];
+        const int kb = ii ? 0 : kbase;
+        int K = ii ? k_spec : k_first;
         if (K > a.max_its - kb) K = a.max_its - kb;
         int *its = a.its + (size_t)m * a.num_steps + t;
         double *rel = a.relnorm + (size_t)m * a.num_steps + t;
@@ -525,52 +568,39 @@ __device__ void commit_chunk(const FomArgs &a, int m, int t0, int n, int kbase, 
             break;
         }
     }
-    if (!stop) {
-        ctl->kbase = 0; ctl->k_first = clampk(knext); ctl->k_spec = clampk(knext); ctl->chunk = a.chunk;
-    } else {
-        ctl->kbase = new_kbase; ctl->k_first = new_kfirst; ctl->chunk = 1;
-    }
+    if (!stop) { ctl->kbase = 0; ctl->k_first = clampk(knext); ctl->k_spec = clampk(knext); }
+    else { ctl->kbase = new_kbase; ctl->k_first = new_kfirst; }
     ctl->t = t;
     if (redo) { ctl->redone += redo; atomicAdd(&a.glob->redone, redo); }
     if (t >= a.num_steps) atomicAdd(&a.glob->done, 1);
 }
 
-// Up to `chunk` time steps of every unfinished sample.  One CTA of kWarpsPerStrip warps <->
-// (sample m, strip j); virtual ids come from a ticket so that a strip's left neighbour (a
-// smaller id) is always already running when the strip waits on it.
+// Up to `chunk` time-step attempts of every unfinished sample.  One CTA <-> (sample m, strip j);
+// virtual ids come from a ticket so that a strip's left neighbour (a smaller id) is always
+// already running when the strip waits on it.
+//
+// Speculation control.  A sample runs its steps back to back with the speculated solve count.
+// The strip that completes a step's norms validates it; on a wrong count it raises the stop
+// bit of the sample's gate.  Every strip passes the gate before each attempt (atomicMax with
+// the attempt index): attempts some strip had already started are still run by all strips
+// (every hand-off record produced is consumed), later ones are refused.  The refused strips
+// wait for the commit by the last of them (all strips of the sample are resident by then: they
+// all took part in the failed step), which rewinds the sample to the failed step with the
+// right count, and carry on inside the same launch.
 template <bool UNI>
-__global__ void __launch_bounds__(32 * kWarpsPerStrip, kWarpsPerStrip == 4 ? 4 : 6) fom_chunk_kernel(const FomArgs a) {
-    BFD_SHARED_ARRAY(double, s_in, [kInRing * kRecDoubles]);
-    BFD_SHARED_ARRAY(double, s_out, [kOutRing * kRecDoubles]);
-    BFD_SHARED_ARRAY(double, s_hand, [kWarpsPerStrip * kHandDoubles]);
-    BFD_SHARED_ARRAY(double, s_pf, [kPfDoubles]);
+__global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk_kernel(const FomArgs a) {
+    constexpr int kSmemDoubles = (kInRing + kOutRing) * kRecDoubles + (kHandIfaces * kHandBytes + kXchgBytes + kPfBytes) / 8;
+    BFD_SHARED_ARRAY(double, s_mem, [kSmemDoubles]);
     BFD_SHARED_ARRAY(int, s_ctl, [8]);
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = lane_id(), warp = threadIdx.x >> 5;
     const int nstrips = a.ssl.nstrips;
-    for (int i = threadIdx.x; i < kWarpsPerStrip * kHandDoubles; i += blockDim.x) s_hand[i] = 0.0;
-    if (threadIdx.x == 0) {
-        const int item = (int)atomicInc(&a.glob->ticket, gridDim.x - 1);
-        s_ctl[0] = item;
-        s_ctl[1] = a.num_steps;      // t: "finished" unless the item is real
-        if (item < a.batch * nstrips) {
-            const FomCtl *c = a.ctl + item / nstrips;
-            s_ctl[1] = c->t; s_ctl[2] = c->kbase; s_ctl[3] = c->k_first; s_ctl[4] = c->k_spec; s_ctl[5] = c->chunk;
-        }
-    }
+    for (int i = threadIdx.x; i < kSmemDoubles; i += blockDim.x) s_mem[i] = 0.0;
+    if (threadIdx.x == 0) s_ctl[0] = (int)atomicInc(&a.glob->ticket, gridDim.x - 1);
     __syncthreads();
-    // control words are broadcast by shuffle: the compiler then knows they are warp-uniform
-    // and keeps the shuffles of the sweep free of convergence bookkeeping
-    int w = (lane < 8) ? s_ctl[lane] : 0;
-    const int item = __shfl_sync(0xffffffffu, w, 0);
-    const int t0 = __shfl_sync(0xffffffffu, w, 1);
-    if (t0 >= a.num_steps) return;   // nothing to do, or this sample has finished its trajectory
-    const int kbase = __shfl_sync(0xffffffffu, w, 2), k_first = __shfl_sync(0xffffffffu, w, 3),
-              k_spec = __shfl_sync(0xffffffffu, w, 4);
-    int n = __shfl_sync(0xffffffffu, w, 5);
-    if (n > a.num_steps - t0) n = a.num_steps - t0;
+    const int item = __shfl_sync(0xffffffffu, s_ctl[0], 0);
+    if (item >= a.batch * nstrips) return;
     const int m = item / nstrips, j = item - m * nstrips;
     FomCtl *ctl = a.ctl + m;
-    const double init_prev = ctl->init_norm;
 
     const int nx = a.ssl.nx, ny = a.ssl.ny;
     const size_t sd = a.ssl.state_doubles;
@@ -579,9 +609,12 @@ __global__ void __launch_bounds__(32 * kWarpsPerStrip, kWarpsPerStrip == 4 ? 4 :
     double *edge_m = a.edge + (size_t)m * a.edge_stride_mu;
 
     StepIo io;
-    io.ring_in = s_in; io.ring_out = s_out;
-    io.hand = s_hand + warp * kHandDoubles;
-    io.pf = s_pf;
+    io.ring_in = smem_addr(s_mem);
+    io.ring_out = io.ring_in + (saddr)(kInRing * kRecBytes);
+    const saddr hand0 = io.ring_out + (saddr)(kOutRing * kRecBytes);
+    io.hand = hand0 + (saddr)(warp * kHandBytes);
+    io.xchg = hand0 + (saddr)(kHandIfaces * kHandBytes);
+    io.pf = io.xchg + (saddr)kXchgBytes;
     io.lbc = a.lbc + (size_t)m * ny;
     io.cy = a.cy; io.cyd = a.cyd;
     io.ny = ny; io.strip = j; io.nstrips = nstrips; io.lane = lane;
@@ -592,48 +625,93 @@ __global__ void __launch_bounds__(32 * kWarpsPerStrip, kWarpsPerStrip == 4 ? 4 :
     io.inlet = (j == 0 && lane == 0);
     io.error = &a.glob->error;
 
-    for (int i = 0; i < n; ++i) {
-        const int t = t0 + i;
-        const int kb = i ? 0 : kbase;
-        int K = i ? k_spec : k_first;
-        if (K > a.max_its - kb) K = a.max_its - kb;
-        io.xwp = pool_m + (size_t)t * sd;
-        io.xout = pool_m + (size_t)(t + 1) * sd;
-        io.xin = kb ? io.xout : io.xwp;
-        const size_t eoff = (size_t)i * ny * kRecDoubles;
-        io.edge_in = edge_m + (size_t)(j > 0 ? j - 1 : 0) * a.edge_stride_strip + eoff;
-        io.edge_out = edge_m + (size_t)(j < nstrips - 1 ? j : 0) * a.edge_stride_strip + eoff;
-        io.partial = a.partial + ((size_t)(m * a.chunk + i) * nstrips + j) * kNormSlots;
-        unsigned long long *tr = a.trace + ((size_t)(m * a.chunk + i) * nstrips + j) * 2;
-        if (threadIdx.x == 0) tr[0] = global_timer_ns();
-        if (kb) {
-            sweep_step<1, true, UNI>(io, warp);
-        } else {
-            switch (K) {
-            case 1: sweep_step<1, false, UNI>(io, warp); break;
-            case 2: sweep_step<2, false, UNI>(io, warp); break;
-            case 3: sweep_step<3, false, UNI>(io, warp); break;
-            case 4: sweep_step<4, false, UNI>(io, warp); break;
-            case 5: sweep_step<5, false, UNI>(io, warp); break;
-            default: sweep_step<6, false, UNI>(io, warp); break;
-            }
-        }
-        __syncthreads();       // both warps have published their norms
+    int attempt = 0;                 // attempts of this launch so far (same on every strip of the sample)
+    for (;;) {                       // segments: runs of steps between two commits
+        __syncthreads();
+        unsigned epoch0 = 0;
         if (threadIdx.x == 0) {
-            tr[1] = global_timer_ns();
-            __threadfence();
-            if (atomicInc(&a.arrive[(size_t)m * a.chunk + i], (unsigned)nstrips - 1) == (unsigned)nstrips - 1) {
+            // control words are read by one thread and broadcast by shuffle: the compiler then
+            // knows they are warp-uniform
+            s_ctl[1] = ctl->t; s_ctl[2] = ctl->kbase; s_ctl[3] = ctl->k_first; s_ctl[4] = ctl->k_spec;
+            epoch0 = *(volatile unsigned *)&ctl->epoch;
+        }
+        __syncthreads();
+        const int w = (lane < 8) ? s_ctl[lane] : 0;
+        const int t0 = __shfl_sync(0xffffffffu, w, 1);
+        if (t0 >= a.num_steps || attempt >= a.chunk) break;   // trajectory finished / budget of this launch used
+        const int kbase = __shfl_sync(0xffffffffu, w, 2), k_first = __shfl_sync(0xffffffffu, w, 3),
+                  k_spec = __shfl_sync(0xffffffffu, w, 4);
+        const double init_prev = ctl->init_norm;
+        const int i0 = attempt;
+        bool refused = false;
+        for (; attempt < a.chunk; ++attempt) {
+            const int ii = attempt - i0, t = t0 + ii;
+            if (t >= a.num_steps) break;
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                const unsigned old = atomicMax(&ctl->gate, (unsigned)attempt);
+                s_ctl[5] = ((old & kGateStop) && (unsigned)attempt > (old & (kGateStop - 1))) ? 0 : 1;
+            }
+            __syncthreads();
+            const int gw = (lane < 8) ? s_ctl[lane] : 0;
+            if (__shfl_sync(0xffffffffu, gw, 5) == 0) { refused = true; break; }
+
+            const int i = attempt;
+            const int kb = ii ? 0 : kbase;
+            int K = ii ? k_spec : k_first;
+            if (K > a.max_its - kb) K = a.max_its - kb;
+            io.xwp = pool_m + (size_t)t * sd;
+            io.xout = pool_m + (size_t)(t + 1) * sd;
+            io.xin = kb ? io.xout : io.xwp;
+            const size_t eoff = (size_t)i * ny * kRecDoubles;
+            io.edge_in = edge_m + (size_t)(j > 0 ? j - 1 : 0) * a.edge_stride_strip + eoff;
+            io.edge_out = edge_m + (size_t)(j < nstrips - 1 ? j : 0) * a.edge_stride_strip + eoff;
+            io.partial = a.partial + ((size_t)(m * a.chunk + i) * nstrips + j) * kNormSlots;
+            unsigned long long *tr = a.trace + ((size_t)(m * a.chunk + i) * nstrips + j) * 3;
+            if (threadIdx.x == 0) tr[0] = global_timer_ns();
+            io.stats = tr + 2;
+            if (kb) {
+                sweep_step<1, true, UNI>(io, warp);
+            } else {
+                switch (K) {
+                case 1: sweep_step<1, false, UNI>(io, warp); break;
+                case 2: sweep_step<2, false, UNI>(io, warp); break;
+                case 3: sweep_step<3, false, UNI>(io, warp); break;
+                case 4: sweep_step<4, false, UNI>(io, warp); break;
+                case 5: sweep_step<5, false, UNI>(io, warp); break;
+                default: sweep_step<6, false, UNI>(io, warp); break;
+                }
+            }
+            __syncthreads();       // every warp has published its norms
+            if (threadIdx.x == 0) {
+                tr[1] = global_timer_ns();
                 __threadfence();
-                validate_step(a, m, i, kb, kb ? 1 : K, init_prev);
+                if (atomicInc(&a.arrive[(size_t)m * a.chunk + i], (unsigned)nstrips - 1) == (unsigned)nstrips - 1) {
+                    __threadfence();
+                    if (validate_step(a, m, i, kb, kb ? 1 : K, init_prev)) atomicOr(&ctl->gate, kGateStop);
+                }
             }
         }
-    }
-    if (threadIdx.x == 0) {
-        __threadfence();
-        if (atomicInc(&ctl->arrive, (unsigned)nstrips - 1) == (unsigned)nstrips - 1) {
+        // end of the segment: the last strip commits; refused strips wait for it and restart
+        if (threadIdx.x == 0) {
             __threadfence();
-            commit_chunk(a, m, t0, n, kbase, k_first, k_spec);
+            if (atomicInc(&ctl->arrive, (unsigned)nstrips - 1) == (unsigned)nstrips - 1) {
+                __threadfence();
+                commit_segment(a, m, t0, i0, attempt - i0, kbase, k_first, k_spec);
+                // next segment of this launch continues at `attempt`; a new launch starts at 0
+                *(volatile unsigned *)&ctl->gate = refused ? (unsigned)(attempt > 0 ? attempt - 1 : 0) : 0u;
+                __threadfence();
+                atomicAdd(&ctl->epoch, 1u);
+            } else if (refused) {
+                unsigned spins = 0;
+                while (*(volatile unsigned *)&ctl->epoch == epoch0) {
+                    spin_pause();
+                    if (++spins > kSpinLimit) { atomicExch(&a.glob->error, BFD_ETIMEOUT); break; }
+                }
+                __threadfence();
+            }
         }
+        if (!refused) break;
     }
 }
 
@@ -683,8 +761,7 @@ __global__ void fom_reset_kernel(const FomArgs a) {
     if (g < a.batch) {
         FomCtl c;
         c.t = 0; c.kbase = 0; c.k_first = a.hint; c.k_spec = a.hint;
-        c.chunk = 1;      // the first launch probes the solve count on one step
-        c.arrive = 0; c.redone = 0; c.pad0 = 0; c.init_norm = 0.0;
+        c.gate = 0; c.arrive = 0; c.redone = 0; c.epoch = 0; c.init_norm = 0.0;
         c.pad1[0] = c.pad1[1] = c.pad1[2] = 0.0;
         a.ctl[g] = c;
     }
@@ -770,9 +847,9 @@ extern "C" int bfd_fom_set_initial(const bfd_fom_desc *d, void *ws, const double
 static int launch_chunk(const FomArgs &a, cudaStream_t st) {
     const int grid = a.batch * a.ssl.nstrips;
     if (a.uniform_y) {
-        BFD_LAUNCH_CORESIDENT(fom_chunk_kernel<true>, grid, 32 * kWarpsPerStrip, 0, st, a);
+        BFD_LAUNCH_CORESIDENT(fom_chunk_kernel<true>, grid, 32 * (kWarpsPerStrip + 1), 0, st, a);
     } else {
-        BFD_LAUNCH_CORESIDENT(fom_chunk_kernel<false>, grid, 32 * kWarpsPerStrip, 0, st, a);
+        BFD_LAUNCH_CORESIDENT(fom_chunk_kernel<false>, grid, 32 * (kWarpsPerStrip + 1), 0, st, a);
     }
     BFD_LAUNCHED();
     return BFD_OK;
@@ -852,7 +929,7 @@ extern "C" int bfd_fom_trace(const bfd_fom_desc *d, const void *ws, uint64_t *ou
     if (check_desc(d) != BFD_OK || !ws || !out) return BFD_EINVAL;
     const FomLayout L = fom_layout(d);
     const FomArgs a = fom_args(d, L, const_cast<void *>(ws));
-    const size_t n = (size_t)d->batch * L.chunk * L.ssl.nstrips * 2;
+    const size_t n = (size_t)d->batch * L.chunk * L.ssl.nstrips * 3;
     BFD_CUDA(cudaMemcpyAsync(out, a.trace, n * sizeof(uint64_t), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
     return BFD_OK;
 }

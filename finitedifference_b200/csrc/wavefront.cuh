@@ -8,22 +8,40 @@ namespace bfd {
 __device__ __forceinline__ double shfl_up1(double x) { return __shfl_up_sync(0xffffffffu, x, 1); }
 
 #ifndef BFD_EMULATE
-// 16-byte hand-off accesses (one transaction each, L2-coherent).
+// 16-byte hand-off accesses (one transaction each), relaxed at GPU scope: coherent in L2,
+// without the system-scope ordering of ld/st.volatile (which serialises back-to-back stores).
 __device__ __forceinline__ void ld_volatile2(const double *p, double &a, double &b) {
-    asm volatile("ld.volatile.global.v2.f64 {%0, %1}, [%2];" : "=d"(a), "=d"(b) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.gpu.global.v2.f64 {%0, %1}, [%2];" : "=d"(a), "=d"(b) : "l"(p) : "memory");
 }
 __device__ __forceinline__ void st_volatile2(double *p, double a, double b) {
-    asm volatile("st.volatile.global.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(a), "d"(b) : "memory");
+    asm volatile("st.relaxed.gpu.global.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(a), "d"(b) : "memory");
 }
+// plain 16-byte store: re-arming a record only has to be visible to the next launch
+__device__ __forceinline__ void st_weak2(double *p, double a, double b) {
+    asm volatile("st.global.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(a), "d"(b) : "memory");
+}
+// Shared memory is addressed by 32-bit shared-window byte addresses computed once per kernel,
+// so the hot loop never re-derives a generic pointer (S2R + LEA per access otherwise).
+typedef unsigned saddr;
+__device__ __forceinline__ saddr smem_addr(const void *p) { return (saddr)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ double lds(saddr a) {
+    double v; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a) : "memory"); return v;
+}
+__device__ __forceinline__ void lds2(saddr a, double &x, double &y) {
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(x), "=d"(y) : "r"(a) : "memory");
+}
+__device__ __forceinline__ void sts(saddr a, double v) { asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory"); }
+__device__ __forceinline__ void sts2(saddr a, double x, double y) {
+    asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(a), "d"(x), "d"(y) : "memory");
+}
+__device__ __forceinline__ int lane_id() { int l; asm volatile("mov.u32 %0, %%laneid;" : "=r"(l)); return l; }
 // 16 bytes global -> shared without a register round trip (LDGSTS, L2 only)
-__device__ __forceinline__ void cp_async16(double *smem_dst, const double *gsrc) {
-    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gsrc) : "memory");
+__device__ __forceinline__ void cp_async16(saddr dst, const double *gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(gsrc) : "memory");
 }
 // 8 bytes global -> shared (each lane copies its own element)
-__device__ __forceinline__ void cp_async8(double *smem_dst, const double *gsrc) {
-    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gsrc) : "memory");
+__device__ __forceinline__ void cp_async8(saddr dst, const double *gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(gsrc) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 // wait until at most N of this thread's committed groups are still in flight
@@ -59,8 +77,16 @@ inline void st_volatile2(double *p, double a, double b) {
     __atomic_store_n((unsigned long long *)p + 1, y, __ATOMIC_RELEASE);
     __atomic_store_n((unsigned long long *)p, x, __ATOMIC_RELEASE);
 }
-inline void cp_async16(double *dst, const double *src) { ld_volatile2(src, dst[0], dst[1]); }
-inline void cp_async8(double *dst, const double *src) { *dst = *src; }
+typedef uintptr_t saddr;
+inline saddr smem_addr(const void *p) { return (saddr)p; }
+inline double lds(saddr a) { return *(const double *)a; }
+inline void lds2(saddr a, double &x, double &y) { x = ((const double *)a)[0]; y = ((const double *)a)[1]; }
+inline void sts(saddr a, double v) { *(double *)a = v; }
+inline void sts2(saddr a, double x, double y) { ((double *)a)[0] = x; ((double *)a)[1] = y; }
+inline int lane_id() { return emu::tls.lane; }
+inline void cp_async16(saddr dst, const double *src) { ld_volatile2(src, ((double *)dst)[0], ((double *)dst)[1]); }
+inline void cp_async8(saddr dst, const double *src) { *(double *)dst = *src; }
+inline void st_weak2(double *p, double a, double b) { st_volatile2(p, a, b); }
 inline void cp_async_commit() {}
 template <int N> inline void cp_async_wait_pending() {}
 inline double rcp_fast(double x) { return 1.0 / x; }
@@ -95,105 +121,140 @@ constexpr int kInRing = 32;                        // rows in the consumer's rin
 constexpr int kOutRing = 16;                       // rows in the producer's ring (2 blocks)
 constexpr unsigned kSpinLimit = 1u << 22;
 
+constexpr int kRecBytes = kRecDoubles * 8;
+
+// Per-lane piece assignment inside a block of kEdgeBlock rows, computed once: lane handles
+// pieces q = lane + 32*it of the block's kEdgeBlock*NPR pieces (row-major [row][piece]).
+template <int NPR>
+struct BlockMap {
+    static constexpr int kIters = (kEdgeBlock * NPR + 31) / 32;
+    int row[kIters];        // row inside the block; >= kEdgeBlock marks "no piece"
+    int goff[kIters];       // offset in doubles from the block's first record
+    int soff[kIters];       // offset in bytes from the block's first ring row
+    __device__ __forceinline__ void init(int lane) {
+#pragma unroll
+        for (int it = 0; it < kIters; ++it) {
+            const int q = lane + 32 * it, r = q / NPR, piece = q - r * NPR;
+            row[it] = q < kEdgeBlock * NPR ? r : 2 * kEdgeBlock;
+            goff[it] = r * kRecDoubles + 2 * piece;
+            soff[it] = r * kRecBytes + 16 * piece;
+        }
+    }
+};
+
 template <int NPR>
 struct EdgeIn {
-    static constexpr int kIters = (kEdgeBlock * NPR + 31) / 32;
+    static constexpr int kIters = BlockMap<NPR>::kIters;
+    BlockMap<NPR> map;
     double *g;       // records written by the strip on the left, [ny][kRecDoubles]
-    double *ring;    // [kInRing][kRecDoubles] shared memory of this warp
+    saddr ring;      // [kInRing][kRecDoubles] shared memory of this CTA
     int ny, lane;
     bool active, dead;
+    unsigned spins_total, misses;   // statistics for bfd_fom_trace
 
-    // `opener`: this warp is the one that calls open() (the others only read rows)
-    __device__ __forceinline__ void init(double *g_, double *ring_, int ny_, int lane_, bool active_, bool opener) {
+    __device__ __forceinline__ void init(double *g_, saddr ring_, int ny_, int lane_, bool active_) {
         g = g_; ring = ring_; ny = ny_; lane = lane_; active = active_; dead = false;
-        if (active && opener) prefetch(0);
+        spins_total = 0; misses = 0;
+        map.init(lane);
+        if (active) prefetch(0);
     }
-    // start copying the block whose first row is row0 into the ring
+    // start copying the block whose first row is row0 (a multiple of kEdgeBlock) into the ring
     __device__ __forceinline__ void prefetch(int row0) {
+        const double *gb = g + (size_t)row0 * kRecDoubles;
+        const saddr sb = ring + (saddr)((row0 % kInRing) * kRecBytes);
 #pragma unroll
-        for (int it = 0; it < kIters; ++it) {
-            const int q = lane + 32 * it, row = row0 + q / NPR, piece = q % NPR;
-            if (q < kEdgeBlock * NPR && row < ny)
-                cp_async16(ring + (row % kInRing) * kRecDoubles + 2 * piece, g + (size_t)row * kRecDoubles + 2 * piece);
-        }
+        for (int it = 0; it < kIters; ++it)
+            if (row0 + map.row[it] < ny && map.row[it] < kEdgeBlock) cp_async16(sb + (saddr)map.soff[it], gb + map.goff[it]);
     }
-    // Whole warp, every step; works when step `s` opens a block.  Returns BFD_ETIMEOUT once if
-    // the producer never showed up (the block then reads as zeros).  Every branch is
-    // warp-uniform (votes), so the caller's shuffles stay convergent.
+    // Whole warp, every step; works when `s` opens a block.  Returns BFD_ETIMEOUT once if the
+    // producer never showed up (the block then reads as zeros).  Every branch is warp-uniform.
     __device__ __forceinline__ int open(int s) {
+#ifdef BFD_X_NOOPEN
+        return 0;
+#endif
         if (!active || s >= ny || (s % kEdgeBlock) != 0) return 0;
         int err = 0;
+        double *gb = g + (size_t)s * kRecDoubles;
+        const saddr sb = ring + (saddr)((s % kInRing) * kRecBytes);
         double p0[kIters], p1[kIters];
         bool mine[kIters];
+        bool ok = true;
 #pragma unroll
         for (int it = 0; it < kIters; ++it) {
-            const int q = lane + 32 * it, row = s + q / NPR, piece = q % NPR;
-            mine[it] = q < kEdgeBlock * NPR && row < ny;
-            const double *slot = ring + ((mine[it] ? row : s) % kInRing) * kRecDoubles + 2 * (mine[it] ? piece : 0);
-            p0[it] = slot[0]; p1[it] = slot[1];
+            mine[it] = s + map.row[it] < ny && map.row[it] < kEdgeBlock;
+            p0[it] = 0.0; p1[it] = 0.0;
+            if (mine[it]) lds2(sb + (saddr)map.soff[it], p0[it], p1[it]);
+            ok = ok && !(is_sentinel(p0[it]) || is_sentinel(p1[it]));
         }
-        if (!dead) {
+        if (!__all_sync(0xffffffffu, ok || dead)) {
+            // some piece had not arrived when the block was prefetched: poll global memory
+            ++misses;
             unsigned spins = 0;
             for (;;) {
-                bool ok = true;
-#pragma unroll
-                for (int it = 0; it < kIters; ++it)
-                    ok = ok && (!mine[it] || !(is_sentinel(p0[it]) || is_sentinel(p1[it])));
-                if (__all_sync(0xffffffffu, ok)) break;
-                if (++spins > kSpinLimit) { dead = true; err = BFD_ETIMEOUT; break; }
-                if (spins > 2) spin_pause();
+                ok = true;
 #pragma unroll
                 for (int it = 0; it < kIters; ++it) {
-                    const int q = lane + 32 * it, row = s + q / NPR, piece = q % NPR;
-                    if (mine[it] && (is_sentinel(p0[it]) || is_sentinel(p1[it])))
-                        ld_volatile2(g + (size_t)row * kRecDoubles + 2 * piece, p0[it], p1[it]);
+                    if (mine[it] && (is_sentinel(p0[it]) || is_sentinel(p1[it]))) {
+                        ld_volatile2(gb + map.goff[it], p0[it], p1[it]);
+                        ok = ok && !(is_sentinel(p0[it]) || is_sentinel(p1[it]));
+                    }
                 }
+                if (__all_sync(0xffffffffu, ok)) break;
+                ++spins_total;
+                if (++spins > kSpinLimit) { dead = true; err = BFD_ETIMEOUT; break; }
+                if (spins > 2) spin_pause();
             }
-        }
 #pragma unroll
-        for (int it = 0; it < kIters; ++it) {
-            const int q = lane + 32 * it, row = s + q / NPR, piece = q % NPR;
-            if (mine[it]) {
-                double *slot = ring + (row % kInRing) * kRecDoubles + 2 * piece;
-                slot[0] = dead ? 0.0 : p0[it];
-                slot[1] = dead ? 0.0 : p1[it];
-                if (!dead) st_volatile2(g + (size_t)row * kRecDoubles + 2 * piece, sentinel_value(), sentinel_value());   // re-arm
-            }
+            for (int it = 0; it < kIters; ++it)
+                if (mine[it]) sts2(sb + (saddr)map.soff[it], dead ? 0.0 : p0[it], dead ? 0.0 : p1[it]);
+        } else if (dead) {
+#pragma unroll
+            for (int it = 0; it < kIters; ++it)
+                if (mine[it]) sts2(sb + (saddr)map.soff[it], 0.0, 0.0);
         }
+#ifndef BFD_X_NOREARM
+        if (!dead) {
+#pragma unroll
+            for (int it = 0; it < kIters; ++it)
+                if (mine[it]) st_weak2(gb + map.goff[it], sentinel_value(), sentinel_value());   // re-arm
+        }
+#endif
         __syncwarp();
+#ifndef BFD_X_NOEDGEPF
         if (!dead && s + kEdgeBlock < ny) prefetch(s + kEdgeBlock);
+#endif
         return err;
     }
-    __device__ __forceinline__ const double *row(int r) const { return ring + (r % kInRing) * kRecDoubles; }
 };
 
 template <int NPR>
 struct EdgeOut {
-    static constexpr int kIters = (kEdgeBlock * NPR + 31) / 32;
+    static constexpr int kIters = BlockMap<NPR>::kIters;
+    BlockMap<NPR> map;
     double *g;      // records of this strip, [ny][kRecDoubles]
-    double *ring;   // [kOutRing][kRecDoubles]
+    saddr ring;     // [kOutRing][kRecDoubles]
     int ny, lane;
     bool active;
 
-    __device__ __forceinline__ void init(double *g_, double *ring_, int ny_, int lane_, bool active_) {
+    __device__ __forceinline__ void init(double *g_, saddr ring_, int ny_, int lane_, bool active_) {
         g = g_; ring = ring_; ny = ny_; lane = lane_; active = active_;
+        map.init(lane);
     }
-    __device__ __forceinline__ double *row(int r) const { return ring + (r % kOutRing) * kRecDoubles; }
-    // Whole warp, every step, with the row whose LAST level lane 31 has just finished.
+    // Whole warp, every step, with the row whose LAST level has been filed in the ring.
     __device__ __forceinline__ void close(int r_done) {
         if (!active || r_done < 0 || r_done >= ny) return;
         if ((r_done % kEdgeBlock) != kEdgeBlock - 1 && r_done != ny - 1) return;
         const int row0 = r_done - (r_done % kEdgeBlock);
-        __syncwarp();
+        double *gb = g + (size_t)row0 * kRecDoubles;
+        const saddr sb = ring + (saddr)((row0 % kOutRing) * kRecBytes);
 #pragma unroll
         for (int it = 0; it < kIters; ++it) {
-            const int q = lane + 32 * it, row = row0 + q / NPR, piece = q % NPR;
-            if (q < kEdgeBlock * NPR && row < ny) {
-                const double *slot = ring + (row % kOutRing) * kRecDoubles + 2 * piece;
-                st_volatile2(g + (size_t)row * kRecDoubles + 2 * piece, slot[0], slot[1]);
+            if (row0 + map.row[it] < ny && map.row[it] < kEdgeBlock) {
+                double x, y;
+                lds2(sb + (saddr)map.soff[it], x, y);
+                st_volatile2(gb + map.goff[it], x, y);
             }
         }
-        __syncwarp();
     }
 };
 

@@ -57,7 +57,7 @@ typedef struct bfd_fom_desc {
     int32_t batch;           /* number of mu samples advanced together */
     int32_t num_steps;       /* T; T+1 snapshots are kept per mu */
     int32_t max_its;         /* Newton cap; the reference passes 100 (:123) */
-    int32_t chunk_steps;     /* time steps per launch, 1..BFD_FOM_MAX_CHUNK; 0 = default (25) */
+    int32_t chunk_steps;     /* time steps per launch, 1..BFD_FOM_MAX_CHUNK; 0 = default (50) */
     int32_t newton_hint;     /* first guess of the Newton solves per step, 1..BFD_FOM_KMAX; 0 = 4 */
     int32_t strict;          /* 1: iteration counts and iterates exactly as newton_raphson decides
                                 them (a step whose speculated solve count was too high is redone);
@@ -103,7 +103,8 @@ int bfd_fom_diagnostics(const bfd_fom_desc *d, const void *workspace, int32_t *i
 
 /* Pipeline trace of the most recent launches: for every (sample, time step of the launch,
  * strip) the %globaltimer (ns) at which the strip started and finished that time step.
- * out: uint64 [batch][chunk_steps][nstrips][2], device pointer; nstrips = ceil(nx/32).  Entries
+ * out: uint64 [batch][chunk_steps][nstrips][3], device pointer (third word: hand-off blocks that
+ * had not arrived when first looked at << 32 | spin iterations); nstrips = ceil(nx/32).  Entries
  * of steps a launch did not run keep older values.  Profiling aid (see profiles/). */
 int bfd_fom_trace(const bfd_fom_desc *d, const void *workspace, uint64_t *out, void *stream);
 

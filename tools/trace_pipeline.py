@@ -35,7 +35,7 @@ def main():
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); s.run(); e1.record(); e1.synchronize()
     ns = (n + 31) // 32
-    tr = torch.zeros((args.batch, args.chunk, ns, 2), dtype=torch.int64, device="cuda")
+    tr = torch.zeros((args.batch, args.chunk, ns, 3), dtype=torch.int64, device="cuda")
     rc = s.lib.bfd_fom_trace(C.byref(s.desc), s.ws.data_ptr(), tr.data_ptr(), torch.cuda.current_stream().cuda_stream)
     assert rc == 0
     tr = tr.cpu().numpy()
@@ -49,7 +49,8 @@ def main():
         st = (t[i, :, 0] - base) / 1e3
         du = (t[i, :, 1] - t[i, :, 0]) / 1e3
         print(i, "start", np.array2string(st[:: max(1, ns // 8)], precision=0),
-              "dur", f"{du[0]:.0f} {du[ns // 2]:.0f} {du[-1]:.0f}", "end last", f"{(t[i, -1, 1] - base) / 1e3:.0f}")
+              "dur", f"{du[0]:.0f} {du[ns // 2]:.0f} {du[-1]:.0f}", "end last", f"{(t[i, -1, 1] - base) / 1e3:.0f}",
+              "misses/spins mid", int(t[i, ns // 2, 2]) >> 32, int(t[i, ns // 2, 2]) & 0xffffffff)
 
 
 if __name__ == "__main__":
