@@ -7,7 +7,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-SOURCES = ["runtime.cu", "fom.cu", "ops.cu"]
+SOURCES = ["runtime.cu", "fom.cu", "ops.cu", "rom.cu"]
 OUT = os.path.join(HERE, "_burgers_b200.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--use_fast_math=false"]
@@ -23,8 +23,8 @@ def _stale(target, deps):
 def build(force: bool = False, verbose: bool = False) -> str:
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     srcs = [os.path.join(CSRC, s) for s in SOURCES]
-    deps = srcs + [os.path.join(CSRC, "common.cuh"),
-                   os.path.join(HERE, "..", "include", "burgers_b200.h")]
+    deps = srcs + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh")] + \
+        [os.path.join(HERE, "..", "include", "burgers_b200.h")]
     if not force and not _stale(OUT, deps):
         return OUT
     flags = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")]

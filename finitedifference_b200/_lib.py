@@ -40,6 +40,12 @@ class FomCoef(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("cx", "cxl", "cy", "cyd", "src", "lbc")]
 
 
+class RomMesh(C.Structure):
+    """``bfd_rom_mesh``."""
+    _fields_ = [("nrows", C.c_int64), ("ncells", C.c_int64)] + \
+               [(n, C.c_void_p) for n in ("p", "xl", "yd", "ja", "jb", "cx", "cxl", "cy", "cyd", "src", "lbc", "weight")]
+
+
 _P = C.c_void_p
 # name -> (restype, argtypes): every symbol include/burgers_b200.h declares
 SIGNATURES = {
@@ -54,6 +60,9 @@ SIGNATURES = {
                                  C.c_size_t, _P, _P]),
     "bfd_fom_trace": (C.c_int, [C.POINTER(FomDesc), _P, _P, _P]),
     "bfd_fom_diagnostics": (C.c_int, [C.POINTER(FomDesc), _P, _P, _P, _P]),
+    "bfd_rom_residual": (C.c_int, [C.POINTER(RomMesh), _P, _P, _P, _P, _P]),
+    "bfd_rom_jv": (C.c_int, [C.POINTER(RomMesh), _P, _P, C.c_int, _P, _P]),
+    "bfd_ecsw_c_block": (C.c_int, [C.c_int64, C.c_int, _P, _P, _P, C.c_size_t, _P]),
     "bfd_residual": (C.c_int, [C.c_int, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
 }
 

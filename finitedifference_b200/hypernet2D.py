@@ -21,9 +21,12 @@ import numpy as np
 
 from .discretisation import make_2D_grid  # noqa: F401  (re-exported, hypernet2D.py:2501)
 from .fom import FomSolver
+from .rom import EcswSolver, LspgSolver, ecsw_training_matrix, generate_augmented_mesh  # noqa: F401
 
 __all__ = [
     "make_2D_grid", "inviscid_burgers_implicit2D", "inviscid_burgers_implicit2D_batch",
+    "inviscid_burgers_implicit2D_LSPG", "inviscid_burgers_ecsw_fixed", "generate_augmented_mesh",
+    "compute_ECSW_training_matrix_2D",
     "load_or_compute_snaps", "param_to_snap_fn", "get_saved_params", "compute_error",
 ]
 
@@ -61,6 +64,54 @@ def inviscid_burgers_implicit2D_batch(grid_x, grid_y, w0, dt, num_steps, mus, *,
     solver.set_initial(w0)
     solver.run()
     return solver
+
+
+def inviscid_burgers_implicit2D_LSPG(grid_x, grid_y, w0, dt, num_steps, mu, basis, *, device=None,
+                                     jacobian="reference", return_info=False):
+    """LSPG PROM trajectory; reference hypernet2D.py:133-200.
+
+    Returns ``(snaps (2N, T+1), (num_its, jac_time, res_time, ls_time))`` like the reference.
+    ``jacobian="reference"`` (default) reproduces the operator the reference builds at :167;
+    ``"exact"`` uses the true Jacobian.  ``return_info=True`` appends
+    ``{"red_coords": (k, T+1), "gn_its": per-step residual evaluations}``.
+    """
+    solver = LspgSolver(grid_x, grid_y, dt, mu, np.asarray(basis, dtype=np.float64), device=device,
+                        jacobian=jacobian)
+    snaps, red, hist = solver.run(np.asarray(w0, dtype=np.float64).ravel(), int(num_steps))
+    out = (np.ascontiguousarray(snaps.T.cpu().numpy()),
+           (sum(len(h) for h in hist), solver.jac_time, solver.res_time, solver.ls_time))
+    if return_info:
+        out += ({"red_coords": np.ascontiguousarray(red.T.cpu().numpy()),
+                 "gn_its": np.array([len(h) for h in hist]), "resnorms": hist},)
+    return out
+
+
+def inviscid_burgers_ecsw_fixed(grid_x, grid_y, weights, w0, dt, num_steps, mu, basis, *, device=None,
+                                return_info=False):
+    """ECSW/ECM HPROM trajectory on the sampled mesh; reference hypernet2D.py:202-273.
+
+    Returns ``(red_coords (k, T+1), (jac_time, res_time, ls_time))`` like the reference.
+    ``return_info=True`` appends ``{"sample_inds", "augmented_sample", "gn_its"}``.
+    """
+    solver = EcswSolver(grid_x, grid_y, weights, dt, mu, np.asarray(basis, dtype=np.float64), device=device)
+    red, hist = solver.run(np.asarray(w0, dtype=np.float64).ravel(), int(num_steps))
+    out = (np.ascontiguousarray(red.T.cpu().numpy()), (solver.jac_time, solver.res_time, solver.ls_time))
+    if return_info:
+        out += ({"sample_inds": solver.sample_inds, "augmented_sample": solver.augmented_sample,
+                 "gn_its": np.array([len(h) for h in hist]), "resnorms": hist},)
+    return out
+
+
+def compute_ECSW_training_matrix_2D(snaps, prev_snaps, basis, res=None, jac=None, grid_x=None, grid_y=None,
+                                    dt=None, mu=None, *, device=None):
+    """ECSW training matrix ``C`` (k*n_snaps, N); reference hypernet2D.py:2795-2816.
+
+    Same positional signature as the reference.  ``res`` and ``jac`` (the reference passes its
+    ``inviscid_burgers_res2D`` and ``inviscid_burgers_exact_jac2D``, run_HPROM_ecsw_joshua.py:61-64)
+    are accepted and ignored: the residual and the exact Jacobian of ``get_ops`` are evaluated by
+    the device kernels.
+    """
+    return ecsw_training_matrix(snaps, prev_snaps, basis, grid_x, grid_y, dt, mu, device=device)
 
 
 # -- snapshot cache (hypernet2D.py:3157-3221) ------------------------------------------------

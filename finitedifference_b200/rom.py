@@ -1,0 +1,256 @@
+"""Reduced-order models on one B200: host side of the LSPG PROM and the ECSW/ECM HPROM paths.
+
+Mirrors ``inviscid_burgers_implicit2D_LSPG`` (reference hypernet2D.py:133-200) with
+``gauss_newton_LSPG`` (:1935-2005), ``inviscid_burgers_ecsw_fixed`` (:202-273) with
+``gauss_newton_ECSW_2D`` (:2007-2044), ``generate_augmented_mesh`` (:2522-2542) and
+``compute_ECSW_training_matrix_2D`` (:2795-2816).
+
+The host builds integer index tables (which state cells each residual row reads) once per
+trajectory; residual rows and the matrix-free ``J @ V`` rows are hand-written kernels
+(csrc/rom.cu) behind ``bfd_rom_residual`` / ``bfd_rom_jv`` / ``bfd_ecsw_c_block``.  The small
+dense algebra of a Gauss-Newton step -- ``V @ y``, the k x k normal equations
+``(JV)^T (JV) dy = -(JV)^T f`` (the reference's ``lstsq``; cond(JV) ~ 1.5) -- are
+plain library GEMM / Cholesky calls on the device (cuBLAS / cuSOLVER through torch, float64).
+The Gauss-Newton stopping tests are evaluated on the host from FP64 norms exactly as the
+reference orders them.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import time
+
+import numpy as np
+import torch
+
+from . import _lib
+from .discretisation import stencil_coefficients
+from .fom import _require_cuda
+
+
+def generate_augmented_mesh(grid_x, grid_y, sample_inds):
+    """Sampled cells plus their (r-1, c) and (r, c-1) neighbours: sorted, unique, int64.
+
+    Same set, order and dtype as the reference's ``generate_augmented_mesh``
+    (hypernet2D.py:2522-2542), which collects them in a Python ``set`` and sorts.
+    """
+    nx = np.asarray(grid_x).size - 1
+    s = np.asarray(sample_inds, dtype=np.int64).ravel()
+    r, c = np.divmod(s, nx)
+    return np.unique(np.concatenate((s, s[r >= 1] - nx, s[c >= 1] - 1))).astype(np.int64)
+
+
+class MeshTables:
+    """Index and coefficient tables of ``bfd_rom_mesh`` for a set of rows, on the device."""
+
+    def __init__(self, grid_x, grid_y, dt, mu, device, rows=None, state_cells=None, weight=None,
+                 jacobian="exact"):
+        gx = np.asarray(grid_x, dtype=np.float64)
+        gy = np.asarray(grid_y, dtype=np.float64)
+        nx, ny = gx.size - 1, gy.size - 1
+        n_cells = nx * ny
+        rows = np.arange(n_cells, dtype=np.int64) if rows is None else np.asarray(rows, dtype=np.int64)
+        r, c = np.divmod(rows, nx)
+        if state_cells is None:                       # state arrays hold the whole grid
+            lookup = None
+            ncells = n_cells
+        else:                                         # state arrays hold `state_cells` (sorted) only
+            state_cells = np.asarray(state_cells, dtype=np.int64)
+            ncells = state_cells.size
+
+        def local(cells, present):
+            """Position of grid cells in the state arrays; -1 where absent."""
+            out = np.full(cells.shape, -1, dtype=np.int64)
+            if state_cells is None:
+                out[present] = cells[present]
+            else:
+                pos = np.searchsorted(state_cells, cells[present])
+                pos = np.minimum(pos, state_cells.size - 1)
+                if not np.array_equal(state_cells[pos], cells[present]):
+                    raise ValueError("a stencil cell is missing from the augmented sample")
+                out[present] = pos
+            return out
+
+        everywhere = np.ones(rows.shape, dtype=bool)
+        p = local(rows, everywhere)
+        xl = local(rows - 1, c >= 1)
+        yd = local(rows - nx, r >= 1)
+        if jacobian == "exact":
+            ja, jb = p.copy(), yd.copy()
+        elif jacobian == "reference":
+            # hypernet2D.py:167: kron(I, Dyec)[permT, :] -- rows permuted, columns not: row (r, c)
+            # reads cells (c, r) and (c, r-1)
+            if nx != ny:
+                raise ValueError("the reference's LSPG operator (hypernet2D.py:167) needs nx == ny")
+            ja = local(c * ny + r, everywhere)
+            jb = local(c * ny + r - 1, r >= 1)
+        else:
+            raise ValueError(jacobian)
+        cx, cxl, cy, cyd = stencil_coefficients(gx, gy, dt)
+        dx = gx[1:] - gx[:-1]
+        xc = (gx[1:] + gx[:-1]) / 2
+        src = (dt * 0.02 * np.exp(mu[1] * xc))[c]
+        if state_cells is None:
+            den = dx[r] if nx == ny else np.full(rows.shape, dx[0])      # :2582 / :2630 (Q3)
+        else:
+            den = np.full(rows.shape, dx[0])                              # :2665
+        lbc = np.where(c == 0, 0.5 * dt * mu[0] ** 2 / den, 0.0)
+        self.nrows, self.ncells, self.device = int(rows.size), int(ncells), device
+        i32 = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.int32)).to(device)
+        f64 = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(device)
+        self._t = [i32(a) for a in (p, xl, yd, ja, jb)] + \
+                  [f64(a) for a in (cx[c], cxl[c], cy[r], cyd[r], src, lbc)]
+        wptr = None
+        if weight is not None:
+            self._t.append(f64(weight))
+            wptr = self._t[-1].data_ptr()
+        self.c = _lib.RomMesh(self.nrows, self.ncells, *[t.data_ptr() for t in self._t[:11]], wptr)
+
+
+class _RomBase:
+    def __init__(self, device=None):
+        self.lib = _lib.get_lib()
+        self.device = _require_cuda(device)
+        self.res_time = self.jac_time = self.ls_time = 0.0
+
+    def _stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _dev(self, a):
+        return torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(self.device)
+
+    def residual(self, mesh, w, wp):
+        """(r, ||r||) with r = [rows u | rows v] (weighted when the mesh has weights)."""
+        r = torch.empty(2 * mesh.nrows, dtype=torch.float64, device=self.device)
+        n2 = torch.zeros(1, dtype=torch.float64, device=self.device)
+        _lib.check(self.lib.bfd_rom_residual(C.byref(mesh.c), w.data_ptr(), wp.data_ptr(), r.data_ptr(),
+                                             n2.data_ptr(), self._stream()), self.lib, "bfd_rom_residual")
+        return r, float(torch.sqrt(n2).item())
+
+    def jv(self, mesh, w, V):
+        k = V.shape[1]
+        JV = torch.empty((2 * mesh.nrows, k), dtype=torch.float64, device=self.device)
+        _lib.check(self.lib.bfd_rom_jv(C.byref(mesh.c), w.data_ptr(), V.data_ptr(), k, JV.data_ptr(),
+                                       self._stream()), self.lib, "bfd_rom_jv")
+        return JV
+
+    def gauss_newton(self, res_mesh, jac_mesh, V, y0, wp, max_its=20, relnorm_cutoff=1e-5, min_delta=0.1):
+        """``gauss_newton_LSPG`` / ``gauss_newton_ECSW_2D`` (:1935-2005, :2007-2044).
+
+        Returns ``(y, w, resnorms)``; the two stopping rules are the reference's, in its order.
+        """
+        y = y0.clone()
+        w = V @ y
+        _, init_norm = self.residual(res_mesh, w, wp)
+        resnorms = []
+        for _ in range(max_its):
+            t0 = time.perf_counter()
+            f, resnorm = self.residual(res_mesh, w, wp)
+            self.res_time += time.perf_counter() - t0
+            resnorms.append(resnorm)
+            if resnorm / init_norm < relnorm_cutoff:
+                break
+            if len(resnorms) > 1 and abs((resnorms[-2] - resnorms[-1]) / resnorms[-2]) < min_delta:
+                break
+            t0 = time.perf_counter()
+            JV = self.jv(jac_mesh, w, V)
+            torch.cuda.synchronize(self.device)
+            self.jac_time += time.perf_counter() - t0
+            t0 = time.perf_counter()
+            G = JV.T @ JV                                  # normal equations of lstsq(JV, -f)
+            b = -(JV.T @ f)
+            dy = torch.cholesky_solve(b[:, None], torch.linalg.cholesky(G))[:, 0]
+            y = y + dy
+            w = V @ y
+            torch.cuda.synchronize(self.device)
+            self.ls_time += time.perf_counter() - t0
+        return y, w, resnorms
+
+
+class LspgSolver(_RomBase):
+    """LSPG PROM on span(basis): ``inviscid_burgers_implicit2D_LSPG`` (:133-200).
+
+    ``jacobian="reference"`` reproduces the operator the reference actually builds at :167
+    (parity); ``"exact"`` uses the true Jacobian.
+    """
+
+    def __init__(self, grid_x, grid_y, dt, mu, basis, device=None, jacobian="reference"):
+        super().__init__(device)
+        self.grid_x, self.grid_y, self.dt, self.mu = grid_x, grid_y, float(dt), list(mu)[:2]
+        self.V = basis if isinstance(basis, torch.Tensor) else self._dev(basis)
+        self.V = self.V.to(self.device, dtype=torch.float64).contiguous()
+        self.res_mesh = MeshTables(grid_x, grid_y, dt, self.mu, self.device)
+        self.jac_mesh = self.res_mesh if jacobian == "exact" else \
+            MeshTables(grid_x, grid_y, dt, self.mu, self.device, jacobian="reference")
+
+    def run(self, w0, num_steps):
+        """Returns ``(snaps_dev (T+1, 2N), red_coords_dev (T+1, k), per-step resnorm lists)``."""
+        V = self.V
+        w0 = w0 if isinstance(w0, torch.Tensor) else self._dev(np.asarray(w0, dtype=np.float64).ravel())
+        y = V.T @ w0                                        # :158
+        w = V @ y                                           # :159
+        snaps = torch.empty((num_steps + 1, V.shape[0]), dtype=torch.float64, device=self.device)
+        red = torch.empty((num_steps + 1, V.shape[1]), dtype=torch.float64, device=self.device)
+        snaps[0], red[0] = w, y
+        history = []
+        for i in range(num_steps):
+            y, w, resnorms = self.gauss_newton(self.res_mesh, self.jac_mesh, V, y, snaps[i])
+            history.append(resnorms)
+            snaps[i + 1], red[i + 1] = w, y                 # :196: the stored snapshot is basis @ y
+        return snaps, red, history
+
+
+class EcswSolver(_RomBase):
+    """ECSW/ECM HPROM on the sampled mesh: ``inviscid_burgers_ecsw_fixed`` (:202-273)."""
+
+    def __init__(self, grid_x, grid_y, weights, dt, mu, basis, device=None):
+        super().__init__(device)
+        weights = np.asarray(weights, dtype=np.float64).ravel()
+        self.sample_inds = np.where(weights != 0)[0].astype(np.int64)             # :225 (Q7: != 0)
+        self.augmented_sample = generate_augmented_mesh(grid_x, grid_y, self.sample_inds)
+        n_cells = weights.size
+        self.sample_weights = np.hstack((weights, weights))[self.sample_inds]     # :239-240
+        self.idx = np.concatenate((self.augmented_sample, n_cells + self.augmented_sample))   # :242
+        self.mu = list(mu)[:2]
+        self.mesh = MeshTables(grid_x, grid_y, dt, self.mu, self.device, rows=self.sample_inds,
+                               state_cells=self.augmented_sample, weight=self.sample_weights)
+        basis = np.asarray(basis, dtype=np.float64) if not isinstance(basis, torch.Tensor) else basis
+        self.V = basis if isinstance(basis, torch.Tensor) else self._dev(basis)
+        self.V = self.V.to(self.device, dtype=torch.float64).contiguous()
+        self.V_red = self.V[torch.from_numpy(self.idx).to(self.device)].contiguous()   # :245
+
+    def run(self, w0, num_steps):
+        """Returns ``(red_coords_dev (T+1, k), per-step resnorm lists)``."""
+        w0 = w0 if isinstance(w0, torch.Tensor) else self._dev(np.asarray(w0, dtype=np.float64).ravel())
+        y = self.V.T @ w0                                   # :213
+        red = torch.empty((num_steps + 1, self.V.shape[1]), dtype=torch.float64, device=self.device)
+        red[0] = y
+        wp = self.V_red @ y                                 # == (basis @ y0)[idx]  (:214, :243)
+        history = []
+        for i in range(num_steps):
+            y, w, resnorms = self.gauss_newton(self.mesh, self.mesh, self.V_red, y, wp)
+            history.append(resnorms)
+            red[i + 1] = y
+            wp = w                                          # :271
+        return red, history
+
+
+def ecsw_training_matrix(snaps, prev_snaps, basis, grid_x, grid_y, dt, mu, device=None, out_device=False):
+    """``compute_ECSW_training_matrix_2D`` (:2795-2816) with the exact Jacobian of ``get_ops``:
+    ``C[i*k:(i+1)*k, cell] = r_u[cell]*(JV)_u[cell, :] + r_v[cell]*(JV)_v[cell, :]``."""
+    base = _RomBase(device)
+    dev = base.device
+    mu = list(mu)[:2]
+    to_dev = lambda a: a.to(dev, dtype=torch.float64) if isinstance(a, torch.Tensor) else base._dev(a)
+    S, P, V = to_dev(snaps), to_dev(prev_snaps), to_dev(basis).contiguous()
+    n2, n_snaps = S.shape
+    n_cells, k = n2 // 2, V.shape[1]
+    mesh = MeshTables(grid_x, grid_y, dt, mu, dev)
+    Cmat = torch.empty((k * n_snaps, n_cells), dtype=torch.float64, device=dev)
+    for i in range(n_snaps):
+        w, wp = S[:, i].contiguous(), P[:, i].contiguous()
+        r, _ = base.residual(mesh, w, wp)
+        JV = base.jv(mesh, w, V)
+        _lib.check(base.lib.bfd_ecsw_c_block(n_cells, k, r.data_ptr(), JV.data_ptr(),
+                                             Cmat[i * k:(i + 1) * k].data_ptr(), n_cells, base._stream()),
+                   base.lib, "bfd_ecsw_c_block")
+    return Cmat if out_device else Cmat.cpu().numpy()

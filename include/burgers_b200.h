@@ -121,6 +121,47 @@ int bfd_residual(int nx, int ny, const double *cx, const double *cxl, const doub
                  const double *cyd, const double *src, const double *lbc, const double *w,
                  const double *wp, double *r, double *norm2, void *stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Reduced-order models (LSPG PROM on the whole grid, ECSW/ECM HPROM on the sampled mesh).
+ *
+ * A "mesh" is a list of rows (cells whose residual is evaluated) with, per row, the state cells
+ * its stencil reads.  State arrays hold `ncells` cells per component: u of state cell q at
+ * w[q], v at w[ncells + q] (the whole grid, or the augmented sample [aug | N+aug] of
+ * inviscid_burgers_ecsw_fixed, hypernet2D.py:242-245).  Index tables are int32, -1 = no such
+ * neighbour (contributes zero, as the first row of make_ddx does, :2491):
+ *   p          own cell
+ *   xl, yd     left (r, c-1) and lower-row (r-1, c) cells: residual (:2544-2586, :2648-2701)
+ *   ja, jb     the two cells of the JACOBIAN's y-difference: (p, yd) for the exact operator
+ *              (get_ops, :2509-2520); the transposed cells (c, r), (c, r-1) for the operator
+ *              inviscid_burgers_implicit2D_LSPG builds at :167 (rows-only permutation)
+ *   cx, cxl, cy, cyd   per-row entries of 0.5*dt*Dx / 0.5*dt*Dy (diagonal, minus sub-diagonal)
+ *   src, lbc   per-row source and inlet terms (:2625-2631, :2660-2669)
+ *   weight     per-row ECSW weight (gauss_newton_ECSW_2D, :2012) or NULL
+ * All pointers are device pointers.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct bfd_rom_mesh {
+    int64_t nrows, ncells;
+    const int32_t *p, *xl, *yd, *ja, *jb;
+    const double *cx, *cxl, *cy, *cyd, *src, *lbc, *weight;
+} bfd_rom_mesh;
+
+/* r[0:nrows] = u-residual rows, r[nrows:2*nrows] = v-residual rows, times weight when given;
+ * adds sum(r^2) to *norm2 (device, zeroed by the caller) when non-NULL.
+ * Replaces inviscid_burgers_res2D (:2544-2586) / _res2D_ecsw (:2648-2701). */
+int bfd_rom_residual(const bfd_rom_mesh *mesh, const double *w, const double *wp, double *r,
+                     double *norm2, void *stream);
+
+/* JV[2*nrows][k] (row-major) = rows of J(w) @ V, times weight when given; V is the basis
+ * restricted to the state cells, row-major [2*ncells][k].  Replaces inviscid_burgers_exact_jac2D
+ * (:2703-2732) / _exact_jac2D_ecsw (:2734-2744) followed by J.dot(basis) (:1993, :2030, :2812). */
+int bfd_rom_jv(const bfd_rom_mesh *mesh, const double *w, const double *V, int k, double *JV,
+               void *stream);
+
+/* One snapshot's block of the ECSW training matrix (compute_ECSW_training_matrix_2D, :2807-2814):
+ * C[j*ldc + cell] = r[cell]*JV[cell][j] + r[nrows+cell]*JV[nrows+cell][j], j < k, cell < nrows. */
+int bfd_ecsw_c_block(int64_t nrows, int k, const double *r, const double *JV, double *C, size_t ldc,
+                     void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,98 @@
+"""ROM kernels (csrc/rom.cu) on CPU: the product's sources compiled against the SIMT emulator,
+driven through the C ABI with the host-side index tables of finitedifference_b200/rom.py, and
+compared with the oracle and with golden vectors generated from the unmodified reference."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from finitedifference_b200 import _lib
+from finitedifference_b200.rom import MeshTables, generate_augmented_mesh
+from oracle import burgers_oracle as orc
+from tests import emu_driver as E
+
+CPU = torch.device("cpu")
+
+
+@pytest.fixture(scope="module")
+def lib():
+    return E.load()
+
+
+def run_residual(lib, mesh, w, wp):
+    r = np.zeros(2 * mesh.nrows)
+    n2 = np.zeros(1)
+    assert lib.bfd_rom_residual(C.byref(mesh.c), E.ptr(w), E.ptr(wp), E.ptr(r), E.ptr(n2), None) == 0
+    return r, n2[0]
+
+
+def run_jv(lib, mesh, w, V):
+    V = np.ascontiguousarray(V)
+    JV = np.zeros((2 * mesh.nrows, V.shape[1]))
+    assert lib.bfd_rom_jv(C.byref(mesh.c), E.ptr(w), E.ptr(V), V.shape[1], E.ptr(JV), None) == 0
+    return JV
+
+
+def test_full_mesh_residual_and_both_jacobians(lib, golden):
+    g = golden("ops_n12.npz")
+    n, dt, mu = int(g["n"]), float(g["dt"]), list(g["mu"])
+    gx, gy = orc.make_2D_grid(0, 100, 0, 100, n, n)
+    w, wp = np.ascontiguousarray(g["w"]), np.ascontiguousarray(g["wp"])
+    rng = np.random.default_rng(0)
+    V = rng.standard_normal((2 * n * n, 5))
+    exact = MeshTables(gx, gy, dt, mu, CPU)
+    quirk = MeshTables(gx, gy, dt, mu, CPU, jacobian="reference")
+    r, n2 = run_residual(lib, exact, w, wp)
+    assert np.max(np.abs(r - g["r_std"])) < 1e-14
+    assert abs(n2 - g["r_std"] @ g["r_std"]) < 1e-12 * n2
+    assert np.max(np.abs(run_jv(lib, exact, w, V) - g["J_exact"] @ V)) < 1e-13      # get_ops operator
+    assert np.max(np.abs(run_jv(lib, quirk, w, V) - g["J_lspg"] @ V)) < 1e-13       # hypernet2D.py:167
+
+
+def test_sampled_mesh_matches_reference_rows(lib, golden):
+    g = golden("ecsw_ops_n24.npz")
+    n, dt, mu = int(g["n"]), float(g["dt"]), list(g["mu"])
+    gx, gy = orc.make_2D_grid(0, 100, 0, 100, n, n)
+    weights = g["weights"]
+    sample = np.where(weights != 0)[0]
+    aug = generate_augmented_mesh(gx, gy, sample)
+    assert aug.dtype == np.int64 and np.array_equal(aug, orc.augmented_mesh(gx, gy, sample))
+    idx = np.concatenate((aug, n * n + aug))
+    w, wp = np.ascontiguousarray(g["w"][idx]), np.ascontiguousarray(g["wp"][idx])
+    mesh = MeshTables(gx, gy, dt, mu, CPU, rows=sample, state_cells=aug)
+    r, _ = run_residual(lib, mesh, w, wp)
+    assert np.max(np.abs(r - g["r_red"])) < 1e-14
+    rng = np.random.default_rng(1)
+    V = rng.standard_normal((2 * aug.size, 4))
+    assert np.max(np.abs(run_jv(lib, mesh, w, V) - g["J_red"] @ V)) < 1e-13
+    wts = np.hstack((weights, weights))[sample]
+    meshw = MeshTables(gx, gy, dt, mu, CPU, rows=sample, state_cells=aug, weight=wts)
+    rw, _ = run_residual(lib, meshw, w, wp)
+    assert np.max(np.abs(rw - g["r_red"] * np.concatenate((wts, wts)))) < 1e-12
+    JVw = run_jv(lib, meshw, w, V)
+    assert np.max(np.abs(JVw - np.concatenate((wts, wts))[:, None] * (g["J_red"] @ V))) < 1e-11
+
+
+def test_training_matrix_block(lib, golden):
+    g = golden("ecswC_n12.npz")
+    n, dt, mu = int(g["n"]), float(g["dt"]), list(g["mu"])
+    gx, gy = orc.make_2D_grid(0, 100, 0, 100, n, n)
+    snaps, V = g["snaps"], np.ascontiguousarray(g["basis"])
+    k, N = V.shape[1], n * n
+    Cref = g["C"]
+    n_snaps = Cref.shape[0] // k
+    steps = int(g["steps"])
+    cur, prev = snaps[:, 3:steps:2], snaps[:, 0:steps - 3:2]      # the pairing oracle/gen_golden.py used
+    assert cur.shape[1] == n_snaps
+    mesh = MeshTables(gx, gy, dt, mu, CPU)
+    Cm = np.zeros_like(Cref)
+    for i in range(n_snaps):
+        w, wp = np.ascontiguousarray(cur[:, i]), np.ascontiguousarray(prev[:, i])
+        r, _ = run_residual(lib, mesh, w, wp)
+        JV = run_jv(lib, mesh, w, V)
+        blk = np.zeros((k, N))
+        assert lib.bfd_ecsw_c_block(N, k, E.ptr(r), E.ptr(JV), E.ptr(blk), N, None) == 0
+        Cm[i * k:(i + 1) * k] = blk
+    assert np.allclose(Cm, Cref, rtol=1e-11, atol=1e-15)
+    assert np.allclose(Cm, orc.ecsw_training_matrix(cur, prev, V, gx, gy, dt, mu), rtol=1e-11, atol=1e-15)

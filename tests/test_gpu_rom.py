@@ -1,0 +1,97 @@
+"""Parity of the CUDA PROM / HPROM paths (drop-in API over the C ABI) with golden vectors generated
+from the unmodified reference and with the oracle.  Tolerance (BASELINE.json north_star): reduced
+states within 1e-8 relative, Gauss-Newton iteration counts equal, ECSW index sets bit-exact."""
+import numpy as np
+import pytest
+
+from oracle import burgers_oracle as orc
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-8
+
+
+@pytest.fixture(scope="module")
+def h():
+    from finitedifference_b200 import hypernet2D
+    return hypernet2D
+
+
+def rel(a, b):
+    return np.linalg.norm(a - b) / np.linalg.norm(b)
+
+
+def test_lspg_golden(h, golden):
+    g = golden("lspg_n24.npz")
+    n, steps = int(g["n"]), int(g["steps"])
+    gx, gy = h.make_2D_grid(0, 100, 0, 100, n, n)
+    w0 = np.ones(2 * n * n)
+    basis = np.ascontiguousarray(g["basis"])
+    snaps, times, info = h.inviscid_burgers_implicit2D_LSPG(gx, gy, w0, float(g["dt"]), steps, list(g["mu"]), basis,
+                                                            return_info=True)
+    assert snaps.shape == g["snaps"].shape and snaps.flags.c_contiguous and len(times) == 4
+    assert info["gn_its"].tolist() == g["gn_its"].tolist()
+    assert times[0] == int(g["num_its"])
+    assert max(rel(snaps[:, i], g["snaps"][:, i]) for i in range(steps + 1)) < TOL
+    assert np.array_equal(w0, np.ones(2 * n * n))
+
+
+@pytest.mark.parametrize("mode", ["reference", "exact"])
+def test_lspg_vs_oracle(h, mode):
+    n, steps, mu = 40, 5, [5.19, 0.026]
+    gx, gy = h.make_2D_grid(0, 100, 0, 100, n, n)
+    w0 = np.ones(2 * n * n)
+    fom = orc.fom_trajectory(gx, gy, w0, 0.05, 12, mu)
+    basis = np.ascontiguousarray(np.linalg.svd(fom, full_matrices=False)[0][:, :7])
+    snaps, times, info = h.inviscid_burgers_implicit2D_LSPG(gx, gy, w0, 0.05, steps, mu, basis, jacobian=mode,
+                                                            return_info=True)
+    ref, rtimes, red, hist = orc.lspg_trajectory(gx, gy, w0, 0.05, steps, mu, basis, jacobian_mode=mode,
+                                                 return_info=True)
+    assert info["gn_its"].tolist() == [len(x) for x in hist]
+    assert max(rel(info["red_coords"][:, i], red[:, i]) for i in range(steps + 1)) < TOL
+    assert max(rel(snaps[:, i], ref[:, i]) for i in range(steps + 1)) < TOL
+
+
+def test_ecsw_golden(h, golden):
+    g = golden("ecsw_n24.npz")
+    n, steps = int(g["n"]), int(g["steps"])
+    gx, gy = h.make_2D_grid(0, 100, 0, 100, n, n)
+    w0 = np.ones(2 * n * n)
+    red, times, info = h.inviscid_burgers_ecsw_fixed(gx, gy, g["weights"], w0, float(g["dt"]), steps, list(g["mu"]),
+                                                     np.ascontiguousarray(g["basis"]), return_info=True)
+    assert red.shape == g["red_coords"].shape and len(times) == 3
+    assert info["sample_inds"].dtype == np.int64 and np.array_equal(info["sample_inds"], g["sample_inds"])
+    assert info["augmented_sample"].dtype == np.int64
+    assert np.array_equal(info["augmented_sample"], g["augmented_sample"])        # bit-exact index sets
+    assert np.array_equal(h.generate_augmented_mesh(gx, gy, g["sample_inds"]), g["augmented_sample"])
+    assert info["gn_its"].tolist() == g["gn_its"].tolist()
+    assert max(rel(red[:, i], g["red_coords"][:, i]) for i in range(steps + 1)) < TOL
+
+
+def test_ecsw_vs_oracle_with_boundary_weights(h):
+    """Weights as run_HPROM_ecsw_joshua.py builds them: bc_w = 10 on every boundary cell, a
+    sparse positive set inside."""
+    n, steps, mu = 32, 6, [4.56, 0.019]
+    gx, gy = h.make_2D_grid(0, 100, 0, 100, n, n)
+    w0 = np.ones(2 * n * n)
+    fom = orc.fom_trajectory(gx, gy, w0, 0.05, 10, mu)
+    basis = np.ascontiguousarray(np.linalg.svd(fom, full_matrices=False)[0][:, :5])
+    rng = np.random.default_rng(3)
+    wts = np.zeros((n, n))
+    wts[1:-1, 1:-1] = np.where(rng.random((n - 2, n - 2)) < 0.08, rng.uniform(0.8, 40.0, (n - 2, n - 2)), 0.0)
+    wts[0, :] = wts[-1, :] = wts[:, 0] = wts[:, -1] = 10.0
+    red, times, info = h.inviscid_burgers_ecsw_fixed(gx, gy, wts.ravel(), w0, 0.05, steps, mu, basis, return_info=True)
+    ref, _, s_ref, a_ref, hist = orc.ecsw_trajectory(gx, gy, wts.ravel(), w0, 0.05, steps, mu, basis, return_info=True)
+    assert np.array_equal(info["sample_inds"], s_ref) and np.array_equal(info["augmented_sample"], a_ref)
+    assert info["gn_its"].tolist() == [len(x) for x in hist]
+    assert max(rel(red[:, i], ref[:, i]) for i in range(steps + 1)) < TOL
+
+
+def test_training_matrix_golden(h, golden):
+    g = golden("ecswC_n12.npz")
+    n, steps = int(g["n"]), int(g["steps"])
+    gx, gy = h.make_2D_grid(0, 100, 0, 100, n, n)
+    S = g["snaps"]
+    Cm = h.compute_ECSW_training_matrix_2D(S[:, 3:steps:2], S[:, 0:steps - 3:2], g["basis"], None, None, gx, gy,
+                                           float(g["dt"]), list(g["mu"]))
+    assert Cm.shape == g["C"].shape
+    assert np.allclose(Cm, g["C"], rtol=1e-11, atol=1e-15)
