@@ -32,17 +32,17 @@ DT = 0.05
 NUM_STEPS = 500
 MU1_RANGE = (4.25, 5.5)
 MU2_RANGE = (0.015, 0.03)
+NCU_DRAM_BYTES_PER_CELL_UPDATE = 44.7     # ncu --set full, profiles/r01_fom_full_ncu.md
+FP64_INSTR_PER_CELL_UPDATE_K4 = 228       # DFMA/DMUL/DADD issued per cell-update with 4 Newton solves (SASS count)
+FP64_PEAK_TFLOPS = 34.09                  # measured DFMA peak, profiles/r01_fp64_microbench.txt
 METRIC = "fom_cell_updates_per_s"
 UNIT = "cell-updates/s"
 
 
 def mu_lattice(count, rank=0, world=1):
-    """`count` samples per rank on a lattice of the training range, split contiguously."""
-    total = count * world
-    m1 = int(np.ceil(np.sqrt(total)))
-    m2 = int(np.ceil(total / m1))
-    pts = [[a, b] for a in np.linspace(*MU1_RANGE, m1) for b in np.linspace(*MU2_RANGE, m2)][:total]
-    return pts[rank * count:(rank + 1) * count]
+    """`count` samples per rank (weak scaling) on a lattice of the training range, split contiguously."""
+    from finitedifference_b200 import sharding
+    return sharding.shard_mus(sharding.mu_lattice(count * world, MU1_RANGE, MU2_RANGE), rank, world)
 
 
 class ClockSampler:
@@ -230,14 +230,22 @@ def main():
     abytes = algorithmic_bytes(its, cells)
     achieved = abytes / (float(np.mean(run_ms)) * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "fom_chunk_kernel",
+                "traffic": NCU_DRAM_BYTES_PER_CELL_UPDATE * cells * T * B / max(sweeps, 1),
+                "kernel": "fom_chunk_kernel",
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6.65 TB/s",
                 "algorithmic_bytes_per_step": abytes, "launches_per_step": sweeps,
                 "avg_launch_us": 1e3 * float(np.mean(run_ms)) / max(sweeps, 1),
                 "note": "algorithmic bytes = (48*solves + 32) B per cell-update (SURVEY 8d: one HBM pass per "
-                        "Newton sweep); the kernel fuses the sweeps of a step in registers, so its DRAM traffic "
-                        "is ~32 B per cell-update and frac may exceed 1: the binding unit is the FP64 pipe",
-                "fused_dram_bytes_model_per_step": int(32 * cells * T * B),
+                        "Newton sweep). The kernel fuses the sweeps of a time step in registers, so its real DRAM "
+                        "traffic is lower (traffic, from ncu) and the binding unit is the FP64 pipe (fp64)",
+                "traffic_source": "profiles/r01_fom_full_ncu.md: dram read+write = 44.7 B per cell-update "
+                                  "(ncu --set full of this command), scaled to this run's cell-updates per launch",
+                "fp64": {"instr_per_cell_update": FP64_INSTR_PER_CELL_UPDATE_K4,
+                         "achieved_tflops": 2e-12 * FP64_INSTR_PER_CELL_UPDATE_K4 * value / world,
+                         "peak_tflops": FP64_PEAK_TFLOPS, "frac": 2e-12 * FP64_INSTR_PER_CELL_UPDATE_K4 * value
+                         / world / FP64_PEAK_TFLOPS,
+                         "source": "profiles/r01_fp64_microbench.txt (DFMA peak measured on this pool) and the "
+                                   "SASS count of FP64 instructions per cell-update at 4 solves"},
                 "steps_redone": redone}
 
     # end to end through the drop-in API: host w0 in, (2N, T+1) host snapshot arrays out

@@ -101,6 +101,25 @@ __global__ void __launch_bounds__(256) rom_jv_kernel(const RomArgs a) {
     }
 }
 
+// The Jacobian itself, for callers that want the matrix (inviscid_burgers_exact_jac2D, :2703-2732):
+// 12 values per row pair in fixed slots; the host owns the column pattern
+//   u row:  (p) (xl) (ja) (jb) | (N+ja) (N+jb)      v row:  (p) (xl) | (N+p) (N+xl) (N+ja) (N+jb)
+__global__ void __launch_bounds__(256) rom_jac_values_kernel(const RomArgs a) {
+    const bfd_rom_mesh &m = a.m;
+    const long long n = m.nrows, nc = m.ncells;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const int p = m.p[i], xl = m.xl[i], ja = m.ja[i], jb = m.jb[i];
+        const double cx = m.cx[i], cxl = (xl >= 0) ? m.cxl[i] : 0.0, cy = (ja >= 0) ? m.cy[i] : 0.0,
+                     cyd = (jb >= 0) ? m.cyd[i] : 0.0;
+        const int xls = xl >= 0 ? xl : p, jas = ja >= 0 ? ja : p, jbs = jb >= 0 ? jb : p;
+        const double pxu = cx * a.w[p], pxv = cx * a.w[nc + p], lxu = cxl * a.w[xls], lxv = cxl * a.w[nc + xls];
+        const double ayu = cy * a.w[jas], ayv = cy * a.w[nc + jas], byu = cyd * a.w[jbs], byv = cyd * a.w[nc + jbs];
+        double *o = a.JV + 12 * i;
+        o[0] = 1.0 + pxu;  o[1] = -lxu;       o[2] = 0.5 * ayv;        o[3] = -0.5 * byv;  o[4] = 0.5 * ayu;  o[5] = -0.5 * byu;
+        o[6] = 0.5 * pxv;  o[7] = -0.5 * lxv; o[8] = 1.0 + 0.5 * pxu;  o[9] = -0.5 * lxu;  o[10] = ayv;       o[11] = -byv;
+    }
+}
+
 // C[j, cell] = r_u[cell]*(JV)_u[cell, j] + r_v[cell]*(JV)_v[cell, j]   (:2813-2814), one snapshot's
 // k x nrows block written row-major with leading dimension ldc; 32x32 tiles through shared memory
 // so that reads run along modes and writes along cells.
@@ -151,6 +170,16 @@ extern "C" int bfd_rom_jv(const bfd_rom_mesh *m, const double *w, const double *
     long long grid = (m->nrows + 7) / 8;
     if (grid > 148 * 16) grid = 148 * 16;
     BFD_LAUNCH(rom_jv_kernel, BFD_GRID((int)grid), dim3(32, 8), 0, (cudaStream_t)stream, a);
+    BFD_LAUNCHED();
+    return BFD_OK;
+}
+
+extern "C" int bfd_jac_csr_values(const bfd_rom_mesh *m, const double *w, double *vals, void *stream) {
+    if (check_mesh(m) != BFD_OK || !w || !vals) return BFD_EINVAL;
+    RomArgs a{*m, w, nullptr, nullptr, nullptr, nullptr, vals, 0};
+    long long grid = (m->nrows + 255) / 256;
+    if (grid > 148 * 8) grid = 148 * 8;
+    BFD_LAUNCH(rom_jac_values_kernel, BFD_GRID((int)grid), 256, 0, (cudaStream_t)stream, a);
     BFD_LAUNCHED();
     return BFD_OK;
 }

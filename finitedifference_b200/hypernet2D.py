@@ -21,12 +21,16 @@ import numpy as np
 
 from .discretisation import make_2D_grid  # noqa: F401  (re-exported, hypernet2D.py:2501)
 from .fom import FomSolver
+from .operators import (get_ops, inviscid_burgers_exact_jac2D, inviscid_burgers_exact_jac2D_ecsw,  # noqa: F401
+                        inviscid_burgers_res2D, inviscid_burgers_res2D_alt, inviscid_burgers_res2D_ecsw, make_ddx)
 from .rom import EcswSolver, LspgSolver, ecsw_training_matrix, generate_augmented_mesh  # noqa: F401
 
 __all__ = [
     "make_2D_grid", "inviscid_burgers_implicit2D", "inviscid_burgers_implicit2D_batch",
     "inviscid_burgers_implicit2D_LSPG", "inviscid_burgers_ecsw_fixed", "generate_augmented_mesh",
     "compute_ECSW_training_matrix_2D",
+    "make_ddx", "get_ops", "inviscid_burgers_res2D", "inviscid_burgers_res2D_alt", "inviscid_burgers_res2D_ecsw",
+    "inviscid_burgers_exact_jac2D", "inviscid_burgers_exact_jac2D_ecsw",
     "load_or_compute_snaps", "param_to_snap_fn", "get_saved_params", "compute_error",
 ]
 

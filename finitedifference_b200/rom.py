@@ -94,16 +94,27 @@ class MeshTables:
         else:
             den = np.full(rows.shape, dx[0])                              # :2665
         lbc = np.where(c == 0, 0.5 * dt * mu[0] ** 2 / den, 0.0)
-        self.nrows, self.ncells, self.device = int(rows.size), int(ncells), device
+        self._upload(dict(p=p, xl=xl, yd=yd, ja=ja, jb=jb, cx=cx[c], cxl=cxl[c], cy=cy[r], cyd=cyd[r], src=src,
+                          lbc=lbc), ncells, device, weight)
+
+    @classmethod
+    def from_tables(cls, tables, ncells, device, weight=None):
+        """Tables given directly (keys as in ``bfd_rom_mesh``), e.g. read off caller-supplied operators."""
+        self = cls.__new__(cls)
+        self._upload(tables, ncells, device, weight)
+        return self
+
+    def _upload(self, t, ncells, device, weight):
+        self.nrows, self.ncells, self.device = int(np.asarray(t["p"]).size), int(ncells), device
         i32 = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.int32)).to(device)
         f64 = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(device)
-        self._t = [i32(a) for a in (p, xl, yd, ja, jb)] + \
-                  [f64(a) for a in (cx[c], cxl[c], cy[r], cyd[r], src, lbc)]
+        self._t = [i32(t[k]) for k in ("p", "xl", "yd", "ja", "jb")] + \
+                  [f64(t[k]) for k in ("cx", "cxl", "cy", "cyd", "src", "lbc")]
         wptr = None
         if weight is not None:
             self._t.append(f64(weight))
             wptr = self._t[-1].data_ptr()
-        self.c = _lib.RomMesh(self.nrows, self.ncells, *[t.data_ptr() for t in self._t[:11]], wptr)
+        self.c = _lib.RomMesh(self.nrows, self.ncells, *[x.data_ptr() for x in self._t[:11]], wptr)
 
 
 class _RomBase:

@@ -157,6 +157,14 @@ int bfd_rom_residual(const bfd_rom_mesh *mesh, const double *w, const double *wp
 int bfd_rom_jv(const bfd_rom_mesh *mesh, const double *w, const double *V, int k, double *JV,
                void *stream);
 
+/* Values of the Jacobian rows of `mesh` at state w, 12 per row i at vals[12*i ..], in fixed slots
+ * whose columns the caller derives from the index tables (N = ncells):
+ *   u row i:      (p) (xl) (ja) (jb) (N+ja) (N+jb)
+ *   v row nrows+i:(p) (xl) (N+p) (N+xl) (N+ja) (N+jb)
+ * Slots of an absent neighbour hold 0.  Replaces the sparse products and bmat of
+ * inviscid_burgers_exact_jac2D (:2703-2732) / _exact_jac2D_ecsw (:2734-2744); weight is ignored. */
+int bfd_jac_csr_values(const bfd_rom_mesh *mesh, const double *w, double *vals, void *stream);
+
 /* One snapshot's block of the ECSW training matrix (compute_ECSW_training_matrix_2D, :2807-2814):
  * C[j*ldc + cell] = r[cell]*JV[cell][j] + r[nrows+cell]*JV[nrows+cell][j], j < k, cell < nrows. */
 int bfd_ecsw_c_block(int64_t nrows, int k, const double *r, const double *JV, double *C, size_t ldc,

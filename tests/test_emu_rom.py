@@ -96,3 +96,52 @@ def test_training_matrix_block(lib, golden):
         Cm[i * k:(i + 1) * k] = blk
     assert np.allclose(Cm, Cref, rtol=1e-11, atol=1e-15)
     assert np.allclose(Cm, orc.ecsw_training_matrix(cur, prev, V, gx, gy, dt, mu), rtol=1e-11, atol=1e-15)
+
+
+def run_jac(lib, tables, ncells, w):
+    from finitedifference_b200 import operators as ops
+    mesh = MeshTables.from_tables(tables, ncells, CPU)
+    vals = np.zeros((mesh.nrows, 12))
+    assert lib.bfd_jac_csr_values(C.byref(mesh.c), E.ptr(np.ascontiguousarray(w)), E.ptr(vals), None) == 0
+    return ops.assemble_csr(vals, tables, ncells)
+
+
+def test_jacobian_csr_from_caller_operators(lib, golden):
+    """inviscid_burgers_exact_jac2D as a matrix: tables read off the operators the caller passes
+    (get_ops' and the rows-only-permuted one of hypernet2D.py:167), values from the kernel."""
+    from finitedifference_b200 import operators as ops
+    g = golden("ops_n12.npz")
+    n, dt = int(g["n"]), float(g["dt"])
+    gx, gy = orc.make_2D_grid(0, 100, 0, 100, n, n)
+    w = np.ascontiguousarray(g["w"])
+    own = np.arange(n * n)
+    dxec, dyec, jdx, jdy, eye = ops.get_ops(gx, gy)
+    ox, oy = orc.lifted_operators(gx, gy)
+    assert abs(jdx - ox).max() == 0 and abs(jdy - oy).max() == 0 and eye.shape == (2 * n * n,) * 2
+    assert abs(dxec.tocsr() - orc.backward_difference(gx)).max() == 0 and dxec.format == "lil"
+    J = run_jac(lib, ops.jacobian_tables(jdx, jdy, dt, own), n * n, w)
+    assert J.shape == g["J_exact"].shape and np.max(np.abs(J.toarray() - g["J_exact"])) < 1e-14
+    assert J.nnz == np.count_nonzero(g["J_exact"])
+    qx, qy = orc.lifted_operators(gx, gy, "unpermuted")
+    J = run_jac(lib, ops.jacobian_tables(qx, qy, dt, own), n * n, w)
+    assert np.max(np.abs(J.toarray() - g["J_lspg"])) < 1e-14
+
+
+def test_jacobian_csr_sampled_rows(lib, golden):
+    from finitedifference_b200 import operators as ops
+    g = golden("ecsw_ops_n24.npz")
+    n, dt = int(g["n"]), float(g["dt"])
+    gx, gy = orc.make_2D_grid(0, 100, 0, 100, n, n)
+    sample = np.where(g["weights"] != 0)[0]
+    aug = generate_augmented_mesh(gx, gy, sample)
+    jdx_s, jdy_s, eye2 = orc.ecsw_operators(gx, gy, sample, aug)
+    rng = np.random.default_rng(5)
+    w = 1.0 + rng.random(2 * aug.size)
+    J = run_jac(lib, ops.jacobian_tables(jdx_s, jdy_s, dt, np.searchsorted(aug, sample)), aug.size, w)
+    Jo = orc.jacobian_ecsw(w, dt, jdx_s, jdy_s, eye2, sample, aug)
+    assert J.shape == Jo.shape and abs(J - Jo).max() < 1e-14
+    idx = np.concatenate((aug, n * n + aug))
+    J = run_jac(lib, ops.jacobian_tables(jdx_s, jdy_s, dt, np.searchsorted(aug, sample)), aug.size, g["w"][idx])
+    assert np.max(np.abs(J.toarray() - g["J_red"])) < 1e-14                      # the reference's own matrix
+    with pytest.raises(ValueError):
+        ops.jacobian_tables(jdy_s, jdx_s, dt, np.searchsorted(aug, sample) + 1)
