@@ -40,6 +40,15 @@ class FomCoef(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("cx", "cxl", "cy", "cyd", "src", "lbc")]
 
 
+class FomSlab(C.Structure):
+    """``bfd_fom_slab``."""
+    _fields_ = [("rank", C.c_int32), ("world", C.c_int32), ("strip_begin", C.c_int32), ("strip_end", C.c_int32),
+                ("home", C.c_void_p), ("next_halo", C.c_void_p)]
+
+
+IPC_HANDLE_BYTES = 64
+
+
 class RomMesh(C.Structure):
     """``bfd_rom_mesh``."""
     _fields_ = [("nrows", C.c_int64), ("ncells", C.c_int64)] + \
@@ -60,6 +69,19 @@ SIGNATURES = {
                                  C.c_size_t, _P, _P]),
     "bfd_fom_trace": (C.c_int, [C.POINTER(FomDesc), _P, _P, _P]),
     "bfd_fom_diagnostics": (C.c_int, [C.POINTER(FomDesc), _P, _P, _P, _P]),
+    "bfd_fom_slab_workspace_bytes": (C.c_size_t, [C.POINTER(FomDesc), C.POINTER(FomSlab)]),
+    "bfd_fom_slab_halo_offset": (C.c_size_t, [C.POINTER(FomDesc), C.POINTER(FomSlab)]),
+    "bfd_fom_slab_init": (C.c_int, [C.POINTER(FomDesc), C.POINTER(FomSlab), _P, C.c_size_t, _P]),
+    "bfd_fom_slab_set_initial": (C.c_int, [C.POINTER(FomDesc), C.POINTER(FomSlab), _P, _P, C.c_size_t, _P]),
+    "bfd_fom_slab_run": (C.c_int, [C.POINTER(FomDesc), C.POINTER(FomSlab), _P, C.POINTER(FomCoef), _P, _P]),
+    "bfd_fom_slab_export": (C.c_int, [C.POINTER(FomDesc), C.POINTER(FomSlab), _P, C.c_int, C.c_int, C.c_int, C.c_int,
+                                      C.c_size_t, _P, _P]),
+    "bfd_fom_slab_diagnostics": (C.c_int, [C.POINTER(FomDesc), C.POINTER(FomSlab), _P, _P, _P, _P]),
+    "bfd_mem_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
+    "bfd_mem_free": (C.c_int, [_P]),
+    "bfd_ipc_export": (C.c_int, [_P, C.c_char_p]),
+    "bfd_ipc_open": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
+    "bfd_ipc_close": (C.c_int, [_P]),
     "bfd_rom_residual": (C.c_int, [C.POINTER(RomMesh), _P, _P, _P, _P, _P]),
     "bfd_rom_jv": (C.c_int, [C.POINTER(RomMesh), _P, _P, C.c_int, _P, _P]),
     "bfd_jac_csr_values": (C.c_int, [C.POINTER(RomMesh), _P, _P, _P]),

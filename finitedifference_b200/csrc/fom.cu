@@ -52,7 +52,9 @@ struct FomCtl {            // one per mu sample, 64 bytes
     int redone;            // steps redone or continued so far (statistics)
     unsigned epoch;        // bumped by every commit: strips waiting to restart watch it
     double init_norm;      // ||r(x_0)|| of step t, kept for continuation passes
-    double pad1[3];
+    unsigned exits;        // slab runs: strips (of all ranks) that left a launch, summed over launches
+    unsigned pad0;
+    double pad1[2];
 };
 static_assert(sizeof(FomCtl) == 64, "FomCtl must stay 64 bytes");
 
@@ -69,11 +71,23 @@ struct FomGlobal {         // one per workspace, 64 bytes
     int pad[12];
 };
 
+// Which part of the grid a workspace holds.  Whole grid: strip0 = 0, ns_global = local strips.
+// Slab runs (one grid over several GPUs, bfd_fom_slab): this rank owns the 32-column strips
+// [strip0, strip0 + ssl.nstrips); the per-sample control blocks, norms and verdicts of ALL strips
+// live in rank 0's workspace ("home", peer-mapped), the records its first strip consumes in its own
+// "halo" buffer, which the last strip of the rank on the left fills over NVLink.
+struct SlabView {
+    bool slab;
+    int rank, world, strip0, ns_global, nx_local;
+    void *home;
+    double *next_halo;
+};
+
 struct FomLayout {         // byte offsets inside the workspace
-    Ssl ssl;
+    Ssl ssl;               // the strips held here (nx = local columns)
     int batch, num_steps, chunk;
     size_t off_global, off_ctl, off_its, off_relnorm, off_steprec, off_arrive, off_partial, off_trace, off_edge,
-        off_pool, total;
+        off_halo, off_pool, total;
     size_t edge_stride_strip;  // doubles: one strip boundary, [chunk][ny][kRecDoubles]
     size_t edge_stride_mu;     // doubles
     size_t pool_stride_mu;     // doubles
@@ -96,13 +110,36 @@ static int check_desc(const bfd_fom_desc *d) {
     return BFD_OK;
 }
 
-static FomLayout fom_layout(const bfd_fom_desc *d) {
+static SlabView whole_grid(const bfd_fom_desc *d) {
+    SlabView v;
+    v.slab = false; v.rank = 0; v.world = 1; v.strip0 = 0;
+    v.ns_global = make_ssl(d->nx, d->ny, 1).nstrips;
+    v.nx_local = d->nx; v.home = nullptr; v.next_halo = nullptr;
+    return v;
+}
+
+static int slab_view(const bfd_fom_desc *d, const bfd_fom_slab *sl, SlabView *v) {
+    if (check_desc(d) != BFD_OK || !sl) return BFD_EINVAL;
+    const int ns = make_ssl(d->nx, d->ny, 1).nstrips;
+    if (sl->world < 1 || sl->rank < 0 || sl->rank >= sl->world) return BFD_EINVAL;
+    if (sl->strip_begin < 0 || sl->strip_end > ns || sl->strip_begin >= sl->strip_end) return BFD_EINVAL;
+    if ((sl->rank == 0) != (sl->strip_begin == 0) || (sl->rank == sl->world - 1) != (sl->strip_end == ns)) return BFD_EINVAL;
+    v->slab = true; v->rank = sl->rank; v->world = sl->world; v->strip0 = sl->strip_begin; v->ns_global = ns;
+    const int c1 = sl->strip_end * 32 < d->nx ? sl->strip_end * 32 : d->nx;
+    v->nx_local = c1 - sl->strip_begin * 32;
+    v->home = sl->home; v->next_halo = (double *)sl->next_halo;
+    return BFD_OK;
+}
+
+// Control arrays are sized by the GLOBAL strip count and come first, so their offsets are the
+// same in every rank's workspace (the home pointers of a slab run are home + these offsets).
+static FomLayout fom_layout(const bfd_fom_desc *d, const SlabView &v) {
     FomLayout L;
-    L.ssl = make_ssl(d->nx, d->ny, 1);
+    L.ssl = make_ssl(v.nx_local, d->ny, 1);
     L.batch = d->batch;
     L.num_steps = d->num_steps;
     L.chunk = desc_chunk(d);
-    const size_t B = (size_t)d->batch, S = (size_t)L.chunk, ns = (size_t)L.ssl.nstrips;
+    const size_t B = (size_t)d->batch, S = (size_t)L.chunk, ns = (size_t)v.ns_global, nl = (size_t)L.ssl.nstrips;
     size_t o = 0;
     L.off_global = o;   o = align_up(o + sizeof(FomGlobal), 256);
     L.off_ctl = o;      o = align_up(o + sizeof(FomCtl) * B, 256);
@@ -113,8 +150,9 @@ static FomLayout fom_layout(const bfd_fom_desc *d) {
     L.off_partial = o;  o = align_up(o + sizeof(double) * B * S * ns * kNormSlots, 256);
     L.off_trace = o;    o = align_up(o + sizeof(unsigned long long) * B * S * ns * 3, 256);
     L.edge_stride_strip = S * (size_t)d->ny * kRecDoubles;
-    L.edge_stride_mu = L.edge_stride_strip * (ns > 1 ? ns - 1 : 0);
+    L.edge_stride_mu = L.edge_stride_strip * (nl > 1 ? nl - 1 : 0);
     L.off_edge = o;     o = align_up(o + sizeof(double) * L.edge_stride_mu * B, 256);
+    L.off_halo = o;     o = align_up(o + sizeof(double) * L.edge_stride_strip * B * (v.strip0 > 0 ? 1 : 0), 256);
     L.pool_stride_mu = L.ssl.state_doubles * (size_t)(d->num_steps + 1);
     L.off_pool = o;     o = align_up(o + sizeof(double) * L.pool_stride_mu * B, 256);
     L.total = o;
@@ -138,23 +176,33 @@ struct FomArgs {
     double *edge;       // [batch][nstrips-1][chunk][ny][kRecDoubles]
     double *pool;       // [batch][num_steps+1][state]   snapshot t of sample m in slot t
     size_t edge_stride_strip, edge_stride_mu, pool_stride_mu;
+    // slab runs (whole grid: strip0 = 0, ns_global = ssl.nstrips, the rest unused)
+    int strip0, ns_global, launch_index, slab;
+    unsigned *ticket;   // virtual block id dispenser of THIS rank (glob may be rank 0's)
+    double *halo;       // [batch][chunk][ny][kRecDoubles] records consumed by this rank's first strip
+    double *next_halo;  // the same buffer of the rank on the right (peer-mapped), or null
 };
 
-static FomArgs fom_args(const bfd_fom_desc *d, const FomLayout &L, void *ws) {
-    char *b = (char *)ws;
+static FomArgs fom_args(const bfd_fom_desc *d, const FomLayout &L, void *ws, const SlabView &v) {
+    char *b = (char *)ws;                                     // pool, hand-off records, ticket, trace: local
+    char *h = (v.slab && v.home) ? (char *)v.home : b;        // control blocks, norms, verdicts: rank 0's
     FomArgs a;
     a.ssl = L.ssl;
     a.batch = d->batch; a.num_steps = d->num_steps; a.max_its = d->max_its; a.chunk = L.chunk;
     a.strict = d->strict; a.uniform_y = d->uniform_y; a.hint = desc_hint(d);
     a.rel_tol = d->rel_tol;
     a.cx = a.cxl = a.cy = a.cyd = a.src = a.lbc = nullptr;
-    a.glob = (FomGlobal *)(b + L.off_global);
-    a.ctl = (FomCtl *)(b + L.off_ctl);
-    a.its = (int *)(b + L.off_its);
-    a.relnorm = (double *)(b + L.off_relnorm);
-    a.steprec = (StepRec *)(b + L.off_steprec);
-    a.arrive = (unsigned *)(b + L.off_arrive);
-    a.partial = (double *)(b + L.off_partial);
+    a.glob = (FomGlobal *)(h + L.off_global);
+    a.ctl = (FomCtl *)(h + L.off_ctl);
+    a.its = (int *)(h + L.off_its);
+    a.relnorm = (double *)(h + L.off_relnorm);
+    a.steprec = (StepRec *)(h + L.off_steprec);
+    a.arrive = (unsigned *)(h + L.off_arrive);
+    a.partial = (double *)(h + L.off_partial);
+    a.ticket = &((FomGlobal *)(b + L.off_global))->ticket;
+    a.strip0 = v.strip0; a.ns_global = v.ns_global; a.launch_index = 0; a.slab = v.slab ? 1 : 0;
+    a.halo = v.strip0 > 0 ? (double *)(b + L.off_halo) : nullptr;
+    a.next_halo = v.next_halo;
     a.trace = (unsigned long long *)(b + L.off_trace);
     a.edge = (double *)(b + L.off_edge);
     a.pool = (double *)(b + L.off_pool);
@@ -206,6 +254,7 @@ struct StepIo {
     int ny, strip, nstrips, lane;
     double cx, cxl, src;  // column constants of this lane
     bool colok, inlet;
+    bool in_remote, out_remote;   // slab runs: the hand-off on that side crosses to another GPU
     int *error;
     unsigned long long *stats;   // hand-off wait statistics of this (sample, step, strip)
 };
@@ -433,8 +482,8 @@ __device__ __forceinline__ void dma_part(const StepIo &io) {
     const int nsteps = ny + kSkew + K;
     EdgeIn<NPR> ein;
     EdgeOut<NPR> eout;
-    ein.init(io.edge_in, io.ring_in, ny, lane, io.strip > 0);
-    eout.init(io.edge_out, io.ring_out, ny, lane, io.strip < io.nstrips - 1);
+    ein.init(io.edge_in, io.ring_in, ny, lane, io.strip > 0, io.in_remote);
+    eout.init(io.edge_out, io.ring_out, ny, lane, io.strip < io.nstrips - 1, io.out_remote);
     const saddr pf_lane = io.pf + (saddr)(lane * 8);
     auto pf_issue = [&](int row) {
         const int r = row < last_row ? row : last_row;
@@ -509,7 +558,7 @@ namespace bfd {
 // pass produced: rn[k] = ||r(x_{kb+k})||, k = 0..K.  Run by the last strip to finish the step.
 // Returns true when the speculated solve count was wrong and the sample must stop and restart.
 __device__ bool validate_step(const FomArgs &a, int m, int i, int kb, int K, double init_prev) {
-    const int ns = a.ssl.nstrips;
+    const int ns = a.ns_global;
     const volatile double *part = a.partial + (size_t)(m * a.chunk + i) * ns * kNormSlots;
     double rn[kNormSlots];
     for (int k = 0; k <= K; ++k) {
@@ -547,7 +596,9 @@ __device__ void commit_segment(const FomArgs &a, int m, int t0, int i0, int n, i
     int new_kbase = 0, new_kfirst = k_first;
     bool stop = false;
     for (int ii = 0; ii < n && !stop; ++ii) {
-        const StepRec rec = a.steprec[(size_t)m * a.chunk + i0 + ii];
+        const volatile StepRec *vr = a.steprec + (size_t)m * a.chunk + i0 + ii;   // written by another CTA: not through L1
+        StepRec rec;
+        rec.status = vr->status; rec.kconv = vr->kconv; rec.rel = vr->rel; rec.init = vr->init;
         const int kb = ii ? 0 : kbase;
         int K = ii ? k_spec : k_first;
         if (K > a.max_its - kb) K = a.max_its - kb;
@@ -572,7 +623,12 @@ __device__ void commit_segment(const FomArgs &a, int m, int t0, int i0, int n, i
     else { ctl->kbase = new_kbase; ctl->k_first = new_kfirst; }
     ctl->t = t;
     if (redo) { ctl->redone += redo; atomicAdd(&a.glob->redone, redo); }
-    if (t >= a.num_steps) atomicAdd(&a.glob->done, 1);
+    if (t >= a.num_steps) {
+#ifndef BFD_EMULATE
+        if (a.slab) { __threadfence_system(); atomicAdd_system(&a.glob->done, 1); } else
+#endif
+        atomicAdd(&a.glob->done, 1);
+    }
 }
 
 // Up to `chunk` time-step attempts of every unfinished sample.  One CTA <-> (sample m, strip j);
@@ -587,20 +643,66 @@ __device__ void commit_segment(const FomArgs &a, int m, int t0, int i0, int n, i
 // wait for the commit by the last of them (all strips of the sample are resident by then: they
 // all took part in the failed step), which rewinds the sample to the failed step with the
 // right count, and carry on inside the same launch.
-template <bool UNI>
+//
+// SLAB: the strips of a sample are spread over several GPUs (bfd_fom_slab).  Control words live
+// in rank 0's memory, so their atomics and fences are system-scoped, and since the ranks' launch
+// sequences are not ordered by a stream, a launch waits until every strip of every rank has left
+// the launch before it (ctl->exits) before it reads the sample's state.
+template <bool SLAB> __device__ __forceinline__ void fence() { if (SLAB) __threadfence_system(); else __threadfence(); }
+template <bool SLAB> __device__ __forceinline__ unsigned a_inc(unsigned *p, unsigned lim) {
+#ifndef BFD_EMULATE
+    if (SLAB) return atomicInc_system(p, lim);
+#endif
+    return atomicInc(p, lim);
+}
+template <bool SLAB> __device__ __forceinline__ unsigned a_max(unsigned *p, unsigned v) {
+#ifndef BFD_EMULATE
+    if (SLAB) return atomicMax_system(p, v);
+#endif
+    return atomicMax(p, v);
+}
+template <bool SLAB> __device__ __forceinline__ unsigned a_or(unsigned *p, unsigned v) {
+#ifndef BFD_EMULATE
+    if (SLAB) return atomicOr_system(p, v);
+#endif
+    return atomicOr(p, v);
+}
+template <bool SLAB> __device__ __forceinline__ unsigned a_add(unsigned *p, unsigned v) {
+#ifndef BFD_EMULATE
+    if (SLAB) return atomicAdd_system(p, v);
+#endif
+    return atomicAdd(p, v);
+}
+
+template <bool UNI, bool SLAB>
 __global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk_kernel(const FomArgs a) {
     constexpr int kSmemDoubles = (kInRing + kOutRing) * kRecDoubles + (kHandIfaces * kHandBytes + kXchgBytes + kPfBytes) / 8;
     BFD_SHARED_ARRAY(double, s_mem, [kSmemDoubles]);
     BFD_SHARED_ARRAY(int, s_ctl, [8]);
+    BFD_SHARED_ARRAY(double, s_dbl, [2]);
     const int lane = lane_id(), warp = threadIdx.x >> 5;
     const int nstrips = a.ssl.nstrips;
     for (int i = threadIdx.x; i < kSmemDoubles; i += blockDim.x) s_mem[i] = 0.0;
-    if (threadIdx.x == 0) s_ctl[0] = (int)atomicInc(&a.glob->ticket, gridDim.x - 1);
+    if (threadIdx.x == 0) s_ctl[0] = (int)atomicInc(a.ticket, gridDim.x - 1);
     __syncthreads();
     const int item = __shfl_sync(0xffffffffu, s_ctl[0], 0);
     if (item >= a.batch * nstrips) return;
     const int m = item / nstrips, j = item - m * nstrips;
+    const int jg = j + a.strip0, nsg = a.ns_global;        // this strip and the strip count in the whole grid
     FomCtl *ctl = a.ctl + m;
+    if (SLAB) {
+        if (threadIdx.x == 0 && a.launch_index > 0) {
+            const unsigned need = (unsigned)a.launch_index * (unsigned)nsg;
+            unsigned spins = 0;
+            while (*(volatile unsigned *)&ctl->exits < need && *(volatile int *)&ctl->t < a.num_steps &&
+                   *(volatile int *)&a.glob->error == 0) {
+                spin_pause();
+                if (++spins > kSpinLimit) { atomicExch(&a.glob->error, BFD_ETIMEOUT); break; }
+            }
+            fence<SLAB>();
+        }
+        __syncthreads();
+    }
 
     const int nx = a.ssl.nx, ny = a.ssl.ny;
     const size_t sd = a.ssl.state_doubles;
@@ -617,12 +719,14 @@ __global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk
     io.pf = io.xchg + (saddr)kXchgBytes;
     io.lbc = a.lbc + (size_t)m * ny;
     io.cy = a.cy; io.cyd = a.cyd;
-    io.ny = ny; io.strip = j; io.nstrips = nstrips; io.lane = lane;
+    io.ny = ny; io.strip = jg; io.nstrips = nsg; io.lane = lane;
+    io.in_remote = SLAB && j == 0 && jg > 0;
+    io.out_remote = SLAB && j == nstrips - 1 && jg < nsg - 1;
     const int c = j * 32 + lane;
     io.colok = c < nx;
     const int cc = io.colok ? c : nx - 1;
     io.cx = a.cx[cc]; io.cxl = a.cxl[cc]; io.src = a.src[(size_t)m * nx + cc];
-    io.inlet = (j == 0 && lane == 0);
+    io.inlet = (jg == 0 && lane == 0);
     io.error = &a.glob->error;
 
     int attempt = 0;                 // attempts of this launch so far (same on every strip of the sample)
@@ -632,8 +736,10 @@ __global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk
         if (threadIdx.x == 0) {
             // control words are read by one thread and broadcast by shuffle: the compiler then
             // knows they are warp-uniform
-            s_ctl[1] = ctl->t; s_ctl[2] = ctl->kbase; s_ctl[3] = ctl->k_first; s_ctl[4] = ctl->k_spec;
-            epoch0 = *(volatile unsigned *)&ctl->epoch;
+            const volatile FomCtl *vc = ctl;       // written by other CTAs (other GPUs in slab runs)
+            s_ctl[1] = vc->t; s_ctl[2] = vc->kbase; s_ctl[3] = vc->k_first; s_ctl[4] = vc->k_spec;
+            epoch0 = vc->epoch;
+            s_dbl[0] = vc->init_norm;
         }
         __syncthreads();
         const int w = (lane < 8) ? s_ctl[lane] : 0;
@@ -641,7 +747,7 @@ __global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk
         if (t0 >= a.num_steps || attempt >= a.chunk) break;   // trajectory finished / budget of this launch used
         const int kbase = __shfl_sync(0xffffffffu, w, 2), k_first = __shfl_sync(0xffffffffu, w, 3),
                   k_spec = __shfl_sync(0xffffffffu, w, 4);
-        const double init_prev = ctl->init_norm;
+        const double init_prev = s_dbl[0];
         const int i0 = attempt;
         bool refused = false;
         for (; attempt < a.chunk; ++attempt) {
@@ -649,7 +755,7 @@ __global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk
             if (t >= a.num_steps) break;
             __syncthreads();
             if (threadIdx.x == 0) {
-                const unsigned old = atomicMax(&ctl->gate, (unsigned)attempt);
+                const unsigned old = a_max<SLAB>(&ctl->gate, (unsigned)attempt);
                 s_ctl[5] = ((old & kGateStop) && (unsigned)attempt > (old & (kGateStop - 1))) ? 0 : 1;
             }
             __syncthreads();
@@ -666,7 +772,11 @@ __global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk
             const size_t eoff = (size_t)i * ny * kRecDoubles;
             io.edge_in = edge_m + (size_t)(j > 0 ? j - 1 : 0) * a.edge_stride_strip + eoff;
             io.edge_out = edge_m + (size_t)(j < nstrips - 1 ? j : 0) * a.edge_stride_strip + eoff;
-            io.partial = a.partial + ((size_t)(m * a.chunk + i) * nstrips + j) * kNormSlots;
+            if (SLAB) {   // the records that cross a slab boundary live in the consumer's halo buffer
+                if (io.in_remote) io.edge_in = a.halo + (size_t)m * a.edge_stride_strip + eoff;
+                if (io.out_remote) io.edge_out = a.next_halo + (size_t)m * a.edge_stride_strip + eoff;
+            }
+            io.partial = a.partial + ((size_t)(m * a.chunk + i) * nsg + jg) * kNormSlots;
             unsigned long long *tr = a.trace + ((size_t)(m * a.chunk + i) * nstrips + j) * 3;
             if (threadIdx.x == 0) tr[0] = global_timer_ns();
             io.stats = tr + 2;
@@ -685,33 +795,37 @@ __global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk
             __syncthreads();       // every warp has published its norms
             if (threadIdx.x == 0) {
                 tr[1] = global_timer_ns();
-                __threadfence();
-                if (atomicInc(&a.arrive[(size_t)m * a.chunk + i], (unsigned)nstrips - 1) == (unsigned)nstrips - 1) {
-                    __threadfence();
-                    if (validate_step(a, m, i, kb, kb ? 1 : K, init_prev)) atomicOr(&ctl->gate, kGateStop);
+                fence<SLAB>();
+                if (a_inc<SLAB>(&a.arrive[(size_t)m * a.chunk + i], (unsigned)nsg - 1) == (unsigned)nsg - 1) {
+                    fence<SLAB>();
+                    if (validate_step(a, m, i, kb, kb ? 1 : K, init_prev)) a_or<SLAB>(&ctl->gate, kGateStop);
                 }
             }
         }
         // end of the segment: the last strip commits; refused strips wait for it and restart
         if (threadIdx.x == 0) {
-            __threadfence();
-            if (atomicInc(&ctl->arrive, (unsigned)nstrips - 1) == (unsigned)nstrips - 1) {
-                __threadfence();
+            fence<SLAB>();
+            if (a_inc<SLAB>(&ctl->arrive, (unsigned)nsg - 1) == (unsigned)nsg - 1) {
+                fence<SLAB>();
                 commit_segment(a, m, t0, i0, attempt - i0, kbase, k_first, k_spec);
                 // next segment of this launch continues at `attempt`; a new launch starts at 0
                 *(volatile unsigned *)&ctl->gate = refused ? (unsigned)(attempt > 0 ? attempt - 1 : 0) : 0u;
-                __threadfence();
-                atomicAdd(&ctl->epoch, 1u);
+                fence<SLAB>();
+                a_add<SLAB>(&ctl->epoch, 1u);
             } else if (refused) {
                 unsigned spins = 0;
                 while (*(volatile unsigned *)&ctl->epoch == epoch0) {
                     spin_pause();
                     if (++spins > kSpinLimit) { atomicExch(&a.glob->error, BFD_ETIMEOUT); break; }
                 }
-                __threadfence();
+                fence<SLAB>();
             }
         }
         if (!refused) break;
+    }
+    if (SLAB) {   // this strip is done with the launch: its re-armed records and commits are visible
+        __syncthreads();
+        if (threadIdx.x == 0) { fence<SLAB>(); a_add<SLAB>(&ctl->exits, 1u); }
     }
 }
 
@@ -743,26 +857,33 @@ __global__ void fom_import_kernel(const FomArgs a, const double *w0, size_t w0_s
 }
 
 // arm the hand-off records and reset the per-sample control blocks
-__global__ void fom_reset_kernel(const FomArgs a) {
+// `control` = 0 on the ranks of a slab run that do not own the control blocks
+__global__ void fom_reset_kernel(const FomArgs a, int control) {
     const size_t n_edge = a.edge_stride_mu * a.batch;
     const double sentinel = __longlong_as_double((long long)kSentinelBits);
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n_edge;
          i += (size_t)gridDim.x * blockDim.x)
         a.edge[i] = sentinel;
+    const size_t n_halo = a.halo ? a.edge_stride_strip * a.batch : 0;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n_halo;
+         i += (size_t)gridDim.x * blockDim.x)
+        a.halo[i] = sentinel;
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g == 0) *a.ticket = 0;
+    if (!control) return;
     const size_t n_arrive = (size_t)a.batch * a.chunk;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n_arrive;
          i += (size_t)gridDim.x * blockDim.x)
         a.arrive[i] = 0u;
-    const int g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g == 0) {
-        a.glob->ticket = 0; a.glob->done = (a.num_steps == 0) ? a.batch : 0; a.glob->error = 0;
+        a.glob->done = (a.num_steps == 0) ? a.batch : 0; a.glob->error = 0;
         a.glob->redone = 0;
     }
     if (g < a.batch) {
         FomCtl c;
         c.t = 0; c.kbase = 0; c.k_first = a.hint; c.k_spec = a.hint;
         c.gate = 0; c.arrive = 0; c.redone = 0; c.epoch = 0; c.init_norm = 0.0;
-        c.pad1[0] = c.pad1[1] = c.pad1[2] = 0.0;
+        c.exits = 0; c.pad0 = 0; c.pad1[0] = c.pad1[1] = 0.0;
         a.ctl[g] = c;
     }
 }
@@ -819,26 +940,21 @@ __global__ void fom_export_kernel(const FomArgs a, int m, int t0, int t1, int la
 // ------------------------------------------------------------------------------------------
 using namespace bfd;
 
-extern "C" size_t bfd_fom_workspace_bytes(const bfd_fom_desc *d) {
-    if (check_desc(d) != BFD_OK) return 0;
-    return fom_layout(d).total;
-}
-
-extern "C" int bfd_fom_init(const bfd_fom_desc *d, void *ws, size_t ws_bytes, void *stream) {
-    if (check_desc(d) != BFD_OK || !ws) return BFD_EINVAL;
-    const FomLayout L = fom_layout(d);
+static int fom_init_impl(const bfd_fom_desc *d, const SlabView &v, void *ws, size_t ws_bytes, void *stream) {
+    if (!ws) return BFD_EINVAL;
+    const FomLayout L = fom_layout(d, v);
     if (ws_bytes < L.total) return BFD_EWORKSPACE;
-    const FomArgs a = fom_args(d, L, ws);
-    BFD_LAUNCH(fom_reset_kernel, BFD_GRID(592), 256, 0, (cudaStream_t)stream, a);
+    const FomArgs a = fom_args(d, L, ws, v);
+    BFD_LAUNCH(fom_reset_kernel, BFD_GRID(592), 256, 0, (cudaStream_t)stream, a, (!v.slab || v.rank == 0) ? 1 : 0);
     BFD_LAUNCHED();
     return BFD_OK;
 }
 
-extern "C" int bfd_fom_set_initial(const bfd_fom_desc *d, void *ws, const double *w0, size_t w0_stride,
-                                   void *stream) {
-    if (check_desc(d) != BFD_OK || !ws || !w0) return BFD_EINVAL;
-    const FomLayout L = fom_layout(d);
-    const FomArgs a = fom_args(d, L, ws);
+static int fom_set_initial_impl(const bfd_fom_desc *d, const SlabView &v, void *ws, const double *w0,
+                                size_t w0_stride, void *stream) {
+    if (!ws || !w0) return BFD_EINVAL;
+    const FomLayout L = fom_layout(d, v);
+    const FomArgs a = fom_args(d, L, ws, v);
     BFD_LAUNCH(fom_import_kernel, BFD_GRID(592), 256, 0, (cudaStream_t)stream, a, w0, w0_stride);
     BFD_LAUNCHED();
     return BFD_OK;
@@ -846,20 +962,21 @@ extern "C" int bfd_fom_set_initial(const bfd_fom_desc *d, void *ws, const double
 
 static int launch_chunk(const FomArgs &a, cudaStream_t st) {
     const int grid = a.batch * a.ssl.nstrips;
-    if (a.uniform_y) {
-        BFD_LAUNCH_CORESIDENT(fom_chunk_kernel<true>, grid, 32 * (kWarpsPerStrip + 1), 0, st, a);
-    } else {
-        BFD_LAUNCH_CORESIDENT(fom_chunk_kernel<false>, grid, 32 * (kWarpsPerStrip + 1), 0, st, a);
-    }
+    const int block = 32 * (kWarpsPerStrip + 1);
+    void (*kernel)(const FomArgs) =
+        a.slab ? (a.uniform_y ? fom_chunk_kernel<true, true> : fom_chunk_kernel<false, true>)
+               : (a.uniform_y ? fom_chunk_kernel<true, false> : fom_chunk_kernel<false, false>);
+    BFD_LAUNCH_CORESIDENT(kernel, grid, block, 0, st, a);
     BFD_LAUNCHED();
     return BFD_OK;
 }
 
-extern "C" int bfd_fom_run(const bfd_fom_desc *d, void *ws, const bfd_fom_coef *coef, void *h_pinned,
-                           void *stream) {
-    if (check_desc(d) != BFD_OK || !ws || !coef || !h_pinned) return BFD_EINVAL;
-    const FomLayout L = fom_layout(d);
-    FomArgs a = fom_args(d, L, ws);
+static int fom_run_impl(const bfd_fom_desc *d, const SlabView &v, void *ws, const bfd_fom_coef *coef, void *h_pinned,
+                        void *stream) {
+    if (!ws || !coef || !h_pinned) return BFD_EINVAL;
+    if (v.slab && ((v.rank > 0 && !v.home) || (v.rank < v.world - 1 && !v.next_halo))) return BFD_EINVAL;
+    const FomLayout L = fom_layout(d, v);
+    FomArgs a = fom_args(d, L, ws, v);
     a.cx = coef->cx; a.cxl = coef->cxl; a.cy = coef->cy; a.cyd = coef->cyd;
     a.src = coef->src; a.lbc = coef->lbc;
     cudaStream_t st = (cudaStream_t)stream;
@@ -869,7 +986,8 @@ extern "C" int bfd_fom_run(const bfd_fom_desc *d, void *ws, const bfd_fom_coef *
 
     // Samples advance independently on the device; the host keeps two launches queued and looks
     // at the "samples finished" counter of the launch before them, so the GPU never idles on
-    // the poll.  A launch issued after everything finished exits at once.
+    // the poll.  A launch issued after everything finished exits at once.  (Slab runs: the
+    // counter is rank 0's; ranks may issue different numbers of trailing empty launches.)
     cudaEvent_t ev[2];
     BFD_CUDA(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming));
     BFD_CUDA(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
@@ -879,6 +997,7 @@ extern "C" int bfd_fom_run(const bfd_fom_desc *d, void *ws, const bfd_fom_coef *
     int rc = BFD_OK, pending = 0, slot = 0;
     bool finished = false;
     while (!finished && rc == BFD_OK) {
+        a.launch_index = (int)launched;
         rc = launch_chunk(a, st);
         ++launched;
         if (rc != BFD_OK) break;
@@ -911,37 +1030,122 @@ extern "C" int bfd_fom_run(const bfd_fom_desc *d, void *ws, const bfd_fom_coef *
     return rc;
 }
 
-extern "C" int bfd_fom_export(const bfd_fom_desc *d, const void *ws, int mu_index, int t0, int t1, int layout,
-                              size_t ld, double *out, void *stream) {
-    if (check_desc(d) != BFD_OK || !ws || !out) return BFD_EINVAL;
+static int fom_export_impl(const bfd_fom_desc *d, const SlabView &v, const void *ws, int mu_index, int t0, int t1,
+                           int layout, size_t ld, double *out, void *stream) {
+    if (!ws || !out) return BFD_EINVAL;
     if (mu_index < 0 || mu_index >= d->batch || t0 < 0 || t1 > d->num_steps + 1 || t0 >= t1) return BFD_EINVAL;
     if (layout != 0 && layout != 1) return BFD_EINVAL;
     if (layout == 1 && ld < (size_t)(t1 - t0)) return BFD_EINVAL;
-    const FomLayout L = fom_layout(d);
-    const FomArgs a = fom_args(d, L, const_cast<void *>(ws));
+    const FomLayout L = fom_layout(d, v);
+    const FomArgs a = fom_args(d, L, const_cast<void *>(ws), v);
     dim3 grid(d->ny + kSkew, L.ssl.nstrips), block(32, 8);
     BFD_LAUNCH(fom_export_kernel, grid, block, 0, (cudaStream_t)stream, a, mu_index, t0, t1, layout, ld, out);
     BFD_LAUNCHED();
     return BFD_OK;
 }
 
-extern "C" int bfd_fom_trace(const bfd_fom_desc *d, const void *ws, uint64_t *out, void *stream) {
-    if (check_desc(d) != BFD_OK || !ws || !out) return BFD_EINVAL;
-    const FomLayout L = fom_layout(d);
-    const FomArgs a = fom_args(d, L, const_cast<void *>(ws));
-    const size_t n = (size_t)d->batch * L.chunk * L.ssl.nstrips * 3;
-    BFD_CUDA(cudaMemcpyAsync(out, a.trace, n * sizeof(uint64_t), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
-    return BFD_OK;
-}
-
-extern "C" int bfd_fom_diagnostics(const bfd_fom_desc *d, const void *ws, int32_t *its, double *relnorm,
-                                   void *stream) {
-    if (check_desc(d) != BFD_OK || !ws) return BFD_EINVAL;
-    const FomLayout L = fom_layout(d);
-    const FomArgs a = fom_args(d, L, const_cast<void *>(ws));
+static int fom_diagnostics_impl(const bfd_fom_desc *d, const SlabView &v, const void *ws, int32_t *its,
+                                double *relnorm, void *stream) {
+    if (!ws) return BFD_EINVAL;
+    const FomLayout L = fom_layout(d, v);
+    const FomArgs a = fom_args(d, L, const_cast<void *>(ws), v);
     const size_t n = (size_t)d->batch * d->num_steps;
     if (its) BFD_CUDA(cudaMemcpyAsync(its, a.its, n * sizeof(int), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
     if (relnorm)
         BFD_CUDA(cudaMemcpyAsync(relnorm, a.relnorm, n * sizeof(double), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
     return BFD_OK;
+}
+
+// ---- whole grid on one GPU ----------------------------------------------------------------
+extern "C" size_t bfd_fom_workspace_bytes(const bfd_fom_desc *d) {
+    if (check_desc(d) != BFD_OK) return 0;
+    return fom_layout(d, whole_grid(d)).total;
+}
+
+extern "C" int bfd_fom_init(const bfd_fom_desc *d, void *ws, size_t ws_bytes, void *stream) {
+    if (check_desc(d) != BFD_OK) return BFD_EINVAL;
+    return fom_init_impl(d, whole_grid(d), ws, ws_bytes, stream);
+}
+
+extern "C" int bfd_fom_set_initial(const bfd_fom_desc *d, void *ws, const double *w0, size_t w0_stride,
+                                   void *stream) {
+    if (check_desc(d) != BFD_OK) return BFD_EINVAL;
+    return fom_set_initial_impl(d, whole_grid(d), ws, w0, w0_stride, stream);
+}
+
+extern "C" int bfd_fom_run(const bfd_fom_desc *d, void *ws, const bfd_fom_coef *coef, void *h_pinned,
+                           void *stream) {
+    if (check_desc(d) != BFD_OK) return BFD_EINVAL;
+    return fom_run_impl(d, whole_grid(d), ws, coef, h_pinned, stream);
+}
+
+extern "C" int bfd_fom_export(const bfd_fom_desc *d, const void *ws, int mu_index, int t0, int t1, int layout,
+                              size_t ld, double *out, void *stream) {
+    if (check_desc(d) != BFD_OK) return BFD_EINVAL;
+    return fom_export_impl(d, whole_grid(d), ws, mu_index, t0, t1, layout, ld, out, stream);
+}
+
+extern "C" int bfd_fom_diagnostics(const bfd_fom_desc *d, const void *ws, int32_t *its, double *relnorm,
+                                   void *stream) {
+    if (check_desc(d) != BFD_OK) return BFD_EINVAL;
+    return fom_diagnostics_impl(d, whole_grid(d), ws, its, relnorm, stream);
+}
+
+extern "C" int bfd_fom_trace(const bfd_fom_desc *d, const void *ws, uint64_t *out, void *stream) {
+    if (check_desc(d) != BFD_OK || !ws || !out) return BFD_EINVAL;
+    const SlabView v = whole_grid(d);
+    const FomLayout L = fom_layout(d, v);
+    const FomArgs a = fom_args(d, L, const_cast<void *>(ws), v);
+    const size_t n = (size_t)d->batch * L.chunk * L.ssl.nstrips * 3;
+    BFD_CUDA(cudaMemcpyAsync(out, a.trace, n * sizeof(uint64_t), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return BFD_OK;
+}
+
+// ---- one grid over several GPUs: this rank's slab ------------------------------------------
+extern "C" size_t bfd_fom_slab_workspace_bytes(const bfd_fom_desc *d, const bfd_fom_slab *sl) {
+    SlabView v;
+    if (slab_view(d, sl, &v) != BFD_OK) return 0;
+    return fom_layout(d, v).total;
+}
+
+extern "C" size_t bfd_fom_slab_halo_offset(const bfd_fom_desc *d, const bfd_fom_slab *sl) {
+    SlabView v;
+    if (slab_view(d, sl, &v) != BFD_OK || v.strip0 == 0) return 0;
+    return fom_layout(d, v).off_halo;
+}
+
+extern "C" int bfd_fom_slab_init(const bfd_fom_desc *d, const bfd_fom_slab *sl, void *ws, size_t ws_bytes,
+                                 void *stream) {
+    SlabView v;
+    if (slab_view(d, sl, &v) != BFD_OK) return BFD_EINVAL;
+    v.home = nullptr;          // a rank resets what it owns: records and ticket; rank 0 also the control blocks
+    return fom_init_impl(d, v, ws, ws_bytes, stream);
+}
+
+extern "C" int bfd_fom_slab_set_initial(const bfd_fom_desc *d, const bfd_fom_slab *sl, void *ws, const double *w0,
+                                        size_t w0_stride, void *stream) {
+    SlabView v;
+    if (slab_view(d, sl, &v) != BFD_OK) return BFD_EINVAL;
+    return fom_set_initial_impl(d, v, ws, w0, w0_stride, stream);
+}
+
+extern "C" int bfd_fom_slab_run(const bfd_fom_desc *d, const bfd_fom_slab *sl, void *ws, const bfd_fom_coef *coef,
+                                void *h_pinned, void *stream) {
+    SlabView v;
+    if (slab_view(d, sl, &v) != BFD_OK) return BFD_EINVAL;
+    return fom_run_impl(d, v, ws, coef, h_pinned, stream);
+}
+
+extern "C" int bfd_fom_slab_export(const bfd_fom_desc *d, const bfd_fom_slab *sl, const void *ws, int mu_index,
+                                   int t0, int t1, int layout, size_t ld, double *out, void *stream) {
+    SlabView v;
+    if (slab_view(d, sl, &v) != BFD_OK) return BFD_EINVAL;
+    return fom_export_impl(d, v, ws, mu_index, t0, t1, layout, ld, out, stream);
+}
+
+extern "C" int bfd_fom_slab_diagnostics(const bfd_fom_desc *d, const bfd_fom_slab *sl, const void *ws, int32_t *its,
+                                        double *relnorm, void *stream) {
+    SlabView v;
+    if (slab_view(d, sl, &v) != BFD_OK) return BFD_EINVAL;
+    return fom_diagnostics_impl(d, v, ws, its, relnorm, stream);
 }

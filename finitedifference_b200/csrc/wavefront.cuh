@@ -20,6 +20,13 @@ __device__ __forceinline__ void st_volatile2(double *p, double a, double b) {
 __device__ __forceinline__ void st_weak2(double *p, double a, double b) {
     asm volatile("st.global.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(a), "d"(b) : "memory");
 }
+// system scope: records that cross NVLink into (or are polled from under) a peer GPU's writes
+__device__ __forceinline__ void ld_sys2(const double *p, double &a, double &b) {
+    asm volatile("ld.relaxed.sys.global.v2.f64 {%0, %1}, [%2];" : "=d"(a), "=d"(b) : "l"(p) : "memory");
+}
+__device__ __forceinline__ void st_sys2(double *p, double a, double b) {
+    asm volatile("st.relaxed.sys.global.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(a), "d"(b) : "memory");
+}
 // Shared memory is addressed by 32-bit shared-window byte addresses computed once per kernel,
 // so the hot loop never re-derives a generic pointer (S2R + LEA per access otherwise).
 typedef unsigned saddr;
@@ -87,6 +94,8 @@ inline int lane_id() { return emu::tls.lane; }
 inline void cp_async16(saddr dst, const double *src) { ld_volatile2(src, ((double *)dst)[0], ((double *)dst)[1]); }
 inline void cp_async8(saddr dst, const double *src) { *(double *)dst = *src; }
 inline void st_weak2(double *p, double a, double b) { st_volatile2(p, a, b); }
+inline void ld_sys2(const double *p, double &a, double &b) { ld_volatile2(p, a, b); }
+inline void st_sys2(double *p, double a, double b) { st_volatile2(p, a, b); }
 inline void cp_async_commit() {}
 template <int N> inline void cp_async_wait_pending() {}
 inline double rcp_fast(double x) { return 1.0 / x; }
@@ -149,11 +158,11 @@ struct EdgeIn {
     double *g;       // records written by the strip on the left, [ny][kRecDoubles]
     saddr ring;      // [kInRing][kRecDoubles] shared memory of this CTA
     int ny, lane;
-    bool active, dead;
+    bool active, dead, remote;      // remote: the producer is a strip on another GPU (slab runs)
     unsigned spins_total, misses;   // statistics for bfd_fom_trace
 
-    __device__ __forceinline__ void init(double *g_, saddr ring_, int ny_, int lane_, bool active_) {
-        g = g_; ring = ring_; ny = ny_; lane = lane_; active = active_; dead = false;
+    __device__ __forceinline__ void init(double *g_, saddr ring_, int ny_, int lane_, bool active_, bool remote_ = false) {
+        g = g_; ring = ring_; ny = ny_; lane = lane_; active = active_; dead = false; remote = remote_;
         spins_total = 0; misses = 0;
         map.init(lane);
         if (active) prefetch(0);
@@ -195,7 +204,8 @@ struct EdgeIn {
 #pragma unroll
                 for (int it = 0; it < kIters; ++it) {
                     if (mine[it] && (is_sentinel(p0[it]) || is_sentinel(p1[it]))) {
-                        ld_volatile2(gb + map.goff[it], p0[it], p1[it]);
+                        if (remote) ld_sys2(gb + map.goff[it], p0[it], p1[it]);
+                        else ld_volatile2(gb + map.goff[it], p0[it], p1[it]);
                         ok = ok && !(is_sentinel(p0[it]) || is_sentinel(p1[it]));
                     }
                 }
@@ -234,10 +244,10 @@ struct EdgeOut {
     double *g;      // records of this strip, [ny][kRecDoubles]
     saddr ring;     // [kOutRing][kRecDoubles]
     int ny, lane;
-    bool active;
+    bool active, remote;   // remote: the records live in the next GPU's memory (slab runs)
 
-    __device__ __forceinline__ void init(double *g_, saddr ring_, int ny_, int lane_, bool active_) {
-        g = g_; ring = ring_; ny = ny_; lane = lane_; active = active_;
+    __device__ __forceinline__ void init(double *g_, saddr ring_, int ny_, int lane_, bool active_, bool remote_ = false) {
+        g = g_; ring = ring_; ny = ny_; lane = lane_; active = active_; remote = remote_;
         map.init(lane);
     }
     // Whole warp, every step, with the row whose LAST level has been filed in the ring.
@@ -252,7 +262,8 @@ struct EdgeOut {
             if (row0 + map.row[it] < ny && map.row[it] < kEdgeBlock) {
                 double x, y;
                 lds2(sb + (saddr)map.soff[it], x, y);
-                st_volatile2(gb + map.goff[it], x, y);
+                if (remote) st_sys2(gb + map.goff[it], x, y);
+                else st_volatile2(gb + map.goff[it], x, y);
             }
         }
     }

@@ -122,6 +122,53 @@ int bfd_residual(int nx, int ny, const double *cx, const double *cxl, const doub
                  const double *wp, double *r, double *norm2, void *stream);
 
 /* ------------------------------------------------------------------------------------------
+ * One grid over several GPUs: slab decomposition along x (second row).
+ *
+ * The grid's 32-column strips are dealt to the ranks in contiguous blocks; each rank (one process
+ * per GPU) holds only its strips' snapshots.  Upwinding makes the coupling one-directional: the
+ * last strip of rank g hands its right-edge records (the same self-validating records strips on
+ * one GPU exchange) straight into the halo buffer of rank g+1 with peer stores over NVLink,
+ * tile by tile inside the running kernel -- there is no separate exchange step and no
+ * collective.  The per-sample control blocks, residual norms and verdicts of a slab run live in
+ * rank 0's workspace ("home"); every rank updates them with system-scope atomics.
+ *
+ * `d` describes the GLOBAL problem.  Arrays passed to the slab entry points are LOCAL to the
+ * slab: coef->cx, cxl [nx_local], coef->src [batch][nx_local], w0 / exported snapshots in the
+ * natural layout of a (ny x nx_local) grid; coef->cy, cyd, lbc are per row and global.
+ * `home` and `next_halo` are addresses valid in THIS process: cudaIpc mappings of the other
+ * ranks' workspaces (bfd_ipc_*), or plain pointers when the slabs live in one process.
+ * Call order on every rank: _init; (all ranks: stream sync + barrier); _set_initial; _run.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct bfd_fom_slab {
+    int32_t rank, world;             /* this slab and the number of slabs */
+    int32_t strip_begin, strip_end;  /* strips [begin, end) of the global grid held here */
+    void *home;                      /* rank 0's workspace (NULL or own workspace on rank 0) */
+    void *next_halo;                 /* rank+1's workspace + bfd_fom_slab_halo_offset(rank+1); NULL on the last rank */
+} bfd_fom_slab;
+
+size_t bfd_fom_slab_workspace_bytes(const bfd_fom_desc *d, const bfd_fom_slab *slab);
+size_t bfd_fom_slab_halo_offset(const bfd_fom_desc *d, const bfd_fom_slab *slab);
+int bfd_fom_slab_init(const bfd_fom_desc *d, const bfd_fom_slab *slab, void *workspace, size_t workspace_bytes,
+                      void *stream);
+int bfd_fom_slab_set_initial(const bfd_fom_desc *d, const bfd_fom_slab *slab, void *workspace, const double *w0,
+                             size_t w0_stride, void *stream);
+int bfd_fom_slab_run(const bfd_fom_desc *d, const bfd_fom_slab *slab, void *workspace, const bfd_fom_coef *coef,
+                     void *h_pinned, void *stream);
+int bfd_fom_slab_export(const bfd_fom_desc *d, const bfd_fom_slab *slab, const void *workspace, int mu_index,
+                        int t0, int t1, int layout, size_t ld, double *out, void *stream);
+int bfd_fom_slab_diagnostics(const bfd_fom_desc *d, const bfd_fom_slab *slab, const void *workspace, int32_t *its,
+                             double *relnorm, void *stream);
+
+/* Device memory that can be mapped into another process on the same node (cudaMalloc +
+ * cudaIpcGetMemHandle / OpenMemHandle; peer access is enabled by the mapping). */
+#define BFD_IPC_HANDLE_BYTES 64
+int bfd_mem_alloc(size_t bytes, void **ptr);
+int bfd_mem_free(void *ptr);
+int bfd_ipc_export(void *ptr, unsigned char handle[BFD_IPC_HANDLE_BYTES]);
+int bfd_ipc_open(const unsigned char handle[BFD_IPC_HANDLE_BYTES], void **ptr);
+int bfd_ipc_close(void *ptr);
+
+/* ------------------------------------------------------------------------------------------
  * Reduced-order models (LSPG PROM on the whole grid, ECSW/ECM HPROM on the sampled mesh).
  *
  * A "mesh" is a list of rows (cells whose residual is evaluated) with, per row, the state cells

@@ -171,6 +171,7 @@ static inline bool __all_sync(unsigned, bool p) {
 static inline void __syncwarp(unsigned = 0xffffffffu) { emu::tls.warp->bar.wait(); }
 static inline void __syncthreads() { emu::tls.cta->bar.wait(); }
 static inline void __threadfence() { std::atomic_thread_fence(std::memory_order_seq_cst); }
+static inline void __threadfence_system() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 static inline void __threadfence_block() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 
 template <class T> static inline T __ldg(const T *p) { return *p; }
