@@ -30,6 +30,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=1)
     ap.add_argument("--check", type=int, default=1024, help="grid size of the parity pre-check (0 = skip)")
     ap.add_argument("--chunk-steps", type=int, default=0)
+    ap.add_argument("--dx", type=float, default=100.0 / 750.0, help="cell size (the fine configuration's)")
     a = ap.parse_args()
 
     import torch
@@ -49,7 +50,9 @@ def main():
     mu, dt = [4.75, 0.02], 0.05
 
     def make(n, T):
-        gx, gy = make_2D_grid(0, 100, 0, 100, n, n)
+        # same cell size as the fine configuration (100/750): at dx = 100/8192 and dt = 0.05 the
+        # reference's Newton iteration itself diverges (oracle), so the domain grows
+        gx, gy = make_2D_grid(0, n * a.dx, 0, n * a.dx, n, n)
         s = FomSlab(gx, gy, dt, T, [mu], rank, world, device=dev, chunk_steps=a.chunk_steps)
         if world > 1:
             connect_distributed(s)
@@ -112,7 +115,7 @@ def main():
             "metric": "fom_cell_updates_per_s", "value": cells * T / (ms * 1e-3), "unit": "cell-updates/s",
             "n_gpus": world, "scaling": "strong", "ms_per_trajectory": ms, "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"single-mu FOM, {n}x{n} grid, {T} steps, slab decomposition over {world} GPU(s)",
-                       "grid": n, "num_steps": T, "strips_rank0": list(s.strips), "columns_rank0": [s.c0, s.c1]},
+                       "grid": n, "num_steps": T, "dx": a.dx, "strips_rank0": list(s.strips), "columns_rank0": [s.c0, s.c1]},
             "newton_its_mean": float(its.mean()), "max_relnorm": float(rel.max()), "steps_redone": s.steps_redone,
             "launches_rank0": int(launches), "check": check,
             "halo_bytes_per_trajectory": int((world - 1) * T * n * (2 * float(its.mean()) + 1) * 16)}), flush=True)
