@@ -230,7 +230,8 @@ constexpr int kPairRow = 32 * 16;              // one pair for each lane
 constexpr int kHandBytes = 2 * 3 * kPairRow;   // level hand-off between two warps: [2 buffers][(xu,xv),(Au,Av),(cy,cyd)][lane]
 constexpr int kHandIfaces = kWarpsPerStrip > 1 ? kWarpsPerStrip - 1 : 1;
 constexpr int kXchgLevels = kKMax + 2;         // levels 0..K, plus (Fp, Gp) of continuation passes
-constexpr int kXchgBytes = kXchgLevels * 2 * 2 * kPairRow;   // left-neighbour exchange: [level][2 buffers][(Fh,Gh),(pu,pm)][lane]
+constexpr int kXRow = 33 * 16;                  // exchange row: slot 0 = halo (last column of the strip on the left), slot l+1 = lane l
+constexpr int kXchgBytes = kXchgLevels * 2 * 2 * kXRow;      // left-neighbour exchange: [level][2 buffers][(Fh,Gh),(pu,pm)][slot]
 constexpr int kPfDepth = 6;                    // rows of level-0 input in flight (cp.async ring)
 constexpr int kPfValues = 7;                   // u, v, up, vp (CONT), lbc (inlet lane), cy, cyd (non-uniform grids)
 constexpr int kPfBytes = kPfDepth * kPfValues * 32 * 8;
@@ -244,7 +245,7 @@ struct StepIo {
     double *xout;         // slot t+1 (all three already offset to this strip and lane)
     double *edge_in;      // hand-off records of the strip on the left for this time step
     double *edge_out;     // ... and the ones this strip produces
-    saddr ring_in, ring_out;   // shared memory of this CTA (shared-window addresses)
+    saddr ring_in;        // staging ring of the left strip's records (shared-window address)
     saddr hand;           // level hand-off written by this warp (the previous warp's is kHandBytes below)
     saddr pf;             // prefetch ring of the level-0 input [kPfDepth][kPfValues][32]
     saddr xchg;           // left-neighbour exchange
@@ -291,8 +292,6 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
     const int last_row = ny + kSkew - 1;   // last slot-row holding cells
     const int nsteps = ny + kSkew + K;
 
-    const bool from_edge = (lane == 0) && io.strip > 0;
-    const bool to_edge = (lane == 31) && io.strip < io.nstrips - 1;
     const bool colok = io.colok;
 
     const double cx = io.cx, cxl = io.cxl, hcx = 0.5 * io.cx, hcxl = 0.5 * io.cxl, ncxl = -io.cxl;
@@ -303,8 +302,6 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
     // level-0 input: rows land in the shared-memory ring one step ahead (dma_part)
     const saddr pf_lane = io.pf + (saddr)(lane * 8);
     auto pf_slot = [&](int row) { return pf_lane + (saddr)((row % kPfDepth) * (kPfValues * 256)); };
-    auto in_slot = [&](int row, int piece) { return io.ring_in + (saddr)((row % kInRing) * kRecBytes + piece * 16); };
-    auto out_slot = [&](int row, int piece) { return io.ring_out + (saddr)((row % kOutRing) * kRecBytes + piece * 16); };
 
     Level prev[K + 1];        // own cell of the previous step at each level = upper neighbour now
     double qGp = 0.0, qHp = 0.0;   // previous-snapshot flux parts of the previous row (CONT)
@@ -317,9 +314,9 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
     for (int k = 0; k <= K; ++k) nrm[k] = 0.0;
     const saddr hand_in = io.hand - (saddr)kHandBytes + (saddr)(lane * 16);   // written by the previous warp
     const saddr hand_out = io.hand + (saddr)(lane * 16);
-    const saddr xc_own = io.xchg + (saddr)(lane * 16);                         // this lane's pairs
-    const saddr xc_left = io.xchg + (saddr)((lane > 0 ? lane - 1 : 0) * 16);  // the left lane's
-    auto xc_level = [](int k, int buf) { return (saddr)((k * 2 + buf) * 2 * kPairRow); };
+    const saddr xc_own = io.xchg + (saddr)((lane + 1) * 16);   // this lane's pairs (slot lane + 1)
+    const saddr xc_left = io.xchg + (saddr)(lane * 16);        // the left column's: lane - 1, or the halo slot for lane 0
+    auto xc_level = [](int k, int buf) { return (saddr)((k * 2 + buf) * 2 * kXRow); };
 
     // One wavefront step.  EP ("edge phase"): some lane's row is outside the grid at some level
     // (first 32+K and last 31+K steps); the main phase runs without row masks.
@@ -351,15 +348,13 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
             const bool top = EP ? (rk <= 0) : false;   // no upper neighbour (row -1 is not a cell)
             const double cy = UNI ? cyU : Cy[k], cyd = UNI ? cydU : Cyd[k];
             const double hcy = 0.5 * cy, hcyd = 0.5 * cyd, ncyd = -cyd;
-            const bool put = to_edge && rowok;
-            const int rrow = rowok ? rk : 0;           // row for record addresses (lanes 0 and 31)
 
-            // left neighbour (r, c-1): lane-1's pairs of the previous step, or the record
-            const bool take = from_edge && rowok;
-            const saddr la = take ? in_slot(rrow, 2 * k) : xc_left + xc_level(k, rbuf);
+            // left neighbour (r, c-1): the pairs slot `lane` received in the previous step -- from
+            // lane - 1, or (lane 0) from the strip on the left through the data-movement warp
+            const saddr la = xc_left + xc_level(k, rbuf);
             double LF, LG, Lpu = 0.0, Lpm = 0.0;
             lds2(la, LF, LG);
-            if (k < K) lds2(la + (take ? 16 : kPairRow), Lpu, Lpm);
+            if (k < K) lds2(la + kXRow, Lpu, Lpm);
 
             if (k == 0) {
                 // previous-snapshot parts and the level-independent terms Au, Av
@@ -369,8 +364,7 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
                 if (EP) { DGp = top ? 0.0 : DGp; DHp = top ? 0.0 : DHp; }
                 double lFp = LF, lGp = LG;
                 if (CONT) {
-                    const saddr lp = take ? in_slot(rrow, 2 * K + 1) : xc_left + xc_level(K + 1, rbuf);
-                    lds2(lp, lFp, lGp);
+                    lds2(xc_left + xc_level(K + 1, rbuf), lFp, lGp);
                 }
                 double au = fma(cx, Fp, -up);
                 au = fma(cy, Gp, au); au = fma(ncxl, lFp, au); au = fma(ncyd, DGp, au);
@@ -381,7 +375,6 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
                 if (CONT) {
                     qGp = Gp; qHp = Hp;
                     sts2(xc_own + xc_level(K + 1, wbuf), Fp, Gp);
-                    if (put) sts2(out_slot(rrow, 2 * K + 1), Fp, Gp);
                 }
             }
 
@@ -397,7 +390,6 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
             const double r2 = fma(rv, rv, ru * ru);
             nrm[k] += valid ? r2 : 0.0;
             sts2(xc_own + xc_level(k, wbuf), Fh, Gh);
-            if (put) sts2(out_slot(rrow, 2 * k), Fh, Gh);
             prev[k].Gh = Gh; prev[k].Hh = Hh;
 
             if (k < K) {
@@ -413,8 +405,7 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
                 const double dv = fma(d00, bv_, -(d10 * bu_)) * inv;
                 const double pu = u * du, pm = fma(v, du, u * dv);
                 prev[k].pm = pm; prev[k].pvv = v * dv;
-                sts2(xc_own + xc_level(k, wbuf) + kPairRow, pu, pm);
-                if (put) sts2(out_slot(rrow, 2 * k + 1), pu, pm);
+                sts2(xc_own + xc_level(k, wbuf) + kXRow, pu, pm);
                 xu[k + 1] = u - du; xv[k + 1] = v - dv;
                 Au[k + 1] = Au[k]; Av[k + 1] = Av[k];
                 if (!UNI) { Cy[k + 1] = Cy[k]; Cyd[k + 1] = Cyd[k]; }
@@ -470,8 +461,12 @@ __device__ __forceinline__ void idle_part(const StepIo &io) {
 
 // The data-movement warp of the CTA: keeps the level-0 input ring kPfDepth-1 rows ahead with
 // cp.async, brings the hand-off blocks of the strip on the left into the shared-memory ring
-// one step before the compute warps need them (spinning there, off their critical path, if the
-// producer is late), and flushes finished blocks of this strip's records to global memory.
+// ahead of time (spinning there, off the compute warps' critical path, if the producer is late),
+// and every step
+//   - drops the pairs lane 0 needs in the NEXT step into the halo slot of the exchange rows, so
+//     that the compute warps treat all 32 lanes alike (no address select, no branch), and
+//   - sends what lane 31 published in the PREVIOUS step to the strip on the right: one 16-byte
+//     piece per lane straight to the records in global (or peer) memory.
 // It meets the compute warps at the same per-step barrier.
 template <int K, bool CONT, bool UNI>
 __device__ __forceinline__ void dma_part(const StepIo &io) {
@@ -481,9 +476,36 @@ __device__ __forceinline__ void dma_part(const StepIo &io) {
     const int last_row = ny + kSkew - 1;
     const int nsteps = ny + kSkew + K;
     EdgeIn<NPR> ein;
-    EdgeOut<NPR> eout;
     ein.init(io.edge_in, io.ring_in, ny, lane, io.strip > 0, io.in_remote);
-    eout.init(io.edge_out, io.ring_out, ny, lane, io.strip < io.nstrips - 1, io.out_remote);
+    // this lane's piece of a row record: level and pair inside the exchange rows, and the level
+    // whose row it travels with (the previous-time-level pair of continuation passes goes with level 0)
+    const bool has_piece = lane < NPR;
+    const int p_lvl = (CONT && lane == 2 * K + 1) ? K + 1 : (lane >> 1);
+    const int p_row = (CONT && lane == 2 * K + 1) ? 0 : (lane >> 1);
+    const bool take = has_piece && io.strip > 0, give = has_piece && io.strip < io.nstrips - 1;
+    const saddr p_x = io.xchg + (saddr)(p_lvl * 4 * kXRow + ((CONT && lane == 2 * K + 1) ? 0 : (lane & 1)) * kXRow);
+    const saddr p_ring = io.ring_in + (saddr)(lane * 16);
+    double *p_out = io.edge_out + 2 * lane;
+    const bool out_remote = io.out_remote;
+    // halo slot of exchange buffer (step & 1) <- what lane 0 reads in step `step + 1`
+    auto halo_in = [&](int step) {
+        const int row = step + 1 - p_row;
+        if (take && (unsigned)row < (unsigned)ny) {
+            double a, b;
+            lds2(p_ring + (saddr)((row & (kInRing - 1)) * kRecBytes), a, b);
+            sts2(p_x + (saddr)((step & 1) * 2 * kXRow), a, b);
+        }
+    };
+    // records <- what lane 31 (slot 32) published in step `step`
+    auto halo_out = [&](int step) {
+        const int row = step - kSkew - p_row;
+        if (give && (unsigned)row < (unsigned)ny) {
+            double a, b;
+            lds2(p_x + (saddr)((step & 1) * 2 * kXRow + 32 * 16), a, b);
+            double *g = p_out + (size_t)row * kRecDoubles;
+            if (out_remote) st_sys2(g, a, b); else st_volatile2(g, a, b);
+        }
+    };
     const saddr pf_lane = io.pf + (saddr)(lane * 8);
     auto pf_issue = [&](int row) {
         const int r = row < last_row ? row : last_row;
@@ -502,16 +524,18 @@ __device__ __forceinline__ void dma_part(const StepIo &io) {
     for (int i = 0; i < kPfDepth - 1; ++i) { pf_issue(i); cp_async_commit(); }
     cp_async_wait_pending<kPfDepth - 2>();
     int err = ein.open(0);
+    halo_in(-1);
     __syncthreads();
     for (int s = 0; s < nsteps; ++s) {
         pf_issue(s + kPfDepth - 1);          // refills the slot read one step ago
         cp_async_commit();
         cp_async_wait_pending<kPfDepth - 2>();   // row s+1 has landed
         err |= ein.open(s + 1);              // block starting at row s+1, if that opens one
-        eout.close(s - 1 - kSkew - K);       // row whose last level finished in the previous step
+        halo_in(s);
+        if (s > 0) halo_out(s - 1);
         __syncthreads();
     }
-    eout.close(nsteps - 1 - kSkew - K);
+    halo_out(nsteps - 1);
     if (lane == 0) {
         if (err) atomicExch(io.error, err);
         if (io.stats) *io.stats = ((unsigned long long)ein.misses << 32) | ein.spins_total;
@@ -676,7 +700,7 @@ template <bool SLAB> __device__ __forceinline__ unsigned a_add(unsigned *p, unsi
 
 template <bool UNI, bool SLAB>
 __global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk_kernel(const FomArgs a) {
-    constexpr int kSmemDoubles = (kInRing + kOutRing) * kRecDoubles + (kHandIfaces * kHandBytes + kXchgBytes + kPfBytes) / 8;
+    constexpr int kSmemDoubles = kInRing * kRecDoubles + (kHandIfaces * kHandBytes + kXchgBytes + kPfBytes) / 8;
     BFD_SHARED_ARRAY(double, s_mem, [kSmemDoubles]);
     BFD_SHARED_ARRAY(int, s_ctl, [8]);
     BFD_SHARED_ARRAY(double, s_dbl, [2]);
@@ -712,8 +736,7 @@ __global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk
 
     StepIo io;
     io.ring_in = smem_addr(s_mem);
-    io.ring_out = io.ring_in + (saddr)(kInRing * kRecBytes);
-    const saddr hand0 = io.ring_out + (saddr)(kOutRing * kRecBytes);
+    const saddr hand0 = io.ring_in + (saddr)(kInRing * kRecBytes);
     io.hand = hand0 + (saddr)(warp * kHandBytes);
     io.xchg = hand0 + (saddr)(kHandIfaces * kHandBytes);
     io.pf = io.xchg + (saddr)kXchgBytes;

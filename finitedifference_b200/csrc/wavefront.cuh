@@ -115,8 +115,8 @@ __device__ __forceinline__ double sentinel_value() { return __longlong_as_double
 //     piece 2k   = (Fh_k, Gh_k)      current-iterate flux parts of level k  (k = 0..K)
 //     piece 2k+1 = (pu_k, pm_k)      u*du and v*du + u*dv of level k        (k < K)
 //     piece 2K+1 = (Fp, Gp)          previous-time-level flux parts (continuation passes only)
-// Rows travel in blocks of kEdgeBlock: the producer collects them in shared memory and the
-// warp flushes a block with coalesced 16-byte volatile stores; the consumer warp copies a block
+// The producer's data-movement warp stores each piece the step after it was computed (one
+// 16-byte relaxed store per lane); the consumer's copies a block of kEdgeBlock rows
 // into its shared-memory ring one block ahead (cp.async, in the caller's per-step commit
 // groups: the caller waits for the group before open()), checks it when the block opens and
 // spins on whatever had not arrived.  No flags, no fences: a piece is valid once neither of its
@@ -127,7 +127,6 @@ constexpr int kEdgeBlock = 8;
 constexpr int kPiecesMax = 2 * BFD_FOM_KMAX + 2;   // pieces per row in global memory (fixed pitch)
 constexpr int kRecDoubles = 2 * kPiecesMax;        // doubles per row record
 constexpr int kInRing = 32;                        // rows in the consumer's ring (4 blocks)
-constexpr int kOutRing = 16;                       // rows in the producer's ring (2 blocks)
 constexpr unsigned kSpinLimit = 1u << 22;
 
 constexpr int kRecBytes = kRecDoubles * 8;
@@ -234,38 +233,6 @@ struct EdgeIn {
         if (!dead && s + kEdgeBlock < ny) prefetch(s + kEdgeBlock);
 #endif
         return err;
-    }
-};
-
-template <int NPR>
-struct EdgeOut {
-    static constexpr int kIters = BlockMap<NPR>::kIters;
-    BlockMap<NPR> map;
-    double *g;      // records of this strip, [ny][kRecDoubles]
-    saddr ring;     // [kOutRing][kRecDoubles]
-    int ny, lane;
-    bool active, remote;   // remote: the records live in the next GPU's memory (slab runs)
-
-    __device__ __forceinline__ void init(double *g_, saddr ring_, int ny_, int lane_, bool active_, bool remote_ = false) {
-        g = g_; ring = ring_; ny = ny_; lane = lane_; active = active_; remote = remote_;
-        map.init(lane);
-    }
-    // Whole warp, every step, with the row whose LAST level has been filed in the ring.
-    __device__ __forceinline__ void close(int r_done) {
-        if (!active || r_done < 0 || r_done >= ny) return;
-        if ((r_done % kEdgeBlock) != kEdgeBlock - 1 && r_done != ny - 1) return;
-        const int row0 = r_done - (r_done % kEdgeBlock);
-        double *gb = g + (size_t)row0 * kRecDoubles;
-        const saddr sb = ring + (saddr)((row0 % kOutRing) * kRecBytes);
-#pragma unroll
-        for (int it = 0; it < kIters; ++it) {
-            if (row0 + map.row[it] < ny && map.row[it] < kEdgeBlock) {
-                double x, y;
-                lds2(sb + (saddr)map.soff[it], x, y);
-                if (remote) st_sys2(gb + map.goff[it], x, y);
-                else st_volatile2(gb + map.goff[it], x, y);
-            }
-        }
     }
 };
 
