@@ -301,7 +301,8 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
 
     // level-0 input: rows land in the shared-memory ring one step ahead (dma_part)
     const saddr pf_lane = io.pf + (saddr)(lane * 8);
-    auto pf_slot = [&](int row) { return pf_lane + (saddr)((row % kPfDepth) * (kPfValues * 256)); };
+    const saddr pf_end = pf_lane + (saddr)(kPfDepth * kPfValues * 256);
+    saddr pf_rd = pf_lane;                  // slot of the row read this step (running, no modulo)
 
     Level prev[K + 1];        // own cell of the previous step at each level = upper neighbour now
     double qGp = 0.0, qHp = 0.0;   // previous-snapshot flux parts of the previous row (CONT)
@@ -325,7 +326,9 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
         const int rbuf = (s + 1) & 1, wbuf = s & 1;      // exchange buffers: written last step / this step
         double up = 0.0, vp = 0.0, lb = 0.0;
         if (FIRST) {
-            const saddr d = pf_slot(s);
+            const saddr d = pf_rd;
+            pf_rd += (saddr)(kPfValues * 256);
+            if (pf_rd == pf_end) pf_rd = pf_lane;
             xu[0] = lds(d); xv[0] = lds(d + 256);
             up = CONT ? lds(d + 512) : xu[0]; vp = CONT ? lds(d + 768) : xv[0];
             if (io.inlet) lb = lds(d + 1024);
@@ -434,11 +437,20 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
     };
 
     __syncthreads();      // row 0 and the first hand-off block are in shared memory (dma_part)
-    int s = 0;
+    // head (rows entering the strip), main (0 < row < ny for every lane and level), tail; the
+    // two edge phases share one copy of the masked body (code size: instruction cache)
     const int head_end = nsteps < kSkew + K + 1 ? nsteps : kSkew + K + 1;
-    for (; s < head_end; ++s) body(s, BoolTag<true>{});
-    for (; s < ny; ++s) body(s, BoolTag<false>{});     // 0 < row < ny for every lane and level
-    for (; s < nsteps; ++s) body(s, BoolTag<true>{});
+    const int main_end = ny > head_end ? ny : head_end;
+    int s = 0;
+#pragma unroll 1
+    for (int phase = 0; phase < 2; ++phase) {
+        const int ep_end = phase == 0 ? head_end : nsteps;
+#pragma unroll 1
+        for (; s < ep_end; ++s) body(s, BoolTag<true>{});
+        if (phase == 0) {
+            for (; s < main_end; ++s) body(s, BoolTag<false>{});
+        }
+    }
 
     // ||r(x_k)||^2 of this strip, fixed reduction order (deterministic iteration counts)
 #pragma unroll
@@ -472,70 +484,105 @@ template <int K, bool CONT, bool UNI>
 __device__ __forceinline__ void dma_part(const StepIo &io) {
     constexpr int NPR = 2 * K + 1 + (CONT ? 1 : 0);
     constexpr int W = 32;
+    constexpr int kNever = -(1 << 30);     // row offset of a lane with nothing to move: never in [0, ny)
     const int lane = io.lane, ny = io.ny;
     const int last_row = ny + kSkew - 1;
     const int nsteps = ny + kSkew + K;
     EdgeIn<NPR> ein;
     ein.init(io.edge_in, io.ring_in, ny, lane, io.strip > 0, io.in_remote);
-    // this lane's piece of a row record: level and pair inside the exchange rows, and the level
-    // whose row it travels with (the previous-time-level pair of continuation passes goes with level 0)
-    const bool has_piece = lane < NPR;
-    const int p_lvl = (CONT && lane == 2 * K + 1) ? K + 1 : (lane >> 1);
-    const int p_row = (CONT && lane == 2 * K + 1) ? 0 : (lane >> 1);
-    const bool take = has_piece && io.strip > 0, give = has_piece && io.strip < io.nstrips - 1;
-    const saddr p_x = io.xchg + (saddr)(p_lvl * 4 * kXRow + ((CONT && lane == 2 * K + 1) ? 0 : (lane & 1)) * kXRow);
+
+    // This lane's piece of a row record: where it sits in the exchange rows, and the row it
+    // belongs to at step s (the previous-time-level pair of continuation passes travels with level 0).
+    const bool special = CONT && lane == 2 * K + 1;
+    const int p_row = special ? 0 : (lane >> 1);
+    const bool take = lane < NPR && io.strip > 0, give = lane < NPR && io.strip < io.nstrips - 1;
+    const int c_in = take ? 1 - p_row : kNever;              // lane 0 of the compute warps reads row s + 1 - level in step s + 1
+    const int c_out = give ? -1 - kSkew - p_row : kNever;    // lane 31 published row s - 1 - 31 - level in step s - 1
+    const saddr p_x = io.xchg + (saddr)((special ? K + 1 : (lane >> 1)) * 4 * kXRow + (special ? 0 : (lane & 1)) * kXRow);
     const saddr p_ring = io.ring_in + (saddr)(lane * 16);
     double *p_out = io.edge_out + 2 * lane;
     const bool out_remote = io.out_remote;
-    // halo slot of exchange buffer (step & 1) <- what lane 0 reads in step `step + 1`
-    auto halo_in = [&](int step) {
-        const int row = step + 1 - p_row;
-        if (take && (unsigned)row < (unsigned)ny) {
+    const saddr x_sum = 2 * p_x + (saddr)(2 * kXRow);        // the two exchange buffers alternate: next = x_sum - current
+    saddr x_cur = p_x + (saddr)(2 * kXRow);                  // buffer of step -1 (odd)
+    saddr x_prev = p_x;
+    // halo slot of the exchange buffer written in step s <- what lane 0 reads in step s + 1;
+    // records <- what lane 31 (slot 32) published in step s - 1
+    auto halo = [&](int s) {
+        const int rin = s + c_in, rout = s + c_out;
+        if ((unsigned)rin < (unsigned)ny) {
             double a, b;
-            lds2(p_ring + (saddr)((row & (kInRing - 1)) * kRecBytes), a, b);
-            sts2(p_x + (saddr)((step & 1) * 2 * kXRow), a, b);
+            lds2(p_ring + (saddr)((rin & (kInRing - 1)) * kRecBytes), a, b);
+            sts2(x_cur, a, b);
         }
-    };
-    // records <- what lane 31 (slot 32) published in step `step`
-    auto halo_out = [&](int step) {
-        const int row = step - kSkew - p_row;
-        if (give && (unsigned)row < (unsigned)ny) {
+        if ((unsigned)rout < (unsigned)ny) {
             double a, b;
-            lds2(p_x + (saddr)((step & 1) * 2 * kXRow + 32 * 16), a, b);
-            double *g = p_out + (size_t)row * kRecDoubles;
+            lds2(x_prev + 32 * 16, a, b);
+            double *g = p_out + (size_t)rout * kRecDoubles;
             if (out_remote) st_sys2(g, a, b); else st_volatile2(g, a, b);
         }
+        x_prev = x_cur;
+        x_cur = x_sum - x_cur;
     };
+
+    // level-0 input ring: one row per step, kPfDepth - 1 rows ahead; running addresses, no modulo
     const saddr pf_lane = io.pf + (saddr)(lane * 8);
-    auto pf_issue = [&](int row) {
-        const int r = row < last_row ? row : last_row;
-        const size_t o = (size_t)r * (2 * W);
-        const saddr d = pf_lane + (saddr)((row % kPfDepth) * (kPfValues * 256));
-        cp_async8(d, io.xin + o);
-        cp_async8(d + 256, io.xin + o + W);
-        if (CONT) { cp_async8(d + 512, io.xwp + o); cp_async8(d + 768, io.xwp + o + W); }
-        const int rc = r - lane < 0 ? 0 : (r - lane >= ny ? ny - 1 : r - lane);   // grid row of this lane's cell
-        if (io.inlet) cp_async8(d + 1024, io.lbc + rc);
-        if (!UNI) { cp_async8(d + 1280, io.cy + rc); cp_async8(d + 1536, io.cyd + rc); }
+    const saddr pf_end = pf_lane + (saddr)(kPfDepth * kPfValues * 256);
+    saddr pf_d = pf_lane;
+    const double *src = io.xin, *srcp = io.xwp, *lbc_p = io.lbc;
+    int pf_row = 0;
+    const bool strip0 = io.strip == 0;
+    auto pf_issue = [&]() {
+        cp_async8(pf_d, src);
+        cp_async8(pf_d + 256, src + W);
+        if (CONT) { cp_async8(pf_d + 512, srcp); cp_async8(pf_d + 768, srcp + W); }
+        if (strip0) {                                        // warp-uniform: only the inlet strip carries lbc
+            if (lane == 0) cp_async8(pf_d + 1024, lbc_p);
+            if (pf_row < ny - 1) ++lbc_p;
+        }
+        if (!UNI) {
+            const int r = pf_row < last_row ? pf_row : last_row;
+            const int rc = r - lane < 0 ? 0 : (r - lane >= ny ? ny - 1 : r - lane);   // grid row of this lane's cell
+            cp_async8(pf_d + 1280, io.cy + rc);
+            cp_async8(pf_d + 1536, io.cyd + rc);
+        }
+        if (pf_row < last_row) { src += 2 * W; if (CONT) srcp += 2 * W; }
+        ++pf_row;
+        pf_d += (saddr)(kPfValues * 256);
+        if (pf_d == pf_end) pf_d = pf_lane;
     };
     // One commit group per step: "all but the newest kPfDepth-2 groups" = "the row of the next
     // step, and the hand-off block prefetched 8 steps ago, have landed".
 #pragma unroll
-    for (int i = 0; i < kPfDepth - 1; ++i) { pf_issue(i); cp_async_commit(); }
+    for (int i = 0; i < kPfDepth - 1; ++i) { pf_issue(); cp_async_commit(); }
     cp_async_wait_pending<kPfDepth - 2>();
     int err = ein.open(0);
-    halo_in(-1);
+    halo(-1);
     __syncthreads();
-    for (int s = 0; s < nsteps; ++s) {
-        pf_issue(s + kPfDepth - 1);          // refills the slot read one step ago
-        cp_async_commit();
-        cp_async_wait_pending<kPfDepth - 2>();   // row s+1 has landed
-        err |= ein.open(s + 1);              // block starting at row s+1, if that opens one
-        halo_in(s);
-        if (s > 0) halo_out(s - 1);
-        __syncthreads();
+    // Groups of kEdgeBlock steps: the first seven only move this step's data (a compact loop),
+    // the eighth also opens the hand-off block that starts at the next row.
+    int s = 0;
+#pragma unroll 1
+    while (s < nsteps) {
+        const int e = s | (kEdgeBlock - 1);
+#pragma unroll 1
+        for (; s < e && s < nsteps; ++s) {
+            pf_issue();                          // row s + kPfDepth - 1: refills the slot read one step ago
+            cp_async_commit();
+            cp_async_wait_pending<kPfDepth - 2>();   // row s+1 has landed
+            halo(s);
+            __syncthreads();
+        }
+        if (s < nsteps) {
+            pf_issue();
+            cp_async_commit();
+            cp_async_wait_pending<kPfDepth - 2>();
+            err |= ein.open(s + 1);              // block starting at row s+1
+            halo(s);
+            __syncthreads();
+            ++s;
+        }
     }
-    halo_out(nsteps - 1);
+    halo(nsteps);                            // what lane 31 published in the last step
     if (lane == 0) {
         if (err) atomicExch(io.error, err);
         if (io.stats) *io.stats = ((unsigned long long)ein.misses << 32) | ein.spins_total;

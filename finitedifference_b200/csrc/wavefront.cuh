@@ -131,48 +131,42 @@ constexpr unsigned kSpinLimit = 1u << 22;
 
 constexpr int kRecBytes = kRecDoubles * 8;
 
-// Per-lane piece assignment inside a block of kEdgeBlock rows, computed once: lane handles
-// pieces q = lane + 32*it of the block's kEdgeBlock*NPR pieces (row-major [row][piece]).
-template <int NPR>
-struct BlockMap {
-    static constexpr int kIters = (kEdgeBlock * NPR + 31) / 32;
-    int row[kIters];        // row inside the block; >= kEdgeBlock marks "no piece"
-    int goff[kIters];       // offset in doubles from the block's first record
-    int soff[kIters];       // offset in bytes from the block's first ring row
-    __device__ __forceinline__ void init(int lane) {
-#pragma unroll
-        for (int it = 0; it < kIters; ++it) {
-            const int q = lane + 32 * it, r = q / NPR, piece = q - r * NPR;
-            row[it] = q < kEdgeBlock * NPR ? r : 2 * kEdgeBlock;
-            goff[it] = r * kRecDoubles + 2 * piece;
-            soff[it] = r * kRecBytes + 16 * piece;
-        }
-    }
-};
-
+// Consumer side of a strip boundary, run by the data-movement warp.  Work on a block of
+// kEdgeBlock = 8 rows is laid out so that every address is one per-lane base plus an immediate:
+// lane l owns piece (l & 15) of rows (l >> 4), (l >> 4) + 2, + 4, + 6 of the block.
 template <int NPR>
 struct EdgeIn {
-    static constexpr int kIters = BlockMap<NPR>::kIters;
-    BlockMap<NPR> map;
+    static_assert(NPR <= 16, "a record row must fit half a warp");
+    static constexpr int kIters = kEdgeBlock / 2;
     double *g;       // records written by the strip on the left, [ny][kRecDoubles]
     saddr ring;      // [kInRing][kRecDoubles] shared memory of this CTA
-    int ny, lane;
-    bool active, dead, remote;      // remote: the producer is a strip on another GPU (slab runs)
-    unsigned spins_total, misses;   // statistics for bfd_fom_trace
+    int ny, lane, hi;
+    bool active, dead, remote, has;   // remote: the producer is a strip on another GPU (slab runs)
+    unsigned spins_total, misses;     // statistics for bfd_fom_trace
 
     __device__ __forceinline__ void init(double *g_, saddr ring_, int ny_, int lane_, bool active_, bool remote_ = false) {
-        g = g_; ring = ring_; ny = ny_; lane = lane_; active = active_; dead = false; remote = remote_;
+        ny = ny_; lane = lane_; active = active_; dead = false; remote = remote_;
+        hi = lane >> 4;
+        has = (lane & 15) < NPR;
+        g = g_ + 2 * (lane & 15) + hi * kRecDoubles;                 // this lane's piece of row `hi`
+        ring = ring_ + (saddr)((lane & 15) * 16 + hi * kRecBytes);
         spins_total = 0; misses = 0;
-        map.init(lane);
         if (active) prefetch(0);
     }
+    __device__ __forceinline__ saddr slot(int row0) const { return ring + (saddr)((row0 & (kInRing - 1)) * kRecBytes); }
     // start copying the block whose first row is row0 (a multiple of kEdgeBlock) into the ring
     __device__ __forceinline__ void prefetch(int row0) {
         const double *gb = g + (size_t)row0 * kRecDoubles;
-        const saddr sb = ring + (saddr)((row0 % kInRing) * kRecBytes);
+        const saddr sb = slot(row0);
+        if (!has) return;
+        if (row0 + kEdgeBlock <= ny) {
 #pragma unroll
-        for (int it = 0; it < kIters; ++it)
-            if (row0 + map.row[it] < ny && map.row[it] < kEdgeBlock) cp_async16(sb + (saddr)map.soff[it], gb + map.goff[it]);
+            for (int it = 0; it < kIters; ++it) cp_async16(sb + (saddr)(it * 2 * kRecBytes), gb + it * 2 * kRecDoubles);
+        } else {
+#pragma unroll
+            for (int it = 0; it < kIters; ++it)
+                if (row0 + hi + 2 * it < ny) cp_async16(sb + (saddr)(it * 2 * kRecBytes), gb + it * 2 * kRecDoubles);
+        }
     }
     // Whole warp, every step; works when `s` opens a block.  Returns BFD_ETIMEOUT once if the
     // producer never showed up (the block then reads as zeros).  Every branch is warp-uniform.
@@ -180,18 +174,18 @@ struct EdgeIn {
 #ifdef BFD_X_NOOPEN
         return 0;
 #endif
-        if (!active || s >= ny || (s % kEdgeBlock) != 0) return 0;
+        if ((s & (kEdgeBlock - 1)) != 0 || !active || s >= ny) return 0;
         int err = 0;
         double *gb = g + (size_t)s * kRecDoubles;
-        const saddr sb = ring + (saddr)((s % kInRing) * kRecBytes);
+        const saddr sb = slot(s);
         double p0[kIters], p1[kIters];
         bool mine[kIters];
         bool ok = true;
 #pragma unroll
         for (int it = 0; it < kIters; ++it) {
-            mine[it] = s + map.row[it] < ny && map.row[it] < kEdgeBlock;
+            mine[it] = has && s + hi + 2 * it < ny;
             p0[it] = 0.0; p1[it] = 0.0;
-            if (mine[it]) lds2(sb + (saddr)map.soff[it], p0[it], p1[it]);
+            if (mine[it]) lds2(sb + (saddr)(it * 2 * kRecBytes), p0[it], p1[it]);
             ok = ok && !(is_sentinel(p0[it]) || is_sentinel(p1[it]));
         }
         if (!__all_sync(0xffffffffu, ok || dead)) {
@@ -203,8 +197,8 @@ struct EdgeIn {
 #pragma unroll
                 for (int it = 0; it < kIters; ++it) {
                     if (mine[it] && (is_sentinel(p0[it]) || is_sentinel(p1[it]))) {
-                        if (remote) ld_sys2(gb + map.goff[it], p0[it], p1[it]);
-                        else ld_volatile2(gb + map.goff[it], p0[it], p1[it]);
+                        if (remote) ld_sys2(gb + it * 2 * kRecDoubles, p0[it], p1[it]);
+                        else ld_volatile2(gb + it * 2 * kRecDoubles, p0[it], p1[it]);
                         ok = ok && !(is_sentinel(p0[it]) || is_sentinel(p1[it]));
                     }
                 }
@@ -215,17 +209,17 @@ struct EdgeIn {
             }
 #pragma unroll
             for (int it = 0; it < kIters; ++it)
-                if (mine[it]) sts2(sb + (saddr)map.soff[it], dead ? 0.0 : p0[it], dead ? 0.0 : p1[it]);
+                if (mine[it]) sts2(sb + (saddr)(it * 2 * kRecBytes), dead ? 0.0 : p0[it], dead ? 0.0 : p1[it]);
         } else if (dead) {
 #pragma unroll
             for (int it = 0; it < kIters; ++it)
-                if (mine[it]) sts2(sb + (saddr)map.soff[it], 0.0, 0.0);
+                if (mine[it]) sts2(sb + (saddr)(it * 2 * kRecBytes), 0.0, 0.0);
         }
 #ifndef BFD_X_NOREARM
         if (!dead) {
 #pragma unroll
             for (int it = 0; it < kIters; ++it)
-                if (mine[it]) st_weak2(gb + map.goff[it], sentinel_value(), sentinel_value());   // re-arm
+                if (mine[it]) st_weak2(gb + it * 2 * kRecDoubles, sentinel_value(), sentinel_value());   // re-arm
         }
 #endif
         __syncwarp();
