@@ -391,7 +391,8 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
             double rv = Av[k] + v;
             rv = fma(cy, Hh, rv); rv = fma(cx, Gh, rv); rv = fma(ncyd, DH, rv); rv = fma(ncxl, LG, rv);
             const double r2 = fma(rv, rv, ru * ru);
-            nrm[k] += valid ? r2 : 0.0;
+            // main phase: every row is a cell; padding columns (last strip) are dropped after the loop
+            nrm[k] += EP ? (valid ? r2 : 0.0) : r2;
             sts2(xc_own + xc_level(k, wbuf), Fh, Gh);
             prev[k].Gh = Gh; prev[k].Hh = Hh;
 
@@ -421,8 +422,10 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
                     if (!EP || (so >= 0 && so <= last_row)) {
 #endif
                         double *o = io.xout + (size_t)so * (2 * W);
-                        o[0] = valid ? xu[K] : 0.0;
-                        o[W] = valid ? xv[K] : 0.0;
+                        // padding columns of the last strip evolve as a phantom continuation of the
+                        // grid: finite, and never read by a real cell (information only moves right)
+                        o[0] = EP ? (valid ? xu[K] : 0.0) : xu[K];
+                        o[W] = EP ? (valid ? xv[K] : 0.0) : xv[K];
                     }
                 }
             }
@@ -448,6 +451,7 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
 #pragma unroll 1
         for (; s < ep_end; ++s) body(s, BoolTag<true>{});
         if (phase == 0) {
+#pragma unroll 2
             for (; s < main_end; ++s) body(s, BoolTag<false>{});
         }
     }
@@ -455,7 +459,7 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
     // ||r(x_k)||^2 of this strip, fixed reduction order (deterministic iteration counts)
 #pragma unroll
     for (int k = LO; k < HI; ++k) {
-        double x = nrm[k];
+        double x = colok ? nrm[k] : 0.0;
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) x += __shfl_xor_sync(0xffffffffu, x, off);
         if (lane == 0) io.partial[k] = x;
@@ -484,47 +488,97 @@ template <int K, bool CONT, bool UNI>
 __device__ __forceinline__ void dma_part(const StepIo &io) {
     constexpr int NPR = 2 * K + 1 + (CONT ? 1 : 0);
     constexpr int W = 32;
-    constexpr int kNever = -(1 << 30);     // row offset of a lane with nothing to move: never in [0, ny)
+    static_assert(NPR <= 32, "one lane per piece of a record row");
     const int lane = io.lane, ny = io.ny;
     const int last_row = ny + kSkew - 1;
     const int nsteps = ny + kSkew + K;
-    EdgeIn<NPR> ein;
-    ein.init(io.edge_in, io.ring_in, ny, lane, io.strip > 0, io.in_remote);
+    int err = 0;
+    unsigned misses = 0, spins_total = 0;
 
-    // This lane's piece of a row record: where it sits in the exchange rows, and the row it
-    // belongs to at step s (the previous-time-level pair of continuation passes travels with level 0).
+    // ---- strip-to-strip hand-off: lane p moves piece p of the row records -------------------
+    // Every lane runs its own stream of rows, one per step, offset by the Newton level its piece
+    // belongs to (the previous-time-level pair of continuation passes travels with level 0):
+    //   in : the halo slot of the exchange rows <- what lane 0 of the compute warps reads in the
+    //        next step.  The piece comes from the shared-memory ring, where it was copied kAhead
+    //        rows earlier (cp.async, in the per-step commit groups), and is read from the ring one
+    //        step before it is needed so that no load is waited for inside a step; a piece that had
+    //        not arrived when it was copied is polled from global memory.  Consumed pieces are
+    //        re-armed (sentinel) for the next launch.
+    //   out: the records of this strip <- what lane 31 (slot 32) published in the previous step.
     const bool special = CONT && lane == 2 * K + 1;
-    const int p_row = special ? 0 : (lane >> 1);
+    const int lvl = special ? 0 : (lane >> 1);
     const bool take = lane < NPR && io.strip > 0, give = lane < NPR && io.strip < io.nstrips - 1;
-    const int c_in = take ? 1 - p_row : kNever;              // lane 0 of the compute warps reads row s + 1 - level in step s + 1
-    const int c_out = give ? -1 - kSkew - p_row : kNever;    // lane 31 published row s - 1 - 31 - level in step s - 1
+    const bool in_remote = io.in_remote, out_remote = io.out_remote;
     const saddr p_x = io.xchg + (saddr)((special ? K + 1 : (lane >> 1)) * 4 * kXRow + (special ? 0 : (lane & 1)) * kXRow);
-    const saddr p_ring = io.ring_in + (saddr)(lane * 16);
-    double *p_out = io.edge_out + 2 * lane;
-    const bool out_remote = io.out_remote;
     const saddr x_sum = 2 * p_x + (saddr)(2 * kXRow);        // the two exchange buffers alternate: next = x_sum - current
     saddr x_cur = p_x + (saddr)(2 * kXRow);                  // buffer of step -1 (odd)
     saddr x_prev = p_x;
-    // halo slot of the exchange buffer written in step s <- what lane 0 reads in step s + 1;
-    // records <- what lane 31 (slot 32) published in step s - 1
-    auto halo = [&](int s) {
-        const int rin = s + c_in, rout = s + c_out;
-        if ((unsigned)rin < (unsigned)ny) {
-            double a, b;
-            lds2(p_ring + (saddr)((rin & (kInRing - 1)) * kRecBytes), a, b);
-            sts2(x_cur, a, b);
+    const saddr ring0 = io.ring_in + (saddr)(lane * 16), ring_end = ring0 + (saddr)(kInRing * kRecBytes);
+    int rc = -lvl;                                           // row consumed by the call for step s: s + 1 - level
+    int ro = -2 - kSkew - lvl;                               // row sent by the call for step s: s - 1 - 31 - level
+    double *gin = io.edge_in + 2 * lane + (ptrdiff_t)rc * kRecDoubles;
+    double *gout = io.edge_out + 2 * lane + (ptrdiff_t)ro * kRecDoubles;
+    saddr sl = ring0 + (saddr)(((rc + 1) & (kInRing - 1)) * kRecBytes);          // slot of the row loaded early
+    saddr pl = ring0 + (saddr)(((rc + kAhead) & (kInRing - 1)) * kRecBytes);     // slot of the row copied now
+    double va = 0.0, vb = 0.0;                               // the piece consumed by the next call
+
+    if (io.strip > 0) {
+        // Keep a distance to the producer: do not start the time step before it is kStartRow rows
+        // into it.  Strips run at the same pace, so the distance stays and the copies find their
+        // data; a strip that starts as soon as row 0 exists would stay that close for ever and
+        // wait for a global-memory round trip in every step.
+        const int rw = kStartRow < ny ? kStartRow : ny - 1;
+        const double *gw = io.edge_in + (size_t)rw * kRecDoubles + 2 * ((NPR - 1) & ~1);   // last Newton level: written last
+        unsigned spins = 0;
+        for (;;) {
+            double a = 0.0, b = 0.0;
+            if (lane == 0) { if (in_remote) ld_sys2(gw, a, b); else ld_volatile2(gw, a, b); }
+            if (__all_sync(0xffffffffu, !(is_sentinel(a) || is_sentinel(b)))) break;
+            ++spins_total;
+            if (++spins > kSpinLimit) { err = BFD_ETIMEOUT; break; }
+            spin_pause();
         }
-        if ((unsigned)rout < (unsigned)ny) {
+        if (take) {
+#pragma unroll
+            for (int r = 0; r < kAhead; ++r)
+                if (r < ny) cp_async16(ring0 + (saddr)(r * kRecBytes), io.edge_in + 2 * lane + (size_t)r * kRecDoubles);
+        }
+    }
+    auto halo = [&]() {
+        double na = 0.0, nb = 0.0;
+        if (take && (unsigned)(rc + 1) < (unsigned)ny) lds2(sl, na, nb);
+        if (take && (unsigned)rc < (unsigned)ny) {
+            if (is_sentinel_hi(va) || is_sentinel_hi(vb)) {          // had not arrived when the row was copied
+                ++misses;
+                unsigned spins = 0;
+                for (;;) {
+                    if (in_remote) ld_sys2(gin, va, vb); else ld_volatile2(gin, va, vb);
+                    if (!(is_sentinel(va) || is_sentinel(vb))) break;
+                    ++spins_total;
+                    if (++spins > kSpinLimit) { err = BFD_ETIMEOUT; va = 0.0; vb = 0.0; break; }
+                    if (spins > 2) spin_pause();
+                }
+            }
+            sts2(x_cur, va, vb);
+#ifndef BFD_X_NOREARM
+            st_weak2(gin, sentinel_value(), sentinel_value());       // re-arm for the next launch
+#endif
+            if (rc + kAhead < ny) cp_async16(pl, gin + (size_t)kAhead * kRecDoubles);
+        }
+        if (give && (unsigned)ro < (unsigned)ny) {
             double a, b;
             lds2(x_prev + 32 * 16, a, b);
-            double *g = p_out + (size_t)rout * kRecDoubles;
-            if (out_remote) st_sys2(g, a, b); else st_volatile2(g, a, b);
+            if (out_remote) st_sys2(gout, a, b); else st_volatile2(gout, a, b);
         }
+        va = na; vb = nb;
+        ++rc; ++ro; gin += kRecDoubles; gout += kRecDoubles;
+        sl += (saddr)kRecBytes; if (sl == ring_end) sl = ring0;
+        pl += (saddr)kRecBytes; if (pl == ring_end) pl = ring0;
         x_prev = x_cur;
         x_cur = x_sum - x_cur;
     };
 
-    // level-0 input ring: one row per step, kPfDepth - 1 rows ahead; running addresses, no modulo
+    // ---- level-0 input ring: one row per step, kPfDepth - 1 rows ahead; running addresses ------
     const saddr pf_lane = io.pf + (saddr)(lane * 8);
     const saddr pf_end = pf_lane + (saddr)(kPfDepth * kPfValues * 256);
     saddr pf_d = pf_lane;
@@ -541,9 +595,9 @@ __device__ __forceinline__ void dma_part(const StepIo &io) {
         }
         if (!UNI) {
             const int r = pf_row < last_row ? pf_row : last_row;
-            const int rc = r - lane < 0 ? 0 : (r - lane >= ny ? ny - 1 : r - lane);   // grid row of this lane's cell
-            cp_async8(pf_d + 1280, io.cy + rc);
-            cp_async8(pf_d + 1536, io.cyd + rc);
+            const int rcy = r - lane < 0 ? 0 : (r - lane >= ny ? ny - 1 : r - lane);   // grid row of this lane's cell
+            cp_async8(pf_d + 1280, io.cy + rcy);
+            cp_async8(pf_d + 1536, io.cyd + rcy);
         }
         if (pf_row < last_row) { src += 2 * W; if (CONT) srcp += 2 * W; }
         ++pf_row;
@@ -551,42 +605,31 @@ __device__ __forceinline__ void dma_part(const StepIo &io) {
         if (pf_d == pf_end) pf_d = pf_lane;
     };
     // One commit group per step: "all but the newest kPfDepth-2 groups" = "the row of the next
-    // step, and the hand-off block prefetched 8 steps ago, have landed".
+    // step, and the hand-off rows copied >= 4 steps ago, have landed".
 #pragma unroll
     for (int i = 0; i < kPfDepth - 1; ++i) { pf_issue(); cp_async_commit(); }
     cp_async_wait_pending<kPfDepth - 2>();
-    int err = ein.open(0);
-    halo(-1);
+    if (take && (unsigned)rc < (unsigned)ny) lds2(ring0 + (saddr)((rc & (kInRing - 1)) * kRecBytes), va, vb);
+    halo();                                  // "step -1": what lane 0 reads in step 0
     __syncthreads();
-    // Groups of kEdgeBlock steps: the first seven only move this step's data (a compact loop),
-    // the eighth also opens the hand-off block that starts at the next row.
-    int s = 0;
 #pragma unroll 1
-    while (s < nsteps) {
-        const int e = s | (kEdgeBlock - 1);
-#pragma unroll 1
-        for (; s < e && s < nsteps; ++s) {
-            pf_issue();                          // row s + kPfDepth - 1: refills the slot read one step ago
-            cp_async_commit();
-            cp_async_wait_pending<kPfDepth - 2>();   // row s+1 has landed
-            halo(s);
-            __syncthreads();
-        }
-        if (s < nsteps) {
-            pf_issue();
-            cp_async_commit();
-            cp_async_wait_pending<kPfDepth - 2>();
-            err |= ein.open(s + 1);              // block starting at row s+1
-            halo(s);
-            __syncthreads();
-            ++s;
+    for (int s = 0; s < nsteps; ++s) {
+        pf_issue();                          // row s + kPfDepth - 1: refills the slot read one step ago
+        cp_async_commit();
+        cp_async_wait_pending<kPfDepth - 2>();
+        halo();
+        __syncthreads();
+    }
+    halo();                                  // what lane 31 published in the last step
+    if (io.stats) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            misses += __shfl_xor_sync(0xffffffffu, misses, off);
+            spins_total += __shfl_xor_sync(0xffffffffu, spins_total, off);
         }
     }
-    halo(nsteps);                            // what lane 31 published in the last step
-    if (lane == 0) {
-        if (err) atomicExch(io.error, err);
-        if (io.stats) *io.stats = ((unsigned long long)ein.misses << 32) | ein.spins_total;
-    }
+    if (__any_sync(0xffffffffu, err != 0) && lane == 0) atomicExch(io.error, BFD_ETIMEOUT);
+    if (lane == 0 && io.stats) *io.stats = ((unsigned long long)misses << 32) | spins_total;
 }
 
 // First level of warp w when the K+1 levels of a pass (K solves + the residual of x_K) are

@@ -106,6 +106,10 @@ inline unsigned long long global_timer_ns() { return 0; }
 __device__ __forceinline__ bool is_sentinel(double x) {
     return (unsigned long long)__double_as_longlong(x) == kSentinelBits;
 }
+// cheaper test for values that came through the ring: no arithmetic result has these high 32 bits
+__device__ __forceinline__ bool is_sentinel_hi(double x) {
+    return (unsigned)((unsigned long long)__double_as_longlong(x) >> 32) == (unsigned)(kSentinelBits >> 32);
+}
 __device__ __forceinline__ double sentinel_value() { return __longlong_as_double((long long)kSentinelBits); }
 
 // ------------------------------------------------------------------------------------------
@@ -126,108 +130,13 @@ __device__ __forceinline__ double sentinel_value() { return __longlong_as_double
 constexpr int kEdgeBlock = 8;
 constexpr int kPiecesMax = 2 * BFD_FOM_KMAX + 2;   // pieces per row in global memory (fixed pitch)
 constexpr int kRecDoubles = 2 * kPiecesMax;        // doubles per row record
-constexpr int kInRing = 32;                        // rows in the consumer's ring (4 blocks)
+constexpr int kInRing = 32;                        // rows in the consumer's ring
 constexpr unsigned kSpinLimit = 1u << 22;
 
 constexpr int kRecBytes = kRecDoubles * 8;
 
-// Consumer side of a strip boundary, run by the data-movement warp.  Work on a block of
-// kEdgeBlock = 8 rows is laid out so that every address is one per-lane base plus an immediate:
-// lane l owns piece (l & 15) of rows (l >> 4), (l >> 4) + 2, + 4, + 6 of the block.
-template <int NPR>
-struct EdgeIn {
-    static_assert(NPR <= 16, "a record row must fit half a warp");
-    static constexpr int kIters = kEdgeBlock / 2;
-    double *g;       // records written by the strip on the left, [ny][kRecDoubles]
-    saddr ring;      // [kInRing][kRecDoubles] shared memory of this CTA
-    int ny, lane, hi;
-    bool active, dead, remote, has;   // remote: the producer is a strip on another GPU (slab runs)
-    unsigned spins_total, misses;     // statistics for bfd_fom_trace
-
-    __device__ __forceinline__ void init(double *g_, saddr ring_, int ny_, int lane_, bool active_, bool remote_ = false) {
-        ny = ny_; lane = lane_; active = active_; dead = false; remote = remote_;
-        hi = lane >> 4;
-        has = (lane & 15) < NPR;
-        g = g_ + 2 * (lane & 15) + hi * kRecDoubles;                 // this lane's piece of row `hi`
-        ring = ring_ + (saddr)((lane & 15) * 16 + hi * kRecBytes);
-        spins_total = 0; misses = 0;
-        if (active) prefetch(0);
-    }
-    __device__ __forceinline__ saddr slot(int row0) const { return ring + (saddr)((row0 & (kInRing - 1)) * kRecBytes); }
-    // start copying the block whose first row is row0 (a multiple of kEdgeBlock) into the ring
-    __device__ __forceinline__ void prefetch(int row0) {
-        const double *gb = g + (size_t)row0 * kRecDoubles;
-        const saddr sb = slot(row0);
-        if (!has) return;
-        if (row0 + kEdgeBlock <= ny) {
-#pragma unroll
-            for (int it = 0; it < kIters; ++it) cp_async16(sb + (saddr)(it * 2 * kRecBytes), gb + it * 2 * kRecDoubles);
-        } else {
-#pragma unroll
-            for (int it = 0; it < kIters; ++it)
-                if (row0 + hi + 2 * it < ny) cp_async16(sb + (saddr)(it * 2 * kRecBytes), gb + it * 2 * kRecDoubles);
-        }
-    }
-    // Whole warp, every step; works when `s` opens a block.  Returns BFD_ETIMEOUT once if the
-    // producer never showed up (the block then reads as zeros).  Every branch is warp-uniform.
-    __device__ __forceinline__ int open(int s) {
-#ifdef BFD_X_NOOPEN
-        return 0;
-#endif
-        if ((s & (kEdgeBlock - 1)) != 0 || !active || s >= ny) return 0;
-        int err = 0;
-        double *gb = g + (size_t)s * kRecDoubles;
-        const saddr sb = slot(s);
-        double p0[kIters], p1[kIters];
-        bool mine[kIters];
-        bool ok = true;
-#pragma unroll
-        for (int it = 0; it < kIters; ++it) {
-            mine[it] = has && s + hi + 2 * it < ny;
-            p0[it] = 0.0; p1[it] = 0.0;
-            if (mine[it]) lds2(sb + (saddr)(it * 2 * kRecBytes), p0[it], p1[it]);
-            ok = ok && !(is_sentinel(p0[it]) || is_sentinel(p1[it]));
-        }
-        if (!__all_sync(0xffffffffu, ok || dead)) {
-            // some piece had not arrived when the block was prefetched: poll global memory
-            ++misses;
-            unsigned spins = 0;
-            for (;;) {
-                ok = true;
-#pragma unroll
-                for (int it = 0; it < kIters; ++it) {
-                    if (mine[it] && (is_sentinel(p0[it]) || is_sentinel(p1[it]))) {
-                        if (remote) ld_sys2(gb + it * 2 * kRecDoubles, p0[it], p1[it]);
-                        else ld_volatile2(gb + it * 2 * kRecDoubles, p0[it], p1[it]);
-                        ok = ok && !(is_sentinel(p0[it]) || is_sentinel(p1[it]));
-                    }
-                }
-                if (__all_sync(0xffffffffu, ok)) break;
-                ++spins_total;
-                if (++spins > kSpinLimit) { dead = true; err = BFD_ETIMEOUT; break; }
-                if (spins > 2) spin_pause();
-            }
-#pragma unroll
-            for (int it = 0; it < kIters; ++it)
-                if (mine[it]) sts2(sb + (saddr)(it * 2 * kRecBytes), dead ? 0.0 : p0[it], dead ? 0.0 : p1[it]);
-        } else if (dead) {
-#pragma unroll
-            for (int it = 0; it < kIters; ++it)
-                if (mine[it]) sts2(sb + (saddr)(it * 2 * kRecBytes), 0.0, 0.0);
-        }
-#ifndef BFD_X_NOREARM
-        if (!dead) {
-#pragma unroll
-            for (int it = 0; it < kIters; ++it)
-                if (mine[it]) st_weak2(gb + it * 2 * kRecDoubles, sentinel_value(), sentinel_value());   // re-arm
-        }
-#endif
-        __syncwarp();
-#ifndef BFD_X_NOEDGEPF
-        if (!dead && s + kEdgeBlock < ny) prefetch(s + kEdgeBlock);
-#endif
-        return err;
-    }
-};
+constexpr int kAhead = 12;                // rows copied into the consumer's ring ahead of their use
+constexpr int kStartRow = kAhead + 6;     // a strip starts a time step when its producer has finished this row
+static_assert(kAhead + 2 <= kInRing, "rows in flight plus the row in use must fit the ring");
 
 }  // namespace bfd

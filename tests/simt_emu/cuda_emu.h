@@ -168,6 +168,7 @@ static inline bool __all_sync(unsigned, bool p) {
     w->bar.wait();
     return all;
 }
+static inline bool __any_sync(unsigned m, bool p) { return !__all_sync(m, !p); }
 static inline void __syncwarp(unsigned = 0xffffffffu) { emu::tls.warp->bar.wait(); }
 static inline void __syncthreads() { emu::tls.cta->bar.wait(); }
 static inline void __threadfence() { std::atomic_thread_fence(std::memory_order_seq_cst); }
