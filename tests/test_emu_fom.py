@@ -22,6 +22,8 @@ def rel_err(a, b):
     (70, 33, [[5.0, 0.02]], dict(uniform_y=False)),               # non-square, ragged last strip, cy[] path
     (33, 20, [[5.0, 0.02]], dict(newton_hint=1, chunk_steps=1)),   # under-speculated: continuation passes
     (20, 20, [[4.4, 0.016]], dict(newton_hint=6)),                 # over-speculated: the step is redone
+    (40, 72, [[4.75, 0.02]], {}),                                  # tall enough for the unmasked main phases (ny > 52)
+    (40, 72, [[4.75, 0.02]], dict(newton_hint=1, chunk_steps=2)),  # ... of the continuation pass too
 ])
 def test_emulated_fom_matches_oracle(lib, nx, ny, mus, kw):
     gx, gy = orc.make_2D_grid(0, 100, 0, 100, nx, ny)
