@@ -53,7 +53,7 @@ struct FomCtl {            // one per mu sample, 64 bytes
     unsigned epoch;        // bumped by every commit: strips waiting to restart watch it
     double init_norm;      // ||r(x_0)|| of step t, kept for continuation passes
     unsigned exits;        // slab runs: strips (of all ranks) that left a launch, summed over launches
-    unsigned pad0;
+    unsigned under;        // consecutive steps that needed a continuation pass (speculation policy)
     double pad1[2];
 };
 static_assert(sizeof(FomCtl) == 64, "FomCtl must stay 64 bytes");
@@ -709,6 +709,16 @@ __device__ void commit_segment(const FomArgs &a, int m, int t0, int i0, int n, i
     int t = t0, knext = k_spec, redo = 0;
     int new_kbase = 0, new_kfirst = k_first;
     bool stop = false;
+    // Speculation policy: a continuation pass (one more sweep in place) is cheaper than redoing a
+    // step, so when a step needed one the count is NOT raised at once -- only when two steps in
+    // a row needed it.  A solve count that flips between K and K+1 from step to step then costs
+    // one continuation pass every other step instead of a redo or a continuation in every step.
+    unsigned under = ctl->under;
+    auto completed = [&](int kb, int total) {
+        if (kb > 0) { ++under; return under >= 2 ? total : kb; }
+        under = 0;
+        return total;
+    };
     for (int ii = 0; ii < n && !stop; ++ii) {
         const volatile StepRec *vr = a.steprec + (size_t)m * a.chunk + i0 + ii;   // written by another CTA: not through L1
         StepRec rec;
@@ -719,8 +729,8 @@ __device__ void commit_segment(const FomArgs &a, int m, int t0, int i0, int n, i
         int *its = a.its + (size_t)m * a.num_steps + t;
         double *rel = a.relnorm + (size_t)m * a.num_steps + t;
         switch (rec.status) {
-        case kStepOk:     *its = kb + K + 1; *rel = rec.rel; knext = kb + K; ++t; break;   // == len(resnorms)
-        case kStepOkCap:  *its = a.max_its;  *rel = rec.rel; knext = kb + K; ++t; break;
+        case kStepOk:     *its = kb + K + 1; *rel = rec.rel; knext = completed(kb, kb + K); ++t; break;   // == len(resnorms)
+        case kStepOkCap:  *its = a.max_its;  *rel = rec.rel; knext = completed(kb, kb + K); ++t; break;
         case kStepEarly:
             if (!a.strict || rec.kconv == 0) {   // keep the further-converged iterate
                 *its = kb + K + 1; *rel = rec.rel; knext = kb + rec.kconv; ++t;
@@ -736,6 +746,7 @@ __device__ void commit_segment(const FomArgs &a, int m, int t0, int i0, int n, i
     if (!stop) { ctl->kbase = 0; ctl->k_first = clampk(knext); ctl->k_spec = clampk(knext); }
     else { ctl->kbase = new_kbase; ctl->k_first = new_kfirst; }
     ctl->t = t;
+    ctl->under = under;
     if (redo) { ctl->redone += redo; atomicAdd(&a.glob->redone, redo); }
     if (t >= a.num_steps) {
 #ifndef BFD_EMULATE
@@ -996,7 +1007,7 @@ __global__ void fom_reset_kernel(const FomArgs a, int control) {
         FomCtl c;
         c.t = 0; c.kbase = 0; c.k_first = a.hint; c.k_spec = a.hint;
         c.gate = 0; c.arrive = 0; c.redone = 0; c.epoch = 0; c.init_norm = 0.0;
-        c.exits = 0; c.pad0 = 0; c.pad1[0] = c.pad1[1] = 0.0;
+        c.exits = 0; c.under = 0; c.pad1[0] = c.pad1[1] = 0.0;
         a.ctl[g] = c;
     }
 }

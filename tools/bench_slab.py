@@ -45,6 +45,7 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        os.environ["NCCL_DEBUG"] = "WARN"      # NCCL prints its version banner on stdout otherwise: one JSON line only
         dist.init_process_group("nccl", device_id=dev)
     barrier = (lambda: dist.barrier()) if world > 1 else (lambda: None)
     mu, dt = [4.75, 0.02], 0.05
@@ -116,7 +117,7 @@ def main():
             "n_gpus": world, "scaling": "strong", "ms_per_trajectory": ms, "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"single-mu FOM, {n}x{n} grid, {T} steps, slab decomposition over {world} GPU(s)",
                        "grid": n, "num_steps": T, "dx": a.dx, "strips_rank0": list(s.strips), "columns_rank0": [s.c0, s.c1]},
-            "newton_its_mean": float(its.mean()), "max_relnorm": float(rel.max()), "steps_redone": s.steps_redone,
+            "newton_its_mean": float(its.mean()), "newton_its": its[0].tolist(), "max_relnorm": float(rel.max()), "steps_redone": s.steps_redone,
             "launches_rank0": int(launches), "check": check,
             "halo_bytes_per_trajectory": int((world - 1) * T * n * (2 * float(its.mean()) + 1) * 16)}), flush=True)
     s.close()
