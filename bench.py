@@ -173,7 +173,7 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        os.environ["NCCL_DEBUG"] = "WARN"      # NCCL prints its version banner on stdout otherwise: one JSON line only
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # keep NCCL's banner / debug lines off stdout: one JSON line only
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.get_lib()
     n, T = args.grid, args.num_steps
