@@ -143,6 +143,45 @@ __global__ void __launch_bounds__(256) ecsw_c_block_kernel(long long n, int k, c
     }
 }
 
+// The same block without the intermediate J V: a 32-cell x 32-mode tile of
+// C[j, cell] = r_u (J V)_u[cell, j] + r_v (J V)_v[cell, j] is formed from the basis rows directly
+// (reads along modes), transposed in shared memory and written along cells.  HBM traffic per
+// snapshot: V once + the C block, instead of V + 3 x (J V) + C.
+__global__ void __launch_bounds__(256) ecsw_c_fused_kernel(const RomArgs a, const double *r, double *C, size_t ldc) {
+    BFD_SHARED_ARRAY(double, tile, [32][33]);
+    const bfd_rom_mesh &m = a.m;
+    const long long n = m.nrows, nc = m.ncells;
+    const int k = a.k;
+    const long long cell0 = (long long)blockIdx.x * 32;
+    const int j = blockIdx.y * 32 + threadIdx.x;
+    for (int cy = threadIdx.y; cy < 32; cy += blockDim.y) {
+        const long long i = cell0 + cy;
+        double val = 0.0;
+        if (i < n && j < k) {
+            const int p = m.p[i], xl = m.xl[i], ja = m.ja[i], jb = m.jb[i];
+            const double cx = m.cx[i], cxl = (xl >= 0) ? m.cxl[i] : 0.0, cy_ = (ja >= 0) ? m.cy[i] : 0.0,
+                         cyd = (jb >= 0) ? m.cyd[i] : 0.0;
+            const int xls = xl >= 0 ? xl : p, jas = ja >= 0 ? ja : p, jbs = jb >= 0 ? jb : p;
+            const double pxu = cx * a.w[p], pxv = cx * a.w[nc + p], lxu = cxl * a.w[xls], lxv = cxl * a.w[nc + xls];
+            const double ayu = cy_ * a.w[jas], ayv = cy_ * a.w[nc + jas], byu = cyd * a.w[jbs], byv = cyd * a.w[nc + jbs];
+            const double vpu = a.V[(size_t)p * k + j], vpv = a.V[(size_t)(nc + p) * k + j];
+            const double vlu = a.V[(size_t)xls * k + j], vlv = a.V[(size_t)(nc + xls) * k + j];
+            const double vau = a.V[(size_t)jas * k + j], vav = a.V[(size_t)(nc + jas) * k + j];
+            const double vbu = a.V[(size_t)jbs * k + j], vbv = a.V[(size_t)(nc + jbs) * k + j];
+            const double ju = vpu + (pxu * vpu - lxu * vlu) + 0.5 * (ayv * vau - byv * vbu) + 0.5 * (ayu * vav - byu * vbv);
+            const double jv = vpv + 0.5 * (pxv * vpu - lxv * vlu) + (ayv * vav - byv * vbv) + 0.5 * (pxu * vpv - lxu * vlv);
+            val = r[i] * ju + r[n + i] * jv;
+        }
+        tile[cy][threadIdx.x] = val;
+    }
+    __syncthreads();
+    for (int jy = threadIdx.y; jy < 32; jy += blockDim.y) {
+        const int jj = blockIdx.y * 32 + jy;
+        const long long cell = cell0 + threadIdx.x;
+        if (cell < n && jj < k) C[(size_t)jj * ldc + cell] = tile[threadIdx.x][jy];
+    }
+}
+
 }  // namespace bfd
 
 using namespace bfd;
@@ -180,6 +219,16 @@ extern "C" int bfd_jac_csr_values(const bfd_rom_mesh *m, const double *w, double
     long long grid = (m->nrows + 255) / 256;
     if (grid > 148 * 8) grid = 148 * 8;
     BFD_LAUNCH(rom_jac_values_kernel, BFD_GRID((int)grid), 256, 0, (cudaStream_t)stream, a);
+    BFD_LAUNCHED();
+    return BFD_OK;
+}
+
+extern "C" int bfd_ecsw_c_fused(const bfd_rom_mesh *m, const double *w, const double *r, const double *V, int k,
+                                double *C, size_t ldc, void *stream) {
+    if (check_mesh(m) != BFD_OK || !w || !r || !V || !C || k < 1 || ldc < (size_t)m->nrows) return BFD_EINVAL;
+    RomArgs a{*m, w, nullptr, V, nullptr, nullptr, nullptr, k};
+    dim3 grid((unsigned)((m->nrows + 31) / 32), (unsigned)((k + 31) / 32)), block(32, 8);
+    BFD_LAUNCH(ecsw_c_fused_kernel, grid, block, 0, (cudaStream_t)stream, a, r, C, ldc);
     BFD_LAUNCHED();
     return BFD_OK;
 }

@@ -245,6 +245,18 @@ class EcswSolver(_RomBase):
         return red, history
 
 
+_TRAINING_MESH = {}
+
+
+def _training_mesh(grid_x, grid_y, dt, mu, dev):
+    """Index tables of the full grid, kept for repeated calls with the same grid (one entry)."""
+    key = (np.asarray(grid_x).tobytes(), np.asarray(grid_y).tobytes(), float(dt), float(mu[0]), float(mu[1]), str(dev))
+    if key not in _TRAINING_MESH:
+        _TRAINING_MESH.clear()
+        _TRAINING_MESH[key] = MeshTables(grid_x, grid_y, dt, mu, dev)
+    return _TRAINING_MESH[key]
+
+
 def ecsw_training_matrix(snaps, prev_snaps, basis, grid_x, grid_y, dt, mu, device=None, out_device=False):
     """``compute_ECSW_training_matrix_2D`` (:2795-2816) with the exact Jacobian of ``get_ops``:
     ``C[i*k:(i+1)*k, cell] = r_u[cell]*(JV)_u[cell, :] + r_v[cell]*(JV)_v[cell, :]``."""
@@ -255,13 +267,12 @@ def ecsw_training_matrix(snaps, prev_snaps, basis, grid_x, grid_y, dt, mu, devic
     S, P, V = to_dev(snaps), to_dev(prev_snaps), to_dev(basis).contiguous()
     n2, n_snaps = S.shape
     n_cells, k = n2 // 2, V.shape[1]
-    mesh = MeshTables(grid_x, grid_y, dt, mu, dev)
+    mesh = _training_mesh(grid_x, grid_y, dt, mu, dev)
     Cmat = torch.empty((k * n_snaps, n_cells), dtype=torch.float64, device=dev)
     for i in range(n_snaps):
         w, wp = S[:, i].contiguous(), P[:, i].contiguous()
         r, _ = base.residual(mesh, w, wp)
-        JV = base.jv(mesh, w, V)
-        _lib.check(base.lib.bfd_ecsw_c_block(n_cells, k, r.data_ptr(), JV.data_ptr(),
+        _lib.check(base.lib.bfd_ecsw_c_fused(C.byref(mesh.c), w.data_ptr(), r.data_ptr(), V.data_ptr(), k,
                                              Cmat[i * k:(i + 1) * k].data_ptr(), n_cells, base._stream()),
-                   base.lib, "bfd_ecsw_c_block")
+                   base.lib, "bfd_ecsw_c_fused")
     return Cmat if out_device else Cmat.cpu().numpy()

@@ -217,6 +217,13 @@ int bfd_jac_csr_values(const bfd_rom_mesh *mesh, const double *w, double *vals, 
 int bfd_ecsw_c_block(int64_t nrows, int k, const double *r, const double *JV, double *C, size_t ldc,
                      void *stream);
 
+/* The same block straight from the basis: C[j*ldc + cell] = r[cell]*(J(w)V)[cell][j] +
+ * r[nrows+cell]*(J(w)V)[nrows+cell][j] without materialising J V (r from bfd_rom_residual on an
+ * unweighted mesh).  Replaces one snapshot's iteration of compute_ECSW_training_matrix_2D
+ * (:2805-2814: residual, exact Jacobian, J.dot(basis), the cell loop). */
+int bfd_ecsw_c_fused(const bfd_rom_mesh *mesh, const double *w, const double *r, const double *V, int k,
+                     double *C, size_t ldc, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

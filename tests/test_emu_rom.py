@@ -94,6 +94,9 @@ def test_training_matrix_block(lib, golden):
         blk = np.zeros((k, N))
         assert lib.bfd_ecsw_c_block(N, k, E.ptr(r), E.ptr(JV), E.ptr(blk), N, None) == 0
         Cm[i * k:(i + 1) * k] = blk
+        fused = np.zeros((k, N))           # the same block without the intermediate J V
+        assert lib.bfd_ecsw_c_fused(C.byref(mesh.c), E.ptr(w), E.ptr(r), E.ptr(V), k, E.ptr(fused), N, None) == 0
+        assert np.allclose(fused, blk, rtol=1e-13, atol=1e-16)
     assert np.allclose(Cm, Cref, rtol=1e-11, atol=1e-15)
     assert np.allclose(Cm, orc.ecsw_training_matrix(cur, prev, V, gx, gy, dt, mu), rtol=1e-11, atol=1e-15)
 

@@ -153,7 +153,7 @@ def main():
     ecsw_training_matrix(cur[:, :1], prev[:, :1], V, gx, gy, dt, test_mu, device=dev, out_device=True)
     l0 = lib.bfd_launch_count()
     Cm, ms = timed(lambda: ecsw_training_matrix(cur, prev, V, gx, gy, dt, test_mu, device=dev, out_device=True))
-    c_bytes = a.c_snaps * (8 * k * N + 8 * 2 * N * k * 3)           # C block written; V read, JV written and read
+    c_bytes = a.c_snaps * (8 * k * N + 8 * 2 * N * k)               # per snapshot: V read once, the C block written (fused kernel)
     print(json.dumps({"stage": "ecsw_training_matrix", "snapshots": a.c_snaps, "shape": list(Cm.shape),
                       "ms": ms, "ms_per_snapshot": ms / a.c_snaps, "bytes_model": c_bytes,
                       "GBps": c_bytes / ms / 1e6, "frac_of_hbm_peak": c_bytes / ms / 1e6 / hbm,
