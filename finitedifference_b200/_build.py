@@ -7,7 +7,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-SOURCES = ["runtime.cu", "fom.cu", "ops.cu", "rom.cu"]
+SOURCES = ["runtime.cu", "fom.cu", "ops.cu", "rom.cu", "rom_grid.cu"]
 OUT = os.path.join(HERE, "_burgers_b200.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--use_fast_math=false"]
@@ -28,11 +28,26 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not _stale(OUT, deps):
         return OUT
     flags = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")]
-    cmd = [nvcc, *flags, "-shared", "-o", OUT, *srcs, "-lcudart"]
     if verbose:
-        cmd.insert(1, "-Xptxas=-v")
-        print(" ".join(cmd), file=sys.stderr)
-    subprocess.run(cmd, check=True)
+        flags = ["-Xptxas=-v"] + flags
+    # one object per source (only what changed is recompiled), then one shared library
+    objdir = os.path.join(HERE, "..", "build", "obj")
+    os.makedirs(objdir, exist_ok=True)
+    common = [d for d in deps if not d.endswith(".cu")]
+    objs, jobs = [], []
+    for src in srcs:
+        obj = os.path.join(objdir, os.path.basename(src) + ".o")
+        objs.append(obj)
+        if force or _stale(obj, [src] + common):
+            cmd = [nvcc, *flags, "-c", src, "-o", obj]
+            if verbose:
+                print(" ".join(cmd), file=sys.stderr)
+            jobs.append(subprocess.Popen(cmd))
+    for j in jobs:
+        if j.wait() != 0:
+            raise subprocess.CalledProcessError(j.returncode, j.args)
+    subprocess.run([nvcc, *[f for f in flags if f != "-Xptxas=-v"], "-shared", "-o", OUT, *objs, "-lcudart"],
+                   check=True)
     return OUT
 
 

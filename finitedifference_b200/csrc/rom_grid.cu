@@ -1,0 +1,170 @@
+// J(w) V on the WHOLE structured grid (the LSPG PROM and the ECSW training matrix): the same rows
+// as rom_jv_kernel (csrc/rom.cu), computed by walking the grid instead of gathering through index
+// tables.
+//
+// Replaces inviscid_burgers_exact_jac2D (BurgersFD_CleanFine/hypernet2D.py:2703-2732) followed by
+// J.dot(basis) at :1993 (gauss_newton_LSPG) and :2812 (compute_ECSW_training_matrix_2D).
+//
+// Why a second kernel: the gather version reads 8 basis rows per (cell, mode) from L2 -- own,
+// left, and the two cells of the y-difference, u and v each -- i.e. 4x the basis per call, and
+// runs at the L2's pace (0.91 ms at 750^2, k = 95: 29 % of the HBM roof).  On the full grid the
+// neighbours are known:
+//   * left (r, c-1): the cell this warp handled one step earlier -> registers;
+//   * y-difference cells A(r, c), B(r, c): B(r, c) = A(r-1, c) both for the exact operator
+//     (A = own cell, get_ops :2509-2520) and for the operator inviscid_burgers_implicit2D_LSPG
+//     builds at :167 (A = the transposed cell (c, r)), so a warp that owns R
+//     consecutive grid rows loads R+1 A-rows for R rows of output.
+// A warp walks a segment of columns for R rows; lane = mode (MC chunks of 32 modes per lane).
+// Loads per (cell, mode): 2 (R+1)/R for the exact operator (3 at R = 2), 2 + 2 (R+1)/R for the
+// :167 operator (5 at R = 2) instead of 8.  Measured at 750^2, k = 95 (profiles/r01_bench_rom.jsonl):
+// 0.44 ms (exact, was 0.89) and 0.58 ms (:167, was 0.91).  HBM: V once (+ once more along the transposed walk
+// for :167) + J V written.
+#include "common.cuh"
+
+namespace bfd {
+
+struct JvGridArgs {
+    int nx, ny, k, seg_len, nseg, ngroups;
+    const double *cx, *cxl, *cy, *cyd;      // per row i = r*nx + c (bfd_rom_mesh tables)
+    const double *w, *V, *rw;               // state, basis [2N][k], optional residual for the C block
+    double *JV;                             // [2N][k]
+};
+
+template <int R, int MC, bool TRANSPOSED>
+__global__ void __launch_bounds__(128) rom_jv_grid_kernel(const JvGridArgs a) {
+    const int nx = a.nx, ny = a.ny, k = a.k;
+    const size_t N = (size_t)nx * ny;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int jbase = blockIdx.y * (32 * MC) + lane;
+    bool jok[MC];
+    int joff[MC];
+#pragma unroll
+    for (int m = 0; m < MC; ++m) {
+        jok[m] = jbase + 32 * m < k;
+        joff[m] = jok[m] ? jbase + 32 * m : 0;
+    }
+    const double *__restrict__ V = a.V;
+    const double *__restrict__ w = a.w;
+    const long long ntasks = (long long)a.ngroups * a.nseg;
+    for (long long task = (long long)blockIdx.x * 4 + warp; task < ntasks; task += (long long)gridDim.x * 4) {
+        const int g = (int)(task / a.nseg), s = (int)(task % a.nseg);
+        const int r0 = g * R, c0 = s * a.seg_len;
+        const int c1 = c0 + a.seg_len < nx ? c0 + a.seg_len : nx;
+        // left neighbour (own cell of the previous column), per owned row
+        double Lu[R][MC], Lv[R][MC], wLu[R], wLv[R];
+#pragma unroll
+        for (int rr = 0; rr < R; ++rr) {
+            const int r = r0 + rr;
+            const bool ok = c0 > 0 && r < ny;
+            const size_t cell = ok ? (size_t)r * nx + (c0 - 1) : 0;
+            wLu[rr] = ok ? w[cell] : 0.0;
+            wLv[rr] = ok ? w[N + cell] : 0.0;
+#pragma unroll
+            for (int m = 0; m < MC; ++m) {
+                Lu[rr][m] = ok ? V[cell * k + joff[m]] : 0.0;
+                Lv[rr][m] = ok ? V[(N + cell) * k + joff[m]] : 0.0;
+            }
+        }
+        for (int c = c0; c < c1; ++c) {
+            // A rows r0-1 .. r0+R-1 of the y-difference at this column
+            double Au[R + 1][MC], Av[R + 1][MC], wAu[R + 1], wAv[R + 1];
+#pragma unroll
+            for (int rr = 0; rr <= R; ++rr) {
+                const int r = r0 - 1 + rr;
+                const bool ok = r >= 0 && r < ny;
+                const size_t cell = !ok ? 0 : TRANSPOSED ? (size_t)c * ny + r : (size_t)r * nx + c;
+                wAu[rr] = ok ? w[cell] : 0.0;
+                wAv[rr] = ok ? w[N + cell] : 0.0;
+#pragma unroll
+                for (int m = 0; m < MC; ++m) {
+                    Au[rr][m] = ok ? V[cell * k + joff[m]] : 0.0;
+                    Av[rr][m] = ok ? V[(N + cell) * k + joff[m]] : 0.0;
+                }
+            }
+#pragma unroll
+            for (int rr = 0; rr < R; ++rr) {
+                const int r = r0 + rr;
+                if (r >= ny) break;
+                const size_t cell = (size_t)r * nx + c;
+                double Pu[MC], Pv[MC], wPu, wPv;
+                if (TRANSPOSED) {
+                    wPu = w[cell];
+                    wPv = w[N + cell];
+#pragma unroll
+                    for (int m = 0; m < MC; ++m) {
+                        Pu[m] = V[cell * k + joff[m]];
+                        Pv[m] = V[(N + cell) * k + joff[m]];
+                    }
+                } else {
+                    wPu = wAu[rr + 1];
+                    wPv = wAv[rr + 1];
+#pragma unroll
+                    for (int m = 0; m < MC; ++m) { Pu[m] = Au[rr + 1][m]; Pv[m] = Av[rr + 1][m]; }
+                }
+                const double cx = a.cx[cell], cxl = c > 0 ? a.cxl[cell] : 0.0, cy = a.cy[cell],
+                             cyd = r > 0 ? a.cyd[cell] : 0.0;
+                // 2x2 blocks of the exact Jacobian (:2719-2732), same grouping as rom_jv_kernel
+                const double pxu = cx * wPu, pxv = cx * wPv, lxu = cxl * wLu[rr], lxv = cxl * wLv[rr];
+                const double ayu = cy * wAu[rr + 1], ayv = cy * wAv[rr + 1], byu = cyd * wAu[rr], byv = cyd * wAv[rr];
+                double *ou = a.JV + cell * k, *ov = a.JV + (N + cell) * k;
+#pragma unroll
+                for (int m = 0; m < MC; ++m) {
+                    const double vpu = Pu[m], vpv = Pv[m], vlu = Lu[rr][m], vlv = Lv[rr][m];
+                    const double vau = Au[rr + 1][m], vav = Av[rr + 1][m], vbu = Au[rr][m], vbv = Av[rr][m];
+                    const double ju = vpu + (pxu * vpu - lxu * vlu) + 0.5 * (ayv * vau - byv * vbu) + 0.5 * (ayu * vav - byu * vbv);
+                    const double jv = vpv + 0.5 * (pxv * vpu - lxv * vlu) + (ayv * vav - byv * vbv) + 0.5 * (pxu * vpv - lxu * vlv);
+                    if (jok[m]) {
+                        ou[joff[m]] = ju;
+                        ov[joff[m]] = jv;
+                    }
+                    Lu[rr][m] = vpu;
+                    Lv[rr][m] = vpv;
+                }
+                wLu[rr] = wPu;
+                wLv[rr] = wPv;
+            }
+        }
+    }
+}
+
+template <int R, bool T>
+static int launch_mc(const JvGridArgs &a, int mc, dim3 grid, cudaStream_t st) {
+    switch (mc) {
+    case 1: BFD_LAUNCH((rom_jv_grid_kernel<R, 1, T>), grid, 128, 0, st, a); break;
+    case 2: BFD_LAUNCH((rom_jv_grid_kernel<R, 2, T>), grid, 128, 0, st, a); break;
+    default: BFD_LAUNCH((rom_jv_grid_kernel<R, 3, T>), grid, 128, 0, st, a); break;
+    }
+    BFD_LAUNCHED();
+    return BFD_OK;
+}
+
+}  // namespace bfd
+
+using namespace bfd;
+
+extern "C" int bfd_rom_jv_grid(const bfd_rom_mesh *m, int nx, int ny, int transposed, int rows_per_warp,
+                               const double *w, const double *V, int k, double *JV, void *stream) {
+    if (!m || nx < 1 || ny < 1 || m->nrows != (int64_t)nx * ny || m->ncells != m->nrows) return BFD_EINVAL;
+    if (!m->cx || !m->cxl || !m->cy || !m->cyd || !w || !V || !JV || k < 1) return BFD_EINVAL;
+    if (m->weight) return BFD_EINVAL;                       // weighted rows belong to the sampled mesh
+    if (transposed && nx != ny) return BFD_EINVAL;          // :167 permutes a square grid
+    const int R = rows_per_warp == 4 ? 4 : 2;   // measured at 750^2, k = 95: 2 rows beat 4 (registers -> occupancy)
+    const int mc = k > 64 ? 3 : k > 32 ? 2 : 1;
+    JvGridArgs a{};
+    a.nx = nx; a.ny = ny; a.k = k;
+    a.ngroups = (ny + R - 1) / R;
+    // enough warps to fill 148 SMs several times over, segments of at least 32 columns
+    const int want = 148 * 24;
+    int nseg = (want + a.ngroups - 1) / a.ngroups;
+    if (nseg > (nx + 31) / 32) nseg = (nx + 31) / 32;
+    if (nseg < 1) nseg = 1;
+    a.seg_len = (nx + nseg - 1) / nseg;
+    a.nseg = (nx + a.seg_len - 1) / a.seg_len;
+    a.cx = m->cx; a.cxl = m->cxl; a.cy = m->cy; a.cyd = m->cyd;
+    a.w = w; a.V = V; a.rw = nullptr; a.JV = JV;
+    const long long ntasks = (long long)a.ngroups * a.nseg;
+    dim3 grid((unsigned)BFD_GRID((int)((ntasks + 3) / 4)), (unsigned)((k + 32 * mc - 1) / (32 * mc)));
+    cudaStream_t st = (cudaStream_t)stream;
+    if (R == 2) return transposed ? launch_mc<2, true>(a, mc, grid, st) : launch_mc<2, false>(a, mc, grid, st);
+    return transposed ? launch_mc<4, true>(a, mc, grid, st) : launch_mc<4, false>(a, mc, grid, st);
+}

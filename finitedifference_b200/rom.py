@@ -27,6 +27,9 @@ from .discretisation import stencil_coefficients
 from .fom import _require_cuda
 
 
+JV_ROWS_PER_WARP = 0     # grid rows a warp of bfd_rom_jv_grid owns: 0 = library default, 2 or 4 (tuning)
+
+
 def generate_augmented_mesh(grid_x, grid_y, sample_inds):
     """Sampled cells plus their (r-1, c) and (r, c-1) neighbours: sorted, unique, int64.
 
@@ -96,6 +99,9 @@ class MeshTables:
         lbc = np.where(c == 0, 0.5 * dt * mu[0] ** 2 / den, 0.0)
         self._upload(dict(p=p, xl=xl, yd=yd, ja=ja, jb=jb, cx=cx[c], cxl=cxl[c], cy=cy[r], cyd=cyd[r], src=src,
                           lbc=lbc), ncells, device, weight)
+        if state_cells is None and weight is None and rows.size == n_cells and np.array_equal(p, np.arange(n_cells)):
+            # the whole grid in row order: J V can walk the grid (bfd_rom_jv_grid) instead of gathering
+            self.grid = (nx, ny, int(jacobian == "reference"))
 
     @classmethod
     def from_tables(cls, tables, ncells, device, weight=None):
@@ -103,6 +109,8 @@ class MeshTables:
         self = cls.__new__(cls)
         self._upload(tables, ncells, device, weight)
         return self
+
+    grid = None          # (nx, ny, transposed) when the rows are the whole grid in row order
 
     def _upload(self, t, ncells, device, weight):
         self.nrows, self.ncells, self.device = int(np.asarray(t["p"]).size), int(ncells), device
@@ -137,11 +145,19 @@ class _RomBase:
                                              n2.data_ptr(), self._stream()), self.lib, "bfd_rom_residual")
         return r, float(torch.sqrt(n2).item())
 
-    def jv(self, mesh, w, V):
+    def jv(self, mesh, w, V, out=None, gather=False):
+        """Rows of ``J(w) @ V``: the grid-walking kernel on a whole-grid mesh, the gather kernel on a
+        sampled mesh (or with ``gather=True``)."""
         k = V.shape[1]
-        JV = torch.empty((2 * mesh.nrows, k), dtype=torch.float64, device=self.device)
-        _lib.check(self.lib.bfd_rom_jv(C.byref(mesh.c), w.data_ptr(), V.data_ptr(), k, JV.data_ptr(),
-                                       self._stream()), self.lib, "bfd_rom_jv")
+        JV = torch.empty((2 * mesh.nrows, k), dtype=torch.float64, device=self.device) if out is None else out
+        if mesh.grid is not None and not gather:
+            nx, ny, transposed = mesh.grid
+            _lib.check(self.lib.bfd_rom_jv_grid(C.byref(mesh.c), nx, ny, transposed, JV_ROWS_PER_WARP, w.data_ptr(),
+                                                V.data_ptr(), k, JV.data_ptr(), self._stream()),
+                       self.lib, "bfd_rom_jv_grid")
+        else:
+            _lib.check(self.lib.bfd_rom_jv(C.byref(mesh.c), w.data_ptr(), V.data_ptr(), k, JV.data_ptr(),
+                                           self._stream()), self.lib, "bfd_rom_jv")
         return JV
 
     def gauss_newton(self, res_mesh, jac_mesh, V, y0, wp, max_its=20, relnorm_cutoff=1e-5, min_delta=0.1):

@@ -204,6 +204,18 @@ int bfd_rom_residual(const bfd_rom_mesh *mesh, const double *w, const double *wp
 int bfd_rom_jv(const bfd_rom_mesh *mesh, const double *w, const double *V, int k, double *JV,
                void *stream);
 
+/* The same J V for a mesh that is the WHOLE nx x ny grid in row order (nrows == ncells == nx*ny,
+ * p[i] == i, no weights), computed by walking the grid instead of gathering: left neighbours stay
+ * in registers and a warp that owns `rows_per_warp` (2 or 4; 0 = default) grid rows shares the
+ * y-difference cells between them, so the basis is read ~1.25x (exact operator) instead of 4x.
+ * transposed = 0: the exact operator of get_ops (:2509-2520), ja = p, jb = yd;
+ * transposed = 1: the operator inviscid_burgers_implicit2D_LSPG builds at :167 (nx == ny),
+ *                 ja = (c, r), jb = (c, r-1).
+ * Only the coefficient tables cx, cxl, cy, cyd of `mesh` are read.  Same arithmetic, in the same
+ * order, as bfd_rom_jv.  Replaces inviscid_burgers_exact_jac2D (:2703-2732) + J.dot(basis) (:1993). */
+int bfd_rom_jv_grid(const bfd_rom_mesh *mesh, int nx, int ny, int transposed, int rows_per_warp,
+                    const double *w, const double *V, int k, double *JV, void *stream);
+
 /* Values of the Jacobian rows of `mesh` at state w, 12 per row i at vals[12*i ..], in fixed slots
  * whose columns the caller derives from the index tables (N = ncells):
  *   u row i:      (p) (xl) (ja) (jb) (N+ja) (N+jb)

@@ -50,6 +50,39 @@ def test_full_mesh_residual_and_both_jacobians(lib, golden):
     assert np.max(np.abs(run_jv(lib, quirk, w, V) - g["J_lspg"] @ V)) < 1e-13       # hypernet2D.py:167
 
 
+def run_jv_grid(lib, mesh, nx, ny, transposed, rows_per_warp, w, V):
+    V = np.ascontiguousarray(V)
+    JV = np.full((2 * mesh.nrows, V.shape[1]), np.nan)
+    assert lib.bfd_rom_jv_grid(C.byref(mesh.c), nx, ny, int(transposed), rows_per_warp, E.ptr(w), E.ptr(V),
+                               V.shape[1], E.ptr(JV), None) == 0
+    return JV
+
+
+@pytest.mark.parametrize("nx,ny,k", [(12, 12, 5), (37, 37, 40), (9, 9, 70), (45, 7, 33), (5, 50, 97)])
+def test_grid_walk_jv_equals_gather_jv(lib, nx, ny, k):
+    """bfd_rom_jv_grid (walks the grid, neighbours in registers) against bfd_rom_jv (index tables):
+    same arithmetic in the same order, for the exact operator and -- on square grids -- for the
+    operator hypernet2D.py:167 builds; row counts that are no multiple of the rows a warp owns,
+    mode counts that need 1, 2, 3 chunks of 32 lanes and more than one chunk group."""
+    gx, gy = orc.make_2D_grid(0, 100, 0, 60, nx, ny)
+    gx = gx + 0.3 * np.sin(gx)                                   # non-uniform spacing
+    rng = np.random.default_rng(nx * 100 + k)
+    w = 1.0 + rng.random(2 * nx * ny)
+    V = rng.standard_normal((2 * nx * ny, k))
+    modes = [("exact", 0)] + ([("reference", 1)] if nx == ny else [])
+    for name, transposed in modes:
+        mesh = MeshTables(gx, gy, 0.05, [4.3, 0.021], CPU, jacobian=name)
+        want = run_jv(lib, mesh, w, V)
+        for rows_per_warp in (0, 2, 4):
+            got = run_jv_grid(lib, mesh, nx, ny, transposed, rows_per_warp, w, V)
+            assert np.array_equal(got, want), (name, rows_per_warp, np.nanmax(np.abs(got - want)))
+    if nx != ny:
+        mesh = MeshTables(gx, gy, 0.05, [4.3, 0.021], CPU)
+        JV = np.zeros((2 * nx * ny, k))
+        assert lib.bfd_rom_jv_grid(C.byref(mesh.c), nx, ny, 1, 0, E.ptr(w), E.ptr(V), k, E.ptr(JV), None) == -1
+        assert lib.bfd_rom_jv_grid(C.byref(mesh.c), nx + 1, ny, 0, 0, E.ptr(w), E.ptr(V), k, E.ptr(JV), None) == -1
+
+
 def test_sampled_mesh_matches_reference_rows(lib, golden):
     g = golden("ecsw_ops_n24.npz")
     n, dt, mu = int(g["n"]), float(g["dt"]), list(g["mu"])

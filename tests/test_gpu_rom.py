@@ -95,3 +95,30 @@ def test_training_matrix_golden(h, golden):
                                            float(g["dt"]), list(g["mu"]))
     assert Cm.shape == g["C"].shape
     assert np.allclose(Cm, g["C"], rtol=1e-11, atol=1e-15)
+
+
+@pytest.mark.parametrize("n,k", [(97, 95), (64, 20), (130, 40)])
+def test_grid_walk_jv_equals_gather_jv(n, k):
+    """bfd_rom_jv_grid against bfd_rom_jv on the device, both operators, 2 and 4 rows per warp."""
+    import torch
+    from finitedifference_b200 import rom
+    gx, gy = orc.make_2D_grid(0, 100, 0, 100, n, n)
+    rng = np.random.default_rng(n + k)
+    base = rom._RomBase()
+    w = base._dev(1.0 + rng.random(2 * n * n))
+    V = base._dev(rng.standard_normal((2 * n * n, k)))
+    for mode in ("exact", "reference"):
+        mesh = rom.MeshTables(gx, gy, 0.05, [4.75, 0.02], base.device, jacobian=mode)
+        assert mesh.grid == (n, n, int(mode == "reference"))
+        want = base.jv(mesh, w, V, gather=True)
+        for rows in (0, 2, 4):
+            rom.JV_ROWS_PER_WARP = rows
+            try:
+                got = base.jv(mesh, w, V)
+            finally:
+                rom.JV_ROWS_PER_WARP = 0
+            assert torch.allclose(got, want, rtol=1e-14, atol=1e-14), (mode, rows, float((got - want).abs().max()))
+    Jo = orc.jacobian(w.cpu().numpy(), 0.05, *orc.lifted_operators(gx, gy)) if n <= 64 else None
+    if Jo is not None:
+        mesh = rom.MeshTables(gx, gy, 0.05, [4.75, 0.02], base.device)
+        assert np.max(np.abs(base.jv(mesh, w, V).cpu().numpy() - Jo @ V.cpu().numpy())) < 1e-12

@@ -86,6 +86,15 @@ def main():
     wp = snaps[a.lspg_steps - 1].contiguous()
     _, jv_ms = timed(lambda: lspg.jv(lspg.jac_mesh, w, V), 5)
     _, res_ms = timed(lambda: lspg.residual(lspg.res_mesh, w, wp), 5)
+    from finitedifference_b200 import rom as rom_mod
+    from finitedifference_b200.rom import MeshTables
+    variants = {}
+    for mode, mesh in (("reference", lspg.jac_mesh), ("exact", lspg.res_mesh)):
+        _, variants[f"{mode}_gather_ms"] = timed(lambda: lspg.jv(mesh, w, V, gather=True), 5)
+        for rows in (2, 4):
+            rom_mod.JV_ROWS_PER_WARP = rows
+            _, variants[f"{mode}_grid_rows{rows}_ms"] = timed(lambda: lspg.jv(mesh, w, V), 5)
+        rom_mod.JV_ROWS_PER_WARP = 0
     JV = lspg.jv(lspg.jac_mesh, w, V)
     _, gram_ms = timed(lambda: JV.T @ JV, 5)
     _, vy_ms = timed(lambda: V @ red[1], 5)
@@ -95,7 +104,7 @@ def main():
         "ms_per_step": ms / a.lspg_steps, "steps_per_s": 1e3 * a.lspg_steps / ms, "wall_s": wall,
         "kernels_launched": lib.bfd_launch_count() - l0,
         "rom_jv_kernel": {"ms": jv_ms, "algorithmic_bytes": jv_bytes, "GBps": jv_bytes / jv_ms / 1e6,
-                          "frac_of_hbm_peak": jv_bytes / jv_ms / 1e6 / hbm},
+                          "frac_of_hbm_peak": jv_bytes / jv_ms / 1e6 / hbm, "variants": variants},
         "rom_residual_kernel": {"ms": res_ms, "algorithmic_bytes": N * (32 + 16 + 3 * 4 + 6 * 8),
                                 "GBps": N * (32 + 16 + 3 * 4 + 6 * 8) / res_ms / 1e6},
         "gram_cublas": {"ms": gram_ms, "flop": 2.0 * 2 * N * k * k, "TFLOPs": 2.0 * 2 * N * k * k / gram_ms / 1e9},
