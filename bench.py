@@ -153,7 +153,9 @@ def main():
     ap.add_argument("--non-strict", action="store_true", help="do not redo over-speculated steps")
     ap.add_argument("--num-steps", type=int, default=NUM_STEPS, help="time steps per trajectory (500 = the named config)")
     ap.add_argument("--grid", type=int, default=GRID_N)
-    ap.add_argument("--e2e-mu", type=int, default=2)
+    ap.add_argument("--e2e-mu", type=int, default=24, help="samples per end-to-end step (<= mu-per-gpu)")
+    ap.add_argument("--e2e-group", type=int, default=2, help="samples a sweep worker advances together")
+    ap.add_argument("--e2e-workers", type=int, default=3, help="sweep worker threads / streams")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -249,32 +251,32 @@ def main():
                                    "SASS count of FP64 instructions per cell-update at 4 solves"},
                 "steps_redone": redone}
 
-    # end to end through the drop-in API: host w0 in, (2N, T+1) host snapshot arrays out
+    # end to end through the public sweep API: host w0 in, every (2N, T+1) snapshot array out to pinned
+    # host memory (finitedifference_b200/sweep.py: groups of samples on worker streams, the copies of
+    # one group overlapping the sweeps of the next; host buffers recycled through a pool)
     del solver
     torch.cuda.empty_cache()
+    from finitedifference_b200.sweep import SnapshotSweep
     Be = max(1, min(args.e2e_mu, B))
     mus_e = mus[:Be]
-    w0_host = torch.ones(2 * cells, dtype=torch.float64).pin_memory()
-    out_host = [torch.empty((2 * cells, T + 1), dtype=torch.float64).pin_memory() for _ in range(Be)]
-    stage = torch.empty((2 * cells, T + 1), dtype=torch.float64, device=dev)
+    w0_np = np.ones(2 * cells)
+    sweep = SnapshotSweep(gx, gy, DT, T, device=dev, group=args.e2e_group, workers=args.e2e_workers, **skw)
+    seen = {}
 
-    def e2e_step():
-        s = FomSolver(gx, gy, DT, T, mus_e, device=dev, **skw)
-        s.set_initial(w0_host.to(dev, non_blocking=True))
-        s.run()
-        for m in range(Be):
-            s.snapshots_device(m, layout=1, out=stage)
-            out_host[m].copy_(stage, non_blocking=False)
-        return s
+    def sink(i, mu, snaps):
+        # the trajectory is on the host: first column is w0, last column is the final state
+        seen[i] = (float(snaps[::4099, 0].sum()), float(snaps[::4099, -1].sum()))
 
-    e2e_step()
+    sweep.run(w0_np, mus_e[:args.e2e_group * args.e2e_workers], sink=sink)        # warm-up: buffers, solvers
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    t0 = time.perf_counter()
     e2e_reps = max(1, min(args.steps, 2))
+    t0 = time.perf_counter()
     for _ in range(e2e_reps):
-        e2e_step()
+        seen.clear()
+        sweep.run(w0_np, mus_e, sink=sink)
+        assert len(seen) == Be and all(np.isfinite(v[1]) and v[0] == len(w0_np[::4099]) for v in seen.values()), seen
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     if world > 1:
@@ -282,9 +284,13 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
     e2e = {"value": world * Be * cells * T * e2e_reps / e2e_s, "unit": UNIT,
-           "h2d_bytes_per_step": int(w0_host.numel() * 8),
+           "h2d_bytes_per_step": int(w0_np.nbytes),
            "d2h_bytes_per_step": int(Be * 2 * cells * (T + 1) * 8),
-           "mu_per_gpu": Be, "seconds_per_step": e2e_s / e2e_reps}
+           "mu_per_gpu": Be, "seconds_per_step": e2e_s / e2e_reps,
+           "d2h_GBps_per_gpu": Be * 2 * cells * (T + 1) * 8 * e2e_reps / e2e_s / 1e9,
+           "api": f"SnapshotSweep(group={args.e2e_group}, workers={args.e2e_workers}).run(w0, mus, sink): every "
+                  "(2N, T+1) trajectory copied to pinned host memory and handed to the sink"}
+    del sweep
 
     if rank == 0:
         cb = None

@@ -35,7 +35,7 @@ int record_cuda_error(cudaError_t e, const char *where);
 
 #define BFD_LAUNCHED()                                                          \
     do {                                                                        \
-        ++bfd::g_launches;                                                      \
+        __atomic_fetch_add(&bfd::g_launches, 1, __ATOMIC_RELAXED);                                                      \
         cudaError_t _e = cudaGetLastError();                                    \
         if (_e != cudaSuccess) return bfd::record_cuda_error(_e, "kernel launch"); \
     } while (0)

@@ -70,6 +70,22 @@ class FomSolver:
         _lib.check(rc, self.lib, what)
 
     # -- API -------------------------------------------------------------------------------
+    def set_parameters(self, mus) -> None:
+        """Replace the parameter samples (same batch size): the workspace and the grid coefficients
+        are kept, only the per-sample source / inlet terms are recomputed and uploaded."""
+        mus = np.atleast_2d(np.asarray(mus, dtype=np.float64))
+        if mus.shape[0] != self.batch:
+            raise ValueError(f"{mus.shape[0]} samples given, the solver holds {self.batch}")
+        self.mus = mus
+        src, lbc = parameter_terms(self.grid_x, self.grid_y, self.dt, self.mus)
+        with torch.cuda.device(self.device):
+            st = torch.cuda.current_stream(self.device)
+            for t, a in ((self._coef_t[4], src), (self._coef_t[5], lbc)):
+                h = torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64))
+                t.copy_(h.to(self.device, non_blocking=False).view_as(t))
+            st.synchronize()
+        self._ready = False
+
     def set_initial(self, w0) -> None:
         """``w0``: (2N,) broadcast to every sample, or (batch, 2N); NumPy or CUDA tensor."""
         n2 = 2 * self.nx * self.ny

@@ -31,7 +31,7 @@ __all__ = [
     "compute_ECSW_training_matrix_2D",
     "make_ddx", "get_ops", "inviscid_burgers_res2D", "inviscid_burgers_res2D_alt", "inviscid_burgers_res2D_ecsw",
     "inviscid_burgers_exact_jac2D", "inviscid_burgers_exact_jac2D_ecsw",
-    "load_or_compute_snaps", "param_to_snap_fn", "get_saved_params", "compute_error",
+    "load_or_compute_snaps", "compute_snaps_to_cache", "param_to_snap_fn", "get_saved_params", "compute_error",
 ]
 
 
@@ -152,6 +152,24 @@ def load_or_compute_snaps(mu, grid_x, grid_y, w0, dt, num_steps, snap_folder="pa
         print("Elapsed time: {:3.3e}".format(time.time() - t0))
         np.save(snap_fn, snaps)
     return snaps
+
+
+def compute_snaps_to_cache(mus, grid_x, grid_y, w0, dt, num_steps, snap_folder="param_snaps", *, device=None,
+                           **sweep_kw):
+    """``load_or_compute_snaps`` for a list of parameters: the missing trajectories are computed
+    together (``SnapshotSweep``: groups of samples on worker streams) and written by the worker
+    threads as they reach the host, under the reference's file names.  Returns the file names, in
+    the order of ``mus``; ``np.load(fn, mmap_mode="r")`` gives the ``(2N, T+1)`` array."""
+    from .sweep import SnapshotSweep, save_sink
+    if not os.path.exists(snap_folder):
+        os.makedirs(snap_folder)
+    names = [param_to_snap_fn(list(mu), snap_folder=snap_folder) for mu in mus]
+    saved = get_saved_params(snap_folder=snap_folder)
+    todo = [i for i, fn in enumerate(names) if fn not in saved]
+    if todo:
+        sweep = SnapshotSweep(grid_x, grid_y, dt, num_steps, device=device, **sweep_kw)
+        sweep.run(w0, [mus[i] for i in todo], sink=save_sink(snap_folder))
+    return names
 
 
 def compute_error(rom_snaps, hdm_snaps):

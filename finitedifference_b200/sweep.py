@@ -1,0 +1,176 @@
+"""Snapshot generation for many parameter samples with the results on the HOST.
+
+The reference loops ``load_or_compute_snaps`` over the training parameters serially
+(run_prom.py:59-71, train_autoencoder.py:63-72): one 4.5 GB ``(2N, T+1)`` array per mu on the fine
+grid.  On a B200 the trajectories themselves take 7.5 ms per mu (24 advancing together), so what
+a sweep with host output costs is the PCIe link: 85 ms per mu at 53 GB/s.  ``SnapshotSweep`` keeps
+that link busy from the first finished group on:
+
+* ``workers`` host threads, each with its own CUDA stream, ``FomSolver`` (``group`` samples) and
+  device staging buffers; a worker advances its group, exports it to the reference's
+  ``(2N, T+1)`` C-order layout on the device and copies it to pinned host memory, while the other
+  workers are in other phases -- copies of one group overlap the sweeps of the next;
+* results land in caller-owned host buffers (``out``) or in a small pool of pinned buffers that
+  are handed to ``sink(index, mu, snaps)`` and recycled when the sink returns (e.g. an ``.npy``
+  writer: ``save_sink``), so a sweep of any length needs ``pool`` x 4.5 GB of pinned memory.
+
+There is no collective and no CPU path: samples are independent, every
+arithmetic operation happens in csrc/fom.cu.
+"""
+from __future__ import annotations
+
+import os
+import queue
+import threading
+
+import numpy as np
+import torch
+
+from . import _lib
+from .fom import FomSolver, _require_cuda
+
+
+def save_sink(snap_folder="param_snaps", name_fn=None):
+    """A sink that writes ``param_snaps/mu1_<..>+mu2_<..>.npy`` files interchangeable with the
+    reference's cache (``load_or_compute_snaps``, hypernet2D.py:3187-3221)."""
+    from .hypernet2D import param_to_snap_fn
+    os.makedirs(snap_folder, exist_ok=True)
+
+    def sink(index, mu, snaps):
+        fn = name_fn(mu) if name_fn else param_to_snap_fn(list(mu), snap_folder=snap_folder)
+        np.save(fn, snaps)
+    return sink
+
+
+class SnapshotSweep:
+    """FOM trajectories of a list of parameter samples, delivered to the host as they finish."""
+
+    def __init__(self, grid_x, grid_y, dt, num_steps, device=None, group=2, workers=3, pool=None, strict=True,
+                 **solver_kw):
+        self.device = _require_cuda(device)
+        self.grid_x, self.grid_y = np.asarray(grid_x, dtype=np.float64), np.asarray(grid_y, dtype=np.float64)
+        self.dt, self.num_steps = float(dt), int(num_steps)
+        self.group, self.workers = max(1, int(group)), max(1, int(workers))
+        self.pool_size = int(pool) if pool else self.group * self.workers
+        self.solver_kw = dict(strict=strict, **solver_kw)
+        self.n2 = 2 * (self.grid_x.size - 1) * (self.grid_y.size - 1)
+        self._pool = None
+        self._pool_lock = threading.Lock()
+        self._solvers = {}        # (worker, batch) -> FomSolver
+        self._stage = {}          # worker -> list of device staging tensors
+        self._streams = [torch.cuda.Stream(device=self.device) for _ in range(self.workers)]
+        self.launches = 0
+        self.steps_redone = 0
+
+    # -- buffers -----------------------------------------------------------------------------
+    def host_buffer(self):
+        """One pinned ``(2N, T+1)`` float64 buffer (what ``out`` entries should be for full speed)."""
+        return torch.empty((self.n2, self.num_steps + 1), dtype=torch.float64).pin_memory()
+
+    def _get_pool(self):
+        with self._pool_lock:
+            if self._pool is None:
+                pool = queue.Queue()
+                for _ in range(self.pool_size):
+                    pool.put(self.host_buffer())
+                self._pool = pool
+        return self._pool
+
+    def _solver(self, wid, batch, mus):
+        key = (wid, batch)
+        s = self._solvers.get(key)
+        if s is None:
+            s = FomSolver(self.grid_x, self.grid_y, self.dt, self.num_steps, mus, device=self.device,
+                          **self.solver_kw)
+            self._solvers[key] = s
+        else:
+            s.set_parameters(mus)
+        return s
+
+    # -- the sweep ---------------------------------------------------------------------------
+    def run(self, w0, mus, out=None, sink=None):
+        """Advance every sample of ``mus`` from ``w0`` ((2N,) NumPy, host).
+
+        ``out``: list of host buffers, one per sample (pinned torch tensors from ``host_buffer()`` or
+        C-contiguous NumPy arrays), filled in place and returned.  Without ``out`` the trajectories
+        go through the pinned pool to ``sink(index, mu, snaps_ndarray)``, called from the worker
+        threads, the buffer being reused after the sink returns; with neither, fresh pinned
+        buffers are allocated and returned as NumPy arrays (slow: pinning 4.5 GB per sample).
+        Returns the list of host arrays (``out`` mode) or ``None`` (sink mode).
+        """
+        mus = [list(m)[:2] for m in mus]
+        n = len(mus)
+        if out is not None and len(out) != n:
+            raise ValueError("one output buffer per parameter sample")
+        if out is None and sink is None:
+            out = [self.host_buffer() for _ in range(n)]
+        w0 = np.ascontiguousarray(np.asarray(w0, dtype=np.float64).ravel())
+        if w0.size != self.n2:
+            raise ValueError(f"w0 has {w0.size} entries, expected {self.n2}")
+        w0_pinned = torch.from_numpy(w0).pin_memory()
+        groups = queue.Queue()
+        for lo in range(0, n, self.group):
+            groups.put(list(range(lo, min(lo + self.group, n))))
+        errors = []
+        stats = {"launches": 0, "redone": 0}
+        lock = threading.Lock()
+
+        def work(wid):
+            stream = self._streams[wid]
+            try:
+                with torch.cuda.device(self.device), torch.cuda.stream(stream):
+                    w0_dev = w0_pinned.to(self.device, non_blocking=True)
+                    while not errors:
+                        try:
+                            idx = groups.get_nowait()
+                        except queue.Empty:
+                            break
+                        solver = self._solver(wid, len(idx), [mus[i] for i in idx])
+                        solver.set_initial(w0_dev)
+                        solver.run()
+                        with lock:
+                            stats["launches"] += solver.launches
+                            stats["redone"] += solver.steps_redone
+                        stage = self._stage.setdefault(wid, [])
+                        while len(stage) < len(idx):
+                            stage.append(torch.empty((self.n2, self.num_steps + 1), dtype=torch.float64,
+                                                     device=self.device))
+                        held = []
+
+                        def flush():
+                            stream.synchronize()
+                            while held:
+                                i, buf = held.pop(0)
+                                try:
+                                    sink(i, mus[i], buf.numpy())
+                                finally:
+                                    self._pool.put(buf)
+
+                        for j, i in enumerate(idx):
+                            solver.snapshots_device(j, layout=1, out=stage[j])
+                            if out is not None:
+                                dst = out[i] if isinstance(out[i], torch.Tensor) else torch.from_numpy(out[i])
+                            else:
+                                pool = self._get_pool()
+                                try:
+                                    dst = pool.get_nowait()
+                                except queue.Empty:
+                                    flush()             # never wait for a buffer while holding one
+                                    dst = pool.get()
+                                held.append((i, dst))
+                            dst.copy_(stage[j], non_blocking=True)
+                        flush()
+            except BaseException as e:          # noqa: BLE001 - re-raised in the caller's thread
+                errors.append(e)
+
+        threads = [threading.Thread(target=work, args=(w,), daemon=True) for w in range(min(self.workers, groups.qsize()))]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        if errors:
+            raise errors[0]
+        self.launches, self.steps_redone = stats["launches"], stats["redone"]
+        if out is None:
+            return None
+        return [o.numpy() if isinstance(o, torch.Tensor) else o for o in out]
