@@ -46,7 +46,7 @@ class MeshTables:
     """Index and coefficient tables of ``bfd_rom_mesh`` for a set of rows, on the device."""
 
     def __init__(self, grid_x, grid_y, dt, mu, device, rows=None, state_cells=None, weight=None,
-                 jacobian="exact"):
+                 jacobian="exact", inlet="auto"):
         gx = np.asarray(grid_x, dtype=np.float64)
         gy = np.asarray(grid_y, dtype=np.float64)
         nx, ny = gx.size - 1, gy.size - 1
@@ -92,7 +92,9 @@ class MeshTables:
         dx = gx[1:] - gx[:-1]
         xc = (gx[1:] + gx[:-1]) / 2
         src = (dt * 0.02 * np.exp(mu[1] * xc))[c]
-        if state_cells is None:
+        if inlet == "auto":                                               # whose inlet term: the full-grid residual's
+            inlet = "grid" if state_cells is None else "sampled"         # or the sampled-mesh residual's
+        if inlet == "grid":
             den = dx[r] if nx == ny else np.full(rows.shape, dx[0])      # :2582 / :2630 (Q3)
         else:
             den = np.full(rows.shape, dx[0])                              # :2665
@@ -126,13 +128,24 @@ class MeshTables:
 
 
 class _RomBase:
-    def __init__(self, device=None):
-        self.lib = _lib.get_lib()
-        self.device = _require_cuda(device)
+    def __init__(self, device=None, _backend=None):
+        # _backend = (library, torch device): the CPU test-suite passes the SIMT-emulated build of
+        # the same kernels (tests/simt_emu); the product always runs the CUDA library
+        if _backend is None:
+            self.lib = _lib.get_lib()
+            self.device = _require_cuda(device)
+        else:
+            self.lib, self.device = _backend
         self.res_time = self.jac_time = self.ls_time = 0.0
 
     def _stream(self):
+        if self.device.type != "cuda":
+            return None
         return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _sync(self):
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
 
     def _dev(self, a):
         return torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(self.device)
@@ -180,7 +193,7 @@ class _RomBase:
                 break
             t0 = time.perf_counter()
             JV = self.jv(jac_mesh, w, V)
-            torch.cuda.synchronize(self.device)
+            self._sync()
             self.jac_time += time.perf_counter() - t0
             t0 = time.perf_counter()
             G = JV.T @ JV                                  # normal equations of lstsq(JV, -f)
@@ -188,7 +201,7 @@ class _RomBase:
             dy = torch.cholesky_solve(b[:, None], torch.linalg.cholesky(G))[:, 0]
             y = y + dy
             w = V @ y
-            torch.cuda.synchronize(self.device)
+            self._sync()
             self.ls_time += time.perf_counter() - t0
         return y, w, resnorms
 
@@ -224,6 +237,132 @@ class LspgSolver(_RomBase):
             history.append(resnorms)
             snaps[i + 1], red[i + 1] = w, y                 # :196: the stored snapshot is basis @ y
         return snaps, red, history
+
+
+class ShardedLspgSolver(_RomBase):
+    """LSPG PROM with the grid rows dealt to the ranks of a process group.
+
+    Rank ``g`` owns a contiguous block of grid rows: it evaluates the residual rows and the
+    ``J V`` rows of its cells and forms its share of the normal equations; one all-reduce of
+    ``[(JV)^T (JV) | (JV)^T f]`` (k x (k+1) doubles, 72 KB at k = 95) and one of ``||f||^2`` per
+    Gauss-Newton iteration are the only exchanges, the reduced state ``y`` is replicated and
+    every rank takes the same stopping decisions from the same reduced numbers
+    (``gauss_newton_LSPG``, hypernet2D.py:1935-2005).  A rank keeps only the basis rows of the
+    state cells its stencils read -- its rows, the row below, and for the :167 operator the
+    transposed cells (a column slab) -- i.e. about 2/world of ``V``; ``w = V y`` is formed locally
+    on exactly those cells, so no halo exchange exists.
+    """
+
+    def __init__(self, grid_x, grid_y, dt, mu, basis, rank=None, world=None, group=None, device=None,
+                 jacobian="reference", _backend=None):
+        import torch.distributed as dist
+        super().__init__(device, _backend)
+        self.dist, self.group = dist, group
+        active = dist.is_available() and dist.is_initialized()
+        self.rank = (dist.get_rank(group) if active else 0) if rank is None else int(rank)
+        self.world = (dist.get_world_size(group) if active else 1) if world is None else int(world)
+        from .sharding import shard_range
+        gx, gy = np.asarray(grid_x, dtype=np.float64), np.asarray(grid_y, dtype=np.float64)
+        nx, ny = gx.size - 1, gy.size - 1
+        self.n_cells, self.mu = nx * ny, list(mu)[:2]
+        block = shard_range(ny, self.rank, self.world)
+        self.row_range = (block.start, block.stop)
+        rows = np.arange(block.start * nx, block.stop * nx, dtype=np.int64)
+        r, c = np.divmod(rows, nx)
+        need = [rows, rows[c >= 1] - 1, rows[r >= 1] - nx]
+        if jacobian == "reference":
+            if nx != ny:
+                raise ValueError("the reference's LSPG operator (hypernet2D.py:167) needs nx == ny")
+            need += [c * ny + r, (c * ny + r - 1)[r >= 1]]
+        elif jacobian != "exact":
+            raise ValueError(jacobian)
+        self.rows = rows
+        self.state_cells = np.unique(np.concatenate(need)).astype(np.int64) if rows.size else rows
+        basis = basis.cpu().numpy() if isinstance(basis, torch.Tensor) else np.asarray(basis, dtype=np.float64)
+        self.k = basis.shape[1]
+        idx = np.concatenate((self.state_cells, self.n_cells + self.state_cells))
+        own = np.concatenate((rows, self.n_cells + rows))
+        self.V_state = self._dev(basis[idx])            # basis on the state cells [u | v]
+        self.V_own = self._dev(basis[own])              # basis on the owned cells [u | v]: y0 and the snapshots
+        if rows.size:
+            self.res_mesh = MeshTables(gx, gy, dt, self.mu, self.device, rows=rows, state_cells=self.state_cells,
+                                       inlet="grid")
+            self.jac_mesh = self.res_mesh if jacobian == "exact" else \
+                MeshTables(gx, gy, dt, self.mu, self.device, rows=rows, state_cells=self.state_cells,
+                           jacobian="reference", inlet="grid")
+
+    def _allreduce(self, t):
+        if self.world > 1:
+            self.dist.all_reduce(t, group=self.group)
+        return t
+
+    def _residual(self, w, wp):
+        """(f_local, ||f|| over all ranks)."""
+        n2 = torch.zeros(1, dtype=torch.float64, device=self.device)
+        if self.rows.size:
+            f = torch.empty(2 * self.rows.size, dtype=torch.float64, device=self.device)
+            _lib.check(self.lib.bfd_rom_residual(C.byref(self.res_mesh.c), w.data_ptr(), wp.data_ptr(), f.data_ptr(),
+                                                 n2.data_ptr(), self._stream()), self.lib, "bfd_rom_residual")
+        else:
+            f = torch.empty(0, dtype=torch.float64, device=self.device)
+        return f, float(torch.sqrt(self._allreduce(n2)).item())
+
+    def _gauss_newton(self, y0, wp, max_its=20, relnorm_cutoff=1e-5, min_delta=0.1):
+        k, V = self.k, self.V_state
+        y = y0.clone()
+        w = V @ y
+        _, init_norm = self._residual(w, wp)
+        resnorms = []
+        for _ in range(max_its):
+            f, resnorm = self._residual(w, wp)
+            resnorms.append(resnorm)
+            if resnorm / init_norm < relnorm_cutoff:
+                break
+            if len(resnorms) > 1 and abs((resnorms[-2] - resnorms[-1]) / resnorms[-2]) < min_delta:
+                break
+            Gb = torch.zeros((k, k + 1), dtype=torch.float64, device=self.device)
+            if self.rows.size:
+                JV = self.jv(self.jac_mesh, w, V)
+                Gb[:, :k] = JV.T @ JV
+                Gb[:, k] = -(JV.T @ f)
+            self._allreduce(Gb)
+            dy = torch.cholesky_solve(Gb[:, k:].contiguous(), torch.linalg.cholesky(Gb[:, :k]))[:, 0]
+            y = y + dy
+            w = V @ y
+        return y, w, resnorms
+
+    def run(self, w0, num_steps):
+        """``w0``: the full (2N,) initial state (host).  Returns ``(snaps_own (T+1, 2*n_own) -- the
+        owned cells' [u | v] --, red_coords (T+1, k), per-step resnorm lists)`` on the device."""
+        w0 = np.asarray(w0.cpu() if isinstance(w0, torch.Tensor) else w0, dtype=np.float64).ravel()
+        own = np.concatenate((self.rows, self.n_cells + self.rows))
+        y = self._allreduce(self.V_own.T @ self._dev(w0[own]))          # :158, summed over the row blocks
+        w = self.V_state @ y                                            # :159 on the cells this rank reads
+        snaps = torch.empty((num_steps + 1, 2 * self.rows.size), dtype=torch.float64, device=self.device)
+        red = torch.empty((num_steps + 1, self.k), dtype=torch.float64, device=self.device)
+        snaps[0], red[0] = self.V_own @ y, y
+        history = []
+        for i in range(num_steps):
+            y, w, resnorms = self._gauss_newton(y, w)
+            history.append(resnorms)
+            snaps[i + 1], red[i + 1] = self.V_own @ y, y
+        return snaps, red, history
+
+    def gather_snapshots(self, snaps_own):
+        """Full ``(2N, T+1)`` NumPy array on every rank from the per-rank row blocks."""
+        T1 = snaps_own.shape[0]
+        parts = [None] * self.world
+        mine = (self.rows, snaps_own.cpu().numpy())
+        if self.world > 1:
+            self.dist.all_gather_object(parts, mine, group=self.group)
+        else:
+            parts = [mine]
+        full = np.empty((2 * self.n_cells, T1))
+        for rows, block in parts:
+            n = rows.size
+            full[rows] = block[:, :n].T
+            full[self.n_cells + rows] = block[:, n:].T
+        return full
 
 
 class EcswSolver(_RomBase):

@@ -122,3 +122,23 @@ def test_grid_walk_jv_equals_gather_jv(n, k):
     if Jo is not None:
         mesh = rom.MeshTables(gx, gy, 0.05, [4.75, 0.02], base.device)
         assert np.max(np.abs(base.jv(mesh, w, V).cpu().numpy() - Jo @ V.cpu().numpy())) < 1e-12
+
+
+@pytest.mark.parametrize("mode", ["reference", "exact"])
+def test_sharded_lspg_one_rank_equals_lspg(h, golden, mode):
+    """ShardedLspgSolver (row blocks + all-reduce of the normal equations; here one rank, the
+    multi-rank cases run on CPU in tests/test_lspg_sharded.py) against LspgSolver and the golden."""
+    from finitedifference_b200.rom import LspgSolver, ShardedLspgSolver
+    g = golden("lspg_n24.npz")
+    n, steps = int(g["n"]), int(g["steps"])
+    gx, gy = h.make_2D_grid(0, 100, 0, 100, n, n)
+    w0 = np.ones(2 * n * n)
+    sh = ShardedLspgSolver(gx, gy, float(g["dt"]), list(g["mu"]), g["basis"], rank=0, world=1, jacobian=mode)
+    snaps_own, red, hist = sh.run(w0, steps)
+    full = sh.gather_snapshots(snaps_own)
+    s1, r1, h1 = LspgSolver(gx, gy, float(g["dt"]), list(g["mu"]), g["basis"], jacobian=mode).run(w0, steps)
+    assert [len(x) for x in hist] == [len(x) for x in h1]
+    assert max(rel(full[:, i], s1[i].cpu().numpy()) for i in range(steps + 1)) < 1e-12
+    if mode == "reference":
+        assert [len(x) for x in hist] == g["gn_its"].tolist()
+        assert max(rel(full[:, i], g["snaps"][:, i]) for i in range(steps + 1)) < TOL
