@@ -260,7 +260,13 @@ def main():
     Be = max(1, min(args.e2e_mu, B))
     mus_e = mus[:Be]
     w0_np = np.ones(2 * cells)
-    sweep = SnapshotSweep(gx, gy, DT, T, device=dev, group=args.e2e_group, workers=args.e2e_workers, **skw)
+    # pinned host buffers: a pool per rank, sized to the host memory the ranks of this box share
+    import psutil
+    buf_bytes = 2 * cells * (T + 1) * 8
+    pool = int(0.35 * psutil.virtual_memory().available / max(world, 1) / buf_bytes)
+    pool = max(2, min(args.e2e_group * args.e2e_workers, pool))
+    sweep = SnapshotSweep(gx, gy, DT, T, device=dev, group=args.e2e_group, workers=args.e2e_workers, pool=pool,
+                          **skw)
     seen = {}
 
     def sink(i, mu, snaps):
@@ -286,7 +292,7 @@ def main():
     e2e = {"value": world * Be * cells * T * e2e_reps / e2e_s, "unit": UNIT,
            "h2d_bytes_per_step": int(w0_np.nbytes),
            "d2h_bytes_per_step": int(Be * 2 * cells * (T + 1) * 8),
-           "mu_per_gpu": Be, "seconds_per_step": e2e_s / e2e_reps,
+           "mu_per_gpu": Be, "seconds_per_step": e2e_s / e2e_reps, "pinned_buffers_per_gpu": pool,
            "d2h_GBps_per_gpu": Be * 2 * cells * (T + 1) * 8 * e2e_reps / e2e_s / 1e9,
            "api": f"SnapshotSweep(group={args.e2e_group}, workers={args.e2e_workers}).run(w0, mus, sink): every "
                   "(2N, T+1) trajectory copied to pinned host memory and handed to the sink"}
