@@ -20,6 +20,7 @@
 // 0.44 ms (exact, was 0.89) and 0.58 ms (:167, was 0.91).  HBM: V once (+ once more along the transposed walk
 // for :167) + J V written.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace bfd {
 
@@ -28,10 +29,19 @@ struct JvGridArgs {
     const double *cx, *cxl, *cy, *cyd;      // per row i = r*nx + c (bfd_rom_mesh tables)
     const double *w, *V, *rw;               // state, basis [2N][k], optional residual for the C block
     double *JV;                             // [2N][k]
+    double *C;                              // CBLOCK: one snapshot's k x N block of the training matrix
+    size_t ldc;
 };
 
-template <int R, int MC, bool TRANSPOSED>
+constexpr int kCSeg = 8;                    // columns per segment of the CBLOCK variant (one 64-byte run per mode)
+
+// CBLOCK (R = 1, exact operator): instead of storing the J V rows, form
+//   C[j, cell] = r_u[cell] (J V)_u[cell, j] + r_v[cell] (J V)_v[cell, j]      (:2813-2814)
+// for the kCSeg cells of the segment, transpose the kCSeg x 32 MC tile through shared memory and
+// write it along cells -- compute_ECSW_training_matrix_2D's cell loop without materialising J V.
+template <int R, int MC, bool TRANSPOSED, bool CBLOCK = false>
 __global__ void __launch_bounds__(128) rom_jv_grid_kernel(const JvGridArgs a) {
+    BFD_SHARED_ARRAY(double, ctile, [CBLOCK ? 4 : 1][CBLOCK ? kCSeg : 1][CBLOCK ? 32 * MC + 1 : 1]);
     const int nx = a.nx, ny = a.ny, k = a.k;
     const size_t N = (size_t)nx * ny;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -113,7 +123,9 @@ __global__ void __launch_bounds__(128) rom_jv_grid_kernel(const JvGridArgs a) {
                     const double vau = Au[rr + 1][m], vav = Av[rr + 1][m], vbu = Au[rr][m], vbv = Av[rr][m];
                     const double ju = vpu + (pxu * vpu - lxu * vlu) + 0.5 * (ayv * vau - byv * vbu) + 0.5 * (ayu * vav - byu * vbv);
                     const double jv = vpv + 0.5 * (pxv * vpu - lxv * vlu) + (ayv * vav - byv * vbv) + 0.5 * (pxu * vpv - lxu * vlv);
-                    if (jok[m]) {
+                    if (CBLOCK) {
+                        ctile[warp][c - c0][32 * m + lane] = a.rw[cell] * ju + a.rw[N + cell] * jv;
+                    } else if (jok[m]) {
                         ou[joff[m]] = ju;
                         ov[joff[m]] = jv;
                     }
@@ -123,6 +135,16 @@ __global__ void __launch_bounds__(128) rom_jv_grid_kernel(const JvGridArgs a) {
                 wLu[rr] = wPu;
                 wLv[rr] = wPv;
             }
+        }
+        if (CBLOCK) {
+            __syncwarp();
+            const int ncol = c1 - c0, j0 = blockIdx.y * (32 * MC);
+            for (int e = lane; e < kCSeg * 32 * MC; e += 32) {
+                const int mode = e / kCSeg, cl = e % kCSeg;
+                if (cl < ncol && j0 + mode < k && r0 < ny)
+                    a.C[(size_t)(j0 + mode) * a.ldc + (size_t)r0 * nx + c0 + cl] = ctile[warp][cl][mode];
+            }
+            __syncwarp();
         }
     }
 }
@@ -138,6 +160,16 @@ static int launch_mc(const JvGridArgs &a, int mc, dim3 grid, cudaStream_t st) {
     return BFD_OK;
 }
 
+static int launch_cblock(const JvGridArgs &a, int mc, dim3 grid, cudaStream_t st) {
+    switch (mc) {
+    case 1: BFD_LAUNCH((rom_jv_grid_kernel<1, 1, false, true>), grid, 128, 0, st, a); break;
+    case 2: BFD_LAUNCH((rom_jv_grid_kernel<1, 2, false, true>), grid, 128, 0, st, a); break;
+    default: BFD_LAUNCH((rom_jv_grid_kernel<1, 3, false, true>), grid, 128, 0, st, a); break;
+    }
+    BFD_LAUNCHED();
+    return BFD_OK;
+}
+
 }  // namespace bfd
 
 using namespace bfd;
@@ -148,23 +180,46 @@ extern "C" int bfd_rom_jv_grid(const bfd_rom_mesh *m, int nx, int ny, int transp
     if (!m->cx || !m->cxl || !m->cy || !m->cyd || !w || !V || !JV || k < 1) return BFD_EINVAL;
     if (m->weight) return BFD_EINVAL;                       // weighted rows belong to the sampled mesh
     if (transposed && nx != ny) return BFD_EINVAL;          // :167 permutes a square grid
-    const int R = rows_per_warp == 4 ? 4 : 2;   // measured at 750^2, k = 95: 2 rows beat 4 (registers -> occupancy)
-    const int mc = k > 64 ? 3 : k > 32 ? 2 : 1;
+    const int R = rows_per_warp == 4 ? 4 : rows_per_warp == 2 ? 2 : rows_per_warp == 1 ? 1 : (transposed ? 2 : 1);   // measured at 750^2, k = 95: 2 rows beat 4 (registers -> occupancy)
+    int mc = k > 64 ? 3 : k > 32 ? 2 : 1;
+    if (const char *e = getenv("BFD_JV_MC")) { const int v = atoi(e); if (v >= 1 && v < mc) mc = v; }   // tuning
     JvGridArgs a{};
     a.nx = nx; a.ny = ny; a.k = k;
     a.ngroups = (ny + R - 1) / R;
-    // enough warps to fill 148 SMs several times over, segments of at least 32 columns
-    const int want = 148 * 24;
-    int nseg = (want + a.ngroups - 1) / a.ngroups;
-    if (nseg > (nx + 31) / 32) nseg = (nx + 31) / 32;
-    if (nseg < 1) nseg = 1;
-    a.seg_len = (nx + nseg - 1) / nseg;
+    // Short segments: the warps in flight then read neighbouring stretches of the basis, which is
+    // what DRAM pages like (measured at 750^2, k = 95: segments of 75 columns 0.44 / 0.59 ms, of
+    // 8-16 columns 0.34 / 0.49 ms for the exact / :167 operator); the price is one extra left
+    // neighbour load from L2 per segment.
+    a.seg_len = transposed ? 16 : 8;
+    if (a.seg_len > nx) a.seg_len = nx;
+    if (const char *e = getenv("BFD_JV_SEG")) { const int v = atoi(e); if (v >= 1) a.seg_len = v < nx ? v : nx; }   // tuning
     a.nseg = (nx + a.seg_len - 1) / a.seg_len;
     a.cx = m->cx; a.cxl = m->cxl; a.cy = m->cy; a.cyd = m->cyd;
     a.w = w; a.V = V; a.rw = nullptr; a.JV = JV;
     const long long ntasks = (long long)a.ngroups * a.nseg;
     dim3 grid((unsigned)BFD_GRID((int)((ntasks + 3) / 4)), (unsigned)((k + 32 * mc - 1) / (32 * mc)));
     cudaStream_t st = (cudaStream_t)stream;
+    if (R == 1) return transposed ? launch_mc<1, true>(a, mc, grid, st) : launch_mc<1, false>(a, mc, grid, st);
     if (R == 2) return transposed ? launch_mc<2, true>(a, mc, grid, st) : launch_mc<2, false>(a, mc, grid, st);
     return transposed ? launch_mc<4, true>(a, mc, grid, st) : launch_mc<4, false>(a, mc, grid, st);
+}
+
+extern "C" int bfd_ecsw_c_grid(const bfd_rom_mesh *m, int nx, int ny, const double *w, const double *r,
+                               const double *V, int k, double *Cblk, size_t ldc, void *stream) {
+    if (!m || nx < 1 || ny < 1 || m->nrows != (int64_t)nx * ny || m->ncells != m->nrows) return BFD_EINVAL;
+    if (!m->cx || !m->cxl || !m->cy || !m->cyd || !w || !r || !V || !Cblk || k < 1 || m->weight) return BFD_EINVAL;
+    if (ldc < (size_t)m->nrows) return BFD_EINVAL;
+    const int mc = k > 64 ? 3 : k > 32 ? 2 : 1;
+    JvGridArgs a{};
+    a.nx = nx; a.ny = ny; a.k = k;
+    a.ngroups = ny;
+    a.seg_len = kCSeg < nx ? kCSeg : nx;
+    a.nseg = (nx + a.seg_len - 1) / a.seg_len;
+    a.cx = m->cx; a.cxl = m->cxl; a.cy = m->cy; a.cyd = m->cyd;
+    a.w = w; a.V = V; a.rw = r; a.JV = nullptr; a.C = Cblk; a.ldc = ldc;
+    const long long ntasks = (long long)a.ngroups * a.nseg;
+    long long blocks = (ntasks + 3) / 4;
+    if (blocks > 148 * 64) blocks = 148 * 64;
+    dim3 grid((unsigned)BFD_GRID((int)blocks), (unsigned)((k + 32 * mc - 1) / (32 * mc)));
+    return launch_cblock(a, mc, grid, (cudaStream_t)stream);
 }

@@ -427,7 +427,13 @@ def ecsw_training_matrix(snaps, prev_snaps, basis, grid_x, grid_y, dt, mu, devic
     for i in range(n_snaps):
         w, wp = S[:, i].contiguous(), P[:, i].contiguous()
         r, _ = base.residual(mesh, w, wp)
-        _lib.check(base.lib.bfd_ecsw_c_fused(C.byref(mesh.c), w.data_ptr(), r.data_ptr(), V.data_ptr(), k,
-                                             Cmat[i * k:(i + 1) * k].data_ptr(), n_cells, base._stream()),
-                   base.lib, "bfd_ecsw_c_fused")
+        blk = Cmat[i * k:(i + 1) * k]
+        if mesh.grid is not None and not mesh.grid[2]:
+            _lib.check(base.lib.bfd_ecsw_c_grid(C.byref(mesh.c), mesh.grid[0], mesh.grid[1], w.data_ptr(), r.data_ptr(),
+                                                V.data_ptr(), k, blk.data_ptr(), n_cells, base._stream()),
+                       base.lib, "bfd_ecsw_c_grid")
+        else:
+            _lib.check(base.lib.bfd_ecsw_c_fused(C.byref(mesh.c), w.data_ptr(), r.data_ptr(), V.data_ptr(), k,
+                                                 blk.data_ptr(), n_cells, base._stream()),
+                       base.lib, "bfd_ecsw_c_fused")
     return Cmat if out_device else Cmat.cpu().numpy()

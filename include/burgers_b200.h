@@ -236,6 +236,15 @@ int bfd_ecsw_c_block(int64_t nrows, int k, const double *r, const double *JV, do
 int bfd_ecsw_c_fused(const bfd_rom_mesh *mesh, const double *w, const double *r, const double *V, int k,
                      double *C, size_t ldc, void *stream);
 
+/* bfd_ecsw_c_fused for a mesh that is the whole nx x ny grid in row order (see bfd_rom_jv_grid):
+ * the grid is walked in segments of 8 cells, left neighbours in registers, the 8 x k tile of
+ *   C[j*ldc + cell] = r[cell]*(J(w)V)[cell][j] + r[nrows+cell]*(J(w)V)[nrows+cell][j]
+ * transposed through shared memory and written along cells.  Exact operator of get_ops only (what
+ * compute_ECSW_training_matrix_2D is called with, run_HPROM_ecsw_joshua.py:61-64).
+ * Replaces one snapshot's iteration of compute_ECSW_training_matrix_2D (:2805-2814). */
+int bfd_ecsw_c_grid(const bfd_rom_mesh *mesh, int nx, int ny, const double *w, const double *r,
+                    const double *V, int k, double *C, size_t ldc, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -76,8 +76,14 @@ def test_grid_walk_jv_equals_gather_jv(lib, nx, ny, k):
         for rows_per_warp in (0, 2, 4):
             got = run_jv_grid(lib, mesh, nx, ny, transposed, rows_per_warp, w, V)
             assert np.array_equal(got, want), (name, rows_per_warp, np.nanmax(np.abs(got - want)))
+    mesh = MeshTables(gx, gy, 0.05, [4.3, 0.021], CPU)
+    r = rng.standard_normal(2 * nx * ny)
+    fused, walked = np.zeros((k, nx * ny + 3)), np.full((k, nx * ny + 3), np.nan)
+    assert lib.bfd_ecsw_c_fused(C.byref(mesh.c), E.ptr(w), E.ptr(r), E.ptr(V), k, E.ptr(fused), nx * ny + 3, None) == 0
+    assert lib.bfd_ecsw_c_grid(C.byref(mesh.c), nx, ny, E.ptr(w), E.ptr(r), E.ptr(V), k, E.ptr(walked), nx * ny + 3,
+                               None) == 0
+    assert np.array_equal(walked[:, :nx * ny], fused[:, :nx * ny]) and np.isnan(walked[:, nx * ny:]).all()
     if nx != ny:
-        mesh = MeshTables(gx, gy, 0.05, [4.3, 0.021], CPU)
         JV = np.zeros((2 * nx * ny, k))
         assert lib.bfd_rom_jv_grid(C.byref(mesh.c), nx, ny, 1, 0, E.ptr(w), E.ptr(V), k, E.ptr(JV), None) == -1
         assert lib.bfd_rom_jv_grid(C.byref(mesh.c), nx + 1, ny, 0, 0, E.ptr(w), E.ptr(V), k, E.ptr(JV), None) == -1
@@ -130,6 +136,9 @@ def test_training_matrix_block(lib, golden):
         fused = np.zeros((k, N))           # the same block without the intermediate J V
         assert lib.bfd_ecsw_c_fused(C.byref(mesh.c), E.ptr(w), E.ptr(r), E.ptr(V), k, E.ptr(fused), N, None) == 0
         assert np.allclose(fused, blk, rtol=1e-13, atol=1e-16)
+        walked = np.full((k, N), np.nan)   # ... and by walking the grid (bfd_ecsw_c_grid)
+        assert lib.bfd_ecsw_c_grid(C.byref(mesh.c), n, n, E.ptr(w), E.ptr(r), E.ptr(V), k, E.ptr(walked), N, None) == 0
+        assert np.array_equal(walked, fused)
     assert np.allclose(Cm, Cref, rtol=1e-11, atol=1e-15)
     assert np.allclose(Cm, orc.ecsw_training_matrix(cur, prev, V, gx, gy, dt, mu), rtol=1e-11, atol=1e-15)
 

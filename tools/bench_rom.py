@@ -91,7 +91,7 @@ def main():
     variants = {}
     for mode, mesh in (("reference", lspg.jac_mesh), ("exact", lspg.res_mesh)):
         _, variants[f"{mode}_gather_ms"] = timed(lambda: lspg.jv(mesh, w, V, gather=True), 5)
-        for rows in (2, 4):
+        for rows in (1, 2, 4):
             rom_mod.JV_ROWS_PER_WARP = rows
             _, variants[f"{mode}_grid_rows{rows}_ms"] = timed(lambda: lspg.jv(mesh, w, V), 5)
         rom_mod.JV_ROWS_PER_WARP = 0
