@@ -383,20 +383,111 @@ class EcswSolver(_RomBase):
         self.V = basis if isinstance(basis, torch.Tensor) else self._dev(basis)
         self.V = self.V.to(self.device, dtype=torch.float64).contiguous()
         self.V_red = self.V[torch.from_numpy(self.idx).to(self.device)].contiguous()   # :245
+        self.graph_kernel_launches = 0      # this library's kernels replayed inside CUDA graphs
 
-    def run(self, w0, num_steps):
-        """Returns ``(red_coords_dev (T+1, k), per-step resnorm lists)``."""
+    def run(self, w0, num_steps, graphs=True):
+        """Returns ``(red_coords_dev (T+1, k), per-step resnorm lists)``.
+
+        ``graphs=True`` (default): a Gauss-Newton iteration is one CUDA-graph launch and one host
+        look at ``||f||`` (the stopping rules stay on the host, in the reference's order);
+        ``graphs=False`` issues the same operations one by one."""
         w0 = w0 if isinstance(w0, torch.Tensor) else self._dev(np.asarray(w0, dtype=np.float64).ravel())
         y = self.V.T @ w0                                   # :213
         red = torch.empty((num_steps + 1, self.V.shape[1]), dtype=torch.float64, device=self.device)
         red[0] = y
         wp = self.V_red @ y                                 # == (basis @ y0)[idx]  (:214, :243)
         history = []
+        if graphs and self.device.type == "cuda":
+            return self._run_graphs(y, wp, red, num_steps)
         for i in range(num_steps):
             y, w, resnorms = self.gauss_newton(self.mesh, self.mesh, self.V_red, y, wp)
             history.append(resnorms)
             red[i + 1] = y
             wp = w                                          # :271
+        return red, history
+
+    # -- Gauss-Newton iterations as CUDA graphs -------------------------------------------------
+    def _capture(self):
+        """Static buffers and two graphs: ``g_res`` (f = weighted residual of w, ||f||^2 to pinned host
+        memory) and ``g_iter`` (J V, normal equations, Cholesky solve, y += dy, w = V y, then g_res's
+        work for the new w)."""
+        dev, V = self.device, self.V_red
+        k, n_state, n_rows = V.shape[1], V.shape[0], 2 * self.mesh.nrows
+        f64 = dict(dtype=torch.float64, device=dev)
+        self._y, self._w, self._wp = torch.zeros(k, **f64), torch.zeros(n_state, **f64), torch.zeros(n_state, **f64)
+        self._f, self._n2, self._JV = torch.zeros(n_rows, **f64), torch.zeros(1, **f64), torch.zeros((n_rows, k), **f64)
+        self._h_n2 = torch.zeros(1, dtype=torch.float64).pin_memory()
+        mesh, lib = self.mesh, self.lib
+
+        def residual_part():
+            self._n2.zero_()
+            _lib.check(lib.bfd_rom_residual(C.byref(mesh.c), self._w.data_ptr(), self._wp.data_ptr(), self._f.data_ptr(),
+                                            self._n2.data_ptr(), self._stream()), lib, "bfd_rom_residual")
+            self._h_n2.copy_(self._n2, non_blocking=True)
+
+        def iteration():
+            _lib.check(lib.bfd_rom_jv(C.byref(mesh.c), self._w.data_ptr(), V.data_ptr(), k, self._JV.data_ptr(),
+                                      self._stream()), lib, "bfd_rom_jv")
+            G = self._JV.T @ self._JV
+            b = self._JV.T @ self._f
+            L, _ = torch.linalg.cholesky_ex(G)
+            dy = torch.cholesky_solve(b[:, None], L)[:, 0]
+            self._y.sub_(dy)                                # y += lstsq(JV, -f)
+            torch.mv(V, self._y, out=self._w)
+            residual_part()
+
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):                       # warm-up outside capture (library handles, workspaces)
+            self._w.copy_(V @ self._y)
+            self._wp.copy_(self._w)
+            residual_part()
+            iteration()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self._g_res, self._g_iter = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._g_res):
+            residual_part()
+        with torch.cuda.graph(self._g_iter, pool=self._g_res.pool()):
+            iteration()
+
+    def _run_graphs(self, y, wp, red, num_steps, max_its=20, relnorm_cutoff=1e-5, min_delta=0.1):
+        with torch.cuda.device(self.device):
+            if not hasattr(self, "_g_iter"):
+                self._capture()
+            stream = torch.cuda.current_stream(self.device)
+            self._y.copy_(y)
+            self._wp.copy_(wp)
+            self._w.copy_(wp)                               # w of the first iterate: V_red @ y0 == wp
+            history = []
+            for i in range(num_steps):
+                t0 = time.perf_counter()
+                self._g_res.replay()
+                stream.synchronize()
+                self.res_time += time.perf_counter() - t0
+                self.graph_kernel_launches += 1             # rom_residual_kernel
+                init_norm = float(np.sqrt(self._h_n2[0].item()))
+                resnorms = [init_norm]                      # resnorms[0] is the same evaluation as init_norm
+                for _ in range(max_its - 1):
+                    if resnorms[-1] / init_norm < relnorm_cutoff:
+                        break
+                    if len(resnorms) > 1 and abs((resnorms[-2] - resnorms[-1]) / resnorms[-2]) < min_delta:
+                        break
+                    t0 = time.perf_counter()
+                    self._g_iter.replay()
+                    stream.synchronize()
+                    self.ls_time += time.perf_counter() - t0
+                    self.graph_kernel_launches += 2         # rom_jv_kernel, rom_residual_kernel
+                    resnorms.append(float(np.sqrt(self._h_n2[0].item())))
+                else:
+                    # max_its evaluations without a stop: the reference still takes its last step (:2024-2043)
+                    if not (resnorms[-1] / init_norm < relnorm_cutoff or
+                            abs((resnorms[-2] - resnorms[-1]) / resnorms[-2]) < min_delta):
+                        self._g_iter.replay()
+                        stream.synchronize()
+                history.append(resnorms)
+                red[i + 1].copy_(self._y)
+                self._wp.copy_(self._w)                     # :271
         return red, history
 
 

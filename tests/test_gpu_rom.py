@@ -142,3 +142,21 @@ def test_sharded_lspg_one_rank_equals_lspg(h, golden, mode):
     if mode == "reference":
         assert [len(x) for x in hist] == g["gn_its"].tolist()
         assert max(rel(full[:, i], g["snaps"][:, i]) for i in range(steps + 1)) < TOL
+
+
+def test_ecsw_graph_iterations_equal_eager(h, golden):
+    """Gauss-Newton iterations replayed as CUDA graphs against the same operations issued one by one."""
+    from finitedifference_b200.rom import EcswSolver
+    g = golden("ecsw_n24.npz")
+    n, steps = int(g["n"]), int(g["steps"])
+    gx, gy = h.make_2D_grid(0, 100, 0, 100, n, n)
+    w0 = np.ones(2 * n * n)
+    args = (gx, gy, g["weights"], float(g["dt"]), list(g["mu"]), np.ascontiguousarray(g["basis"]))
+    red_g, hist_g = EcswSolver(*args).run(w0, steps)
+    red_e, hist_e = EcswSolver(*args).run(w0, steps, graphs=False)
+    assert [len(x) for x in hist_g] == [len(x) for x in hist_e] == g["gn_its"].tolist()
+    assert max(rel(red_g[i].cpu().numpy(), red_e[i].cpu().numpy()) for i in range(steps + 1)) < 1e-12
+    solver = EcswSolver(*args)
+    a, _ = solver.run(w0, 3)
+    b, _ = solver.run(w0, 3)                       # captured graphs are reused by a second trajectory
+    assert np.array_equal(a.cpu().numpy(), b.cpu().numpy())
