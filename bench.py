@@ -164,6 +164,11 @@ def main():
     if args.impl == "reference":
         run_reference_arm(args, rank, world)
         return
+    # stdout carries exactly one JSON line: whatever libraries print there (NCCL's version banner
+    # ignores NCCL_DEBUG_FILE) is sent to stderr, the line is written to the saved descriptor
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
 
     import ctypes as C
     import torch
@@ -256,7 +261,8 @@ def main():
     # one group overlapping the sweeps of the next; host buffers recycled through a pool)
     del solver
     torch.cuda.empty_cache()
-    from finitedifference_b200.sweep import SnapshotSweep
+    from finitedifference_b200.sweep import SnapshotSweep, bind_host_to_gpu_node
+    numa = bind_host_to_gpu_node(dev)           # pinned buffers and worker threads next to this GPU's PCIe root
     Be = max(1, min(args.e2e_mu, B))
     mus_e = mus[:Be]
     w0_np = np.ones(2 * cells)
@@ -293,6 +299,7 @@ def main():
            "h2d_bytes_per_step": int(w0_np.nbytes),
            "d2h_bytes_per_step": int(Be * 2 * cells * (T + 1) * 8),
            "mu_per_gpu": Be, "seconds_per_step": e2e_s / e2e_reps, "pinned_buffers_per_gpu": pool,
+           "host_numa_node": numa,
            "d2h_GBps_per_gpu": Be * 2 * cells * (T + 1) * 8 * e2e_reps / e2e_s / 1e9,
            "api": f"SnapshotSweep(group={args.e2e_group}, workers={args.e2e_workers}).run(w0, mus, sink): every "
                   "(2N, T+1) trajectory copied to pinned host memory and handed to the sink"}
@@ -300,7 +307,7 @@ def main():
 
     if rank == 0:
         cb = None
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:       # the CPU arm is timed at N = 1 only
             cb = cpu_baseline(sample_steps=1, n=n)
             cb = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -318,7 +325,8 @@ def main():
                 "mu_trajectories_per_s": world * B * args.steps / (total_ms * 1e-3),
                 "roofline": roofline, "cpu_baseline": cb, "e2e": e2e, "gpu_launches": int(launches),
                 "clocks": clocks.summary(), "wall_s_timed": wall}
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
 

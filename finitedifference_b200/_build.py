@@ -7,7 +7,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-SOURCES = ["runtime.cu", "fom.cu", "ops.cu", "rom.cu", "rom_grid.cu"]
+SOURCES = ["runtime.cu", "fom.cu", "ops.cu", "rom.cu", "rom_grid.cu", "gram.cu"]
 OUT = os.path.join(HERE, "_burgers_b200.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--use_fast_math=false"]

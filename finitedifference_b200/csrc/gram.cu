@@ -1,0 +1,201 @@
+// Normal equations of the LSPG Gauss-Newton step on the FP64 tensor cores:
+//     G = X^T X  (k x k),   b = X^T f  (k),   X = J V  (M x k row-major, M = 2N rows, k <= 96).
+//
+// Replaces numpy.linalg.lstsq(JV, -f) of gauss_newton_LSPG (BurgersFD_CleanFine/hypernet2D.py:1994):
+// with cond(JV) ~ 1.5 the k x k normal equations give the same step to 1e-13, and
+// forming them is the dense part of the PROM: 2 M k^2 flop (20.3 GFLOP at 750^2, k = 95).
+// cuBLAS runs this tall-skinny shape (95 x 95 output, 1.1 M deep) at 22 TFLOP/s (0.92 ms); it cannot
+// use the symmetry of G.  Here:
+//   * X streams through shared memory in tiles of 16 rows (cp.async, 3 stages), padded to 96 modes
+//     plus one extra column block that carries f, so b falls out of the same contraction;
+//   * G is cut into 8 x 8 blocks; only the 78 blocks on or above the diagonal (+ 12 for b) are
+//     computed, with DMMA (mma.sync.m8n8k4.f64: FP64 tensor pipe).  Warp I of a CTA owns block rows
+//     I and 11-I (15 blocks each way: balanced), and the A fragment of block row i is the B
+//     fragment of block column i, so a warp loads at most 13 fragments for 15 DMMAs per 4 rows;
+//   * every CTA keeps its partial G in registers over all its tiles and writes it once; a second
+//     small kernel adds the partials in a fixed order (deterministic: replicas and ranks agree
+//     bit for bit) and mirrors the upper triangle.
+#include "wavefront.cuh"
+
+namespace bfd {
+
+constexpr int kGramRows = 16;        // rows of X per stage (4 DMMA k-steps)
+constexpr int kGramPitch = 108;      // doubles per shared row: 96 modes + f + pad; 108 mod 16 = 12 -> fragment loads conflict-free
+constexpr int kGramStages = 3;
+constexpr int kGramWarps = 6;        // block rows (I, 11-I), I = 0..5
+constexpr int kGramBlocks = 13;      // 12 mode blocks + the f block
+constexpr int kGramLd = 104;         // leading dimension of a partial: 13 blocks x 8
+
+struct GramArgs {
+    const double *X, *f;
+    long long M;
+    int k, ntiles;
+    double *partial;                 // [gridDim.x][96][kGramLd]
+};
+
+#ifndef BFD_EMULATE
+__device__ __forceinline__ void dmma8x8x4(double (&d)[2], double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+                 : "+d"(d[0]), "+d"(d[1]) : "d"(a), "d"(b));
+}
+#else
+// D[m][n] += sum_k A[m][k] B[k][n]; lane l holds A[l/4][l%4], B[l%4][l/4], D[l/4][2*(l%4) + {0,1}]
+inline void dmma8x8x4(double (&d)[2], double a, double b) {
+    const int l = emu::tls.lane;
+    for (int kk = 0; kk < 4; ++kk) {
+        const double av = __shfl_sync(0xffffffffu, a, (l / 4) * 4 + kk);
+        const double b0 = __shfl_sync(0xffffffffu, b, (2 * (l % 4)) * 4 + kk);
+        const double b1 = __shfl_sync(0xffffffffu, b, (2 * (l % 4) + 1) * 4 + kk);
+        d[0] += av * b0;
+        d[1] += av * b1;
+    }
+}
+#endif
+
+// One warp's share of a 16-row tile: block rows I (columns I..12, acc[0..N1)) and 11-I (columns
+// 11-I..12, acc[N1..15)).  The six instantiations run interleaved on every SM sub-partition, so
+// the loop is kept short (no unrolling over the k-steps: with 4x unrolling the kernel spent 6
+// cycles per issue waiting for instructions, profiles/r01_gram_ncu.md).
+template <int I>
+__device__ __forceinline__ void gram_compute(double (&acc)[15][2], saddr sb) {
+    constexpr int I2 = 11 - I, N1 = kGramBlocks - I, N2 = kGramBlocks - I2;
+#pragma unroll 1
+    for (int ks = 0; ks < kGramRows / 4; ++ks) {
+        double fr[N1];                                       // fragments of column blocks I..12
+#pragma unroll
+        for (int j = 0; j < N1; ++j) fr[j] = lds(sb + (saddr)((ks * 4 * kGramPitch + (I + j) * 8) * 8));
+#pragma unroll
+        for (int j = 0; j < N1; ++j) dmma8x8x4(acc[j], fr[0], fr[j]);
+#pragma unroll
+        for (int j = 0; j < N2; ++j) dmma8x8x4(acc[N1 + j], fr[I2 - I], fr[I2 - I + j]);
+    }
+}
+
+// lane holds rows (l >> 2), columns 2 (l & 3) + {0, 1} of each of its blocks
+template <int I>
+__device__ __forceinline__ void gram_store(const double (&acc)[15][2], double *P, int lane) {
+    constexpr int I2 = 11 - I, N1 = kGramBlocks - I, N2 = kGramBlocks - I2;
+#pragma unroll
+    for (int j = 0; j < N1; ++j) {
+        double *p = P + (size_t)(8 * I + (lane >> 2)) * kGramLd + 8 * (I + j) + 2 * (lane & 3);
+        p[0] = acc[j][0]; p[1] = acc[j][1];
+    }
+#pragma unroll
+    for (int j = 0; j < N2; ++j) {
+        double *p = P + (size_t)(8 * I2 + (lane >> 2)) * kGramLd + 8 * (I2 + j) + 2 * (lane & 3);
+        p[0] = acc[N1 + j][0]; p[1] = acc[N1 + j][1];
+    }
+}
+
+// stage `st` <- tile `nt` of X (and its slice of f in column 96); rows past M are zero
+__device__ __forceinline__ void gram_load(const GramArgs &a, saddr tiles, int st, long long nt) {
+    if (nt < a.ntiles) {
+        const long long r0 = nt * kGramRows;
+        const saddr sb = tiles + (saddr)(st * kGramRows * kGramPitch * 8);
+        const int k = a.k;
+        for (int e = threadIdx.x; e < kGramRows * k; e += 32 * kGramWarps) {
+            const int row = e / k, col = e - row * k;
+            const saddr dst = sb + (saddr)((row * kGramPitch + col) * 8);
+            if (r0 + row < a.M) cp_async8(dst, a.X + r0 * k + e); else sts(dst, 0.0);
+        }
+        if (threadIdx.x < kGramRows) {
+            const saddr dst = sb + (saddr)((threadIdx.x * kGramPitch + 96) * 8);
+            if (r0 + threadIdx.x < a.M) cp_async8(dst, a.f + r0 + threadIdx.x); else sts(dst, 0.0);
+        }
+    }
+    cp_async_commit();
+}
+
+__global__ void __launch_bounds__(32 * kGramWarps) gram_partial_kernel(const GramArgs a) {
+    BFD_SHARED_ARRAY(double, xs, [kGramStages * kGramRows * kGramPitch]);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const saddr tiles = smem_addr(&xs[0]);
+    for (int e = threadIdx.x; e < kGramStages * kGramRows * kGramPitch; e += 32 * kGramWarps) xs[e] = 0.0;   // pad columns stay 0
+    __syncthreads();
+    for (int s = 0; s < kGramStages - 1; ++s) gram_load(a, tiles, s, (long long)blockIdx.x + (long long)s * gridDim.x);
+    double acc[15][2];
+#pragma unroll
+    for (int j = 0; j < 15; ++j) acc[j][0] = acc[j][1] = 0.0;
+    const saddr lane_off = (saddr)(((lane & 3) * kGramPitch + (lane >> 2)) * 8);
+    int it = 0;
+    for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, ++it) {
+        cp_async_wait_pending<kGramStages - 2>();
+        __syncthreads();
+        // refill the stage consumed one tile ago with the tile kGramStages-1 ahead
+        gram_load(a, tiles, (it + kGramStages - 1) % kGramStages, (long long)tile + (long long)(kGramStages - 1) * gridDim.x);
+        const saddr sb = tiles + (saddr)((it % kGramStages) * kGramRows * kGramPitch * 8) + lane_off;
+        switch (warp) {
+        case 0: gram_compute<0>(acc, sb); break;
+        case 1: gram_compute<1>(acc, sb); break;
+        case 2: gram_compute<2>(acc, sb); break;
+        case 3: gram_compute<3>(acc, sb); break;
+        case 4: gram_compute<4>(acc, sb); break;
+        default: gram_compute<5>(acc, sb); break;
+        }
+    }
+    double *P = a.partial + (size_t)blockIdx.x * 96 * kGramLd;
+    switch (warp) {
+    case 0: gram_store<0>(acc, P, lane); break;
+    case 1: gram_store<1>(acc, P, lane); break;
+    case 2: gram_store<2>(acc, P, lane); break;
+    case 3: gram_store<3>(acc, P, lane); break;
+    case 4: gram_store<4>(acc, P, lane); break;
+    default: gram_store<5>(acc, P, lane); break;
+    }
+}
+
+// G[i][j] (k x k, both triangles) and b[i] from the partials: blockDim = (32 outputs, 8 slices of
+// the partials); every slice is summed in order, then the 8 slice sums in order (deterministic)
+__global__ void __launch_bounds__(256) gram_reduce_kernel(const double *partial, int nparts, int k, double *G, double *b) {
+    BFD_SHARED_ARRAY(double, part, [8][33]);
+    const int idx = blockIdx.x * 32 + threadIdx.x;
+    const bool ok = idx < k * (k + 1);
+    const int i = ok ? idx / (k + 1) : 0, j = ok ? idx - i * (k + 1) : 0;
+    int r = i, c = j;
+    if (j == k) c = 96;                                      // the f column
+    else if ((i >> 3) > (j >> 3)) { r = j; c = i; }           // below the block diagonal: mirror
+    double s = 0.0;
+    if (ok)
+        for (int p = threadIdx.y; p < nparts; p += 8) s += partial[((size_t)p * 96 + r) * kGramLd + c];
+    part[threadIdx.y][threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.y == 0 && ok) {
+        double t = 0.0;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) t += part[q][threadIdx.x];
+        if (j == k) b[i] = t; else G[(size_t)i * k + j] = t;
+    }
+}
+
+}  // namespace bfd
+
+using namespace bfd;
+
+static int gram_grid(long long M) {
+    const long long ntiles = (M + kGramRows - 1) / kGramRows;
+    long long g = 148 * 3;                                    // 3 CTAs of 6 warps per SM are resident (94 registers)
+    if (g > ntiles) g = ntiles;
+    return (int)BFD_GRID((int)g);
+}
+
+extern "C" size_t bfd_gram_workspace_bytes(int64_t M, int k) {
+    if (M < 1 || k < 1 || k > 96) return 0;
+    return (size_t)gram_grid(M) * 96 * kGramLd * sizeof(double);
+}
+
+extern "C" int bfd_gram(const double *X, const double *f, int64_t M, int k, double *G, double *b, void *workspace,
+                        size_t workspace_bytes, void *stream) {
+    if (!X || !f || !G || !b || !workspace || M < 1 || k < 1 || k > 96) return BFD_EINVAL;
+    if (workspace_bytes < bfd_gram_workspace_bytes(M, k)) return BFD_EWORKSPACE;
+    GramArgs a{};
+    a.X = X; a.f = f; a.M = M; a.k = k;
+    a.ntiles = (int)((M + kGramRows - 1) / kGramRows);
+    a.partial = (double *)workspace;
+    const int grid = gram_grid(M);
+    cudaStream_t st = (cudaStream_t)stream;
+    BFD_LAUNCH(gram_partial_kernel, grid, 32 * kGramWarps, 0, st, a);
+    BFD_LAUNCHED();
+    BFD_LAUNCH(gram_reduce_kernel, (k * (k + 1) + 31) / 32, dim3(32, 8), 0, st, (const double *)a.partial, grid, k, G, b);
+    BFD_LAUNCHED();
+    return BFD_OK;
+}

@@ -27,6 +27,7 @@ from .discretisation import stencil_coefficients
 from .fom import _require_cuda
 
 
+GRAM_KERNEL_MIN_ROWS = 65536
 JV_ROWS_PER_WARP = 0     # grid rows a warp of bfd_rom_jv_grid owns: 0 = library default, 2 or 4 (tuning)
 
 
@@ -173,6 +174,21 @@ class _RomBase:
                                            self._stream()), self.lib, "bfd_rom_jv")
         return JV
 
+    def normal_equations(self, JV, f):
+        """``(G, b) = (JV^T JV, JV^T f)``: the DMMA kernel ``bfd_gram`` for k <= 96, library GEMMs beyond."""
+        M, k = JV.shape
+        if k > 96 or M < GRAM_KERNEL_MIN_ROWS:      # small sampled meshes: one library GEMM beats partials + reduce
+            return JV.T @ JV, JV.T @ f
+        ws = getattr(self, "_gram_ws", None)
+        nbytes = self.lib.bfd_gram_workspace_bytes(M, k)
+        if ws is None or ws.numel() < nbytes:
+            ws = self._gram_ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+        G = torch.empty((k, k), dtype=torch.float64, device=self.device)
+        b = torch.empty(k, dtype=torch.float64, device=self.device)
+        _lib.check(self.lib.bfd_gram(JV.data_ptr(), f.data_ptr(), M, k, G.data_ptr(), b.data_ptr(), ws.data_ptr(),
+                                     ws.numel(), self._stream()), self.lib, "bfd_gram")
+        return G, b
+
     def gauss_newton(self, res_mesh, jac_mesh, V, y0, wp, max_its=20, relnorm_cutoff=1e-5, min_delta=0.1):
         """``gauss_newton_LSPG`` / ``gauss_newton_ECSW_2D`` (:1935-2005, :2007-2044).
 
@@ -196,10 +212,9 @@ class _RomBase:
             self._sync()
             self.jac_time += time.perf_counter() - t0
             t0 = time.perf_counter()
-            G = JV.T @ JV                                  # normal equations of lstsq(JV, -f)
-            b = -(JV.T @ f)
+            G, b = self.normal_equations(JV, f)            # normal equations of lstsq(JV, -f)
             dy = torch.cholesky_solve(b[:, None], torch.linalg.cholesky(G))[:, 0]
-            y = y + dy
+            y = y - dy
             w = V @ y
             self._sync()
             self.ls_time += time.perf_counter() - t0
@@ -323,8 +338,9 @@ class ShardedLspgSolver(_RomBase):
             Gb = torch.zeros((k, k + 1), dtype=torch.float64, device=self.device)
             if self.rows.size:
                 JV = self.jv(self.jac_mesh, w, V)
-                Gb[:, :k] = JV.T @ JV
-                Gb[:, k] = -(JV.T @ f)
+                G, b = self.normal_equations(JV, f)
+                Gb[:, :k] = G
+                Gb[:, k] = -b
             self._allreduce(Gb)
             dy = torch.cholesky_solve(Gb[:, k:].contiguous(), torch.linalg.cholesky(Gb[:, :k]))[:, 0]
             y = y + dy
@@ -428,8 +444,7 @@ class EcswSolver(_RomBase):
         def iteration():
             _lib.check(lib.bfd_rom_jv(C.byref(mesh.c), self._w.data_ptr(), V.data_ptr(), k, self._JV.data_ptr(),
                                       self._stream()), lib, "bfd_rom_jv")
-            G = self._JV.T @ self._JV
-            b = self._JV.T @ self._f
+            G, b = self.normal_equations(self._JV, self._f)
             L, _ = torch.linalg.cholesky_ex(G)
             dy = torch.cholesky_solve(b[:, None], L)[:, 0]
             self._y.sub_(dy)                                # y += lstsq(JV, -f)

@@ -245,6 +245,16 @@ int bfd_ecsw_c_fused(const bfd_rom_mesh *mesh, const double *w, const double *r,
 int bfd_ecsw_c_grid(const bfd_rom_mesh *mesh, int nx, int ny, const double *w, const double *r,
                     const double *V, int k, double *C, size_t ldc, void *stream);
 
+/* Normal equations of a Gauss-Newton step on the FP64 tensor cores (DMMA):
+ *   G[k][k] = X^T X (row-major, both triangles),  b[k] = X^T f,   X row-major [M][k], k <= 96.
+ * Replaces numpy.linalg.lstsq(JV, -f) of gauss_newton_LSPG (:1994) / gauss_newton_ECSW_2D (:2038)
+ * together with a k x k Cholesky solve of G dy = -b by the caller.  Only the blocks on or above
+ * the diagonal are computed; partial sums are added in a fixed order (deterministic).
+ * workspace: bfd_gram_workspace_bytes(M, k) bytes of device memory (0 = unsupported k). */
+size_t bfd_gram_workspace_bytes(int64_t M, int k);
+int bfd_gram(const double *X, const double *f, int64_t M, int k, double *G, double *b, void *workspace,
+             size_t workspace_bytes, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -8,7 +8,7 @@ CSRC = os.path.join(ROOT, "finitedifference_b200", "csrc")
 OUT = os.path.join(HERE, "_burgers_emu.so")
 
 
-def build(sources=("runtime.cu", "fom.cu", "ops.cu", "rom.cu", "rom_grid.cu")):
+def build(sources=("runtime.cu", "fom.cu", "ops.cu", "rom.cu", "rom_grid.cu", "gram.cu")):
     srcs = [os.path.join(CSRC, s) for s in sources]
     deps = srcs + [os.path.join(CSRC, "common.cuh"), os.path.join(HERE, "cuda_emu.h"),
                    os.path.join(ROOT, "include", "burgers_b200.h")]

@@ -190,3 +190,20 @@ def test_jacobian_csr_sampled_rows(lib, golden):
     assert np.max(np.abs(J.toarray() - g["J_red"])) < 1e-14                      # the reference's own matrix
     with pytest.raises(ValueError):
         ops.jacobian_tables(jdy_s, jdx_s, dt, np.searchsorted(aug, sample) + 1)
+
+
+@pytest.mark.parametrize("M,k", [(1000, 95), (37, 5), (16, 96), (130, 33), (1, 1)])
+def test_gram_dmma_normal_equations(lib, M, k):
+    """bfd_gram (DMMA blocks on or above the diagonal, f as a 13th column block, partials summed
+    in a fixed order) against NumPy: G = X^T X with both triangles filled, b = X^T f."""
+    rng = np.random.default_rng(M * 100 + k)
+    X = np.ascontiguousarray(rng.standard_normal((M, k)))
+    f = rng.standard_normal(M)
+    nbytes = lib.bfd_gram_workspace_bytes(M, k)
+    assert nbytes > 0 and lib.bfd_gram_workspace_bytes(M, 97) == 0
+    ws = np.zeros(nbytes // 8)
+    G, b = np.full((k, k), np.nan), np.full(k, np.nan)
+    assert lib.bfd_gram(E.ptr(X), E.ptr(f), M, k, E.ptr(G), E.ptr(b), E.ptr(ws), nbytes, None) == 0
+    assert np.allclose(G, X.T @ X, rtol=1e-13, atol=1e-12) and np.array_equal(G, G.T)
+    assert np.allclose(b, X.T @ f, rtol=1e-13, atol=1e-12)
+    assert lib.bfd_gram(E.ptr(X), E.ptr(f), M, k, E.ptr(G), E.ptr(b), E.ptr(ws), nbytes - 8, None) == -3

@@ -160,3 +160,23 @@ def test_ecsw_graph_iterations_equal_eager(h, golden):
     a, _ = solver.run(w0, 3)
     b, _ = solver.run(w0, 3)                       # captured graphs are reused by a second trajectory
     assert np.array_equal(a.cpu().numpy(), b.cpu().numpy())
+
+
+@pytest.mark.parametrize("M,k", [(200000, 95), (12345, 96), (999, 7), (70001, 40)])
+def test_gram_dmma_equals_library_gemm(M, k, request):
+    """bfd_gram (FP64 tensor cores, upper blocks only, fixed-order partial sums) against cuBLAS."""
+    import torch
+    from finitedifference_b200 import rom
+    base = rom._RomBase()
+    rom_min, rom.GRAM_KERNEL_MIN_ROWS = rom.GRAM_KERNEL_MIN_ROWS, 0          # the kernel at every size
+    request.addfinalizer(lambda: setattr(rom, "GRAM_KERNEL_MIN_ROWS", rom_min))
+    g = torch.Generator(device=base.device).manual_seed(M + k)
+    X = torch.randn((M, k), dtype=torch.float64, device=base.device, generator=g)
+    f = torch.randn(M, dtype=torch.float64, device=base.device, generator=g)
+    G, b = base.normal_equations(X, f)
+    Gr, br = X.T @ X, X.T @ f
+    scale = float(Gr.abs().max())
+    assert float((G - Gr).abs().max()) < 1e-12 * scale and torch.equal(G, G.T)
+    assert float((b - br).abs().max()) < 1e-12 * scale
+    G2, b2 = base.normal_equations(X, f)
+    assert torch.equal(G, G2) and torch.equal(b, b2)          # deterministic
