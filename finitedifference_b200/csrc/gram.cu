@@ -199,3 +199,79 @@ extern "C" int bfd_gram(const double *X, const double *f, int64_t M, int k, doub
     BFD_LAUNCHED();
     return BFD_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// G dy = b for the k x k normal equations (k <= 96): Cholesky factorisation and the triangular
+// solves by ONE CTA, thread i owning row i of the packed factor in shared memory.  Replaces the
+// LAPACK solve inside numpy.linalg.lstsq (:1994, :2038).  A library potrf + potrs on a 95 x 95
+// matrix is a chain of about ten tiny kernels (~0.1 ms); this is one launch:
+//   * left-looking Cholesky, ONE barrier per column: at column j every thread i >= j forms
+//     a_ij - sum_p L_ip L_jp from its own row and row j (a broadcast read), and also the diagonal
+//     a_jj - sum_p L_jp^2 itself rather than waiting for thread j to publish it;
+//   * b rides along as row k of the matrix: the same recurrence then yields z = L^-1 b for free;
+//   * back substitution L^T x = z column by column, one barrier per column.
+// ------------------------------------------------------------------------------------------
+namespace bfd {
+
+constexpr int kSolveThreads = 128;
+
+__device__ __forceinline__ int tri(int i, int j) { return i * (i + 1) / 2 + j; }      // j <= i
+
+__global__ void __launch_bounds__(kSolveThreads) spd_solve_kernel(const double *G, const double *b, int k, double scale,
+                                                                    double *x) {
+    BFD_SHARED_ARRAY(double, L, [97 * 98 / 2]);        // rows 0..k-1: the factor; row k: scale*b, then z
+    BFD_SHARED_ARRAY(double, xs, [96]);
+    BFD_SHARED_ARRAY(double, dg, [96]);               // reciprocal diagonal of the factor
+    const int t = threadIdx.x;
+#pragma unroll 8
+    for (int e = t; e < k * k; e += kSolveThreads) {
+        const double g = G[e];                           // unconditional: the loads of 8 iterations go out together
+        const int i = e / k, j = e - i * k;
+        if (j <= i) L[tri(i, j)] = g;
+    }
+    if (t < k) L[tri(k, t)] = scale * b[t];
+    __syncthreads();
+    const int ri = tri(t <= k ? t : k, 0);
+    for (int j = 0; j < k; ++j) {
+        if (t >= j && t <= k) {
+            const int rj = tri(j, 0);
+            double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0, d0 = 0.0, d1 = 0.0, d2 = 0.0, d3 = 0.0;
+            int p = 0;
+            for (; p + 7 < j; p += 8) {                            // 16 loads in flight, 4 independent chains each
+                double a[8], c[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) { a[q] = L[rj + p + q]; c[q] = L[ri + p + q]; }
+#pragma unroll
+                for (int q = 0; q < 8; q += 4) {
+                    s0 += c[q] * a[q]; s1 += c[q + 1] * a[q + 1]; s2 += c[q + 2] * a[q + 2]; s3 += c[q + 3] * a[q + 3];
+                    d0 += a[q] * a[q]; d1 += a[q + 1] * a[q + 1]; d2 += a[q + 2] * a[q + 2]; d3 += a[q + 3] * a[q + 3];
+                }
+            }
+            for (; p < j; ++p) { const double a0 = L[rj + p]; s0 += L[ri + p] * a0; d0 += a0 * a0; }
+            s0 += s2; s1 += s3; d0 += d2; d1 += d3;
+            const double rdiag = rsqrt(L[rj + j] - (d0 + d1));   // 1 / L_jj; NaN for a matrix that is not positive definite
+            const double v = L[ri + j] - (s0 + s1);
+            if (t == j) dg[j] = rdiag;                           // a_jj itself stays in place: nobody waits for it
+            else L[ri + j] = v * rdiag;
+        }
+        __syncthreads();
+    }
+    if (t < k) xs[t] = L[tri(k, t)];                              // z
+    __syncthreads();
+    for (int i = k - 1; i >= 0; --i) {
+        if (t == i) xs[i] = xs[i] * dg[i];
+        __syncthreads();
+        if (t < i) xs[t] -= L[tri(i, t)] * xs[i];
+    }
+    __syncthreads();
+    if (t < k) x[t] = xs[t];
+}
+
+}  // namespace bfd
+
+extern "C" int bfd_spd_solve(const double *G, const double *b, int k, double scale, double *x, void *stream) {
+    if (!G || !b || !x || k < 1 || k > 96) return BFD_EINVAL;
+    BFD_LAUNCH(spd_solve_kernel, 1, kSolveThreads, 0, (cudaStream_t)stream, G, b, k, scale, x);
+    BFD_LAUNCHED();
+    return BFD_OK;
+}

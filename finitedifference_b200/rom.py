@@ -28,6 +28,7 @@ from .fom import _require_cuda
 
 
 GRAM_KERNEL_MIN_ROWS = 65536
+SPD_SOLVE_KERNEL = True      # False: cuSOLVER potrf + potrs through torch (comparison)
 JV_ROWS_PER_WARP = 0     # grid rows a warp of bfd_rom_jv_grid owns: 0 = library default, 2 or 4 (tuning)
 
 
@@ -189,6 +190,18 @@ class _RomBase:
                                      ws.numel(), self._stream()), self.lib, "bfd_gram")
         return G, b
 
+    def gn_step(self, G, b):
+        """``dy = -G^-1 b`` = ``lstsq(JV, -f)``: one single-CTA launch (``bfd_spd_solve``) for k <= 96,
+        cuSOLVER Cholesky beyond."""
+        k = G.shape[0]
+        if k > 96 or not SPD_SOLVE_KERNEL:
+            L, _ = torch.linalg.cholesky_ex(G)
+            return -torch.cholesky_solve(b[:, None], L)[:, 0]
+        dy = torch.empty(k, dtype=torch.float64, device=self.device)
+        _lib.check(self.lib.bfd_spd_solve(G.data_ptr(), b.data_ptr(), k, -1.0, dy.data_ptr(), self._stream()),
+                   self.lib, "bfd_spd_solve")
+        return dy
+
     def gauss_newton(self, res_mesh, jac_mesh, V, y0, wp, max_its=20, relnorm_cutoff=1e-5, min_delta=0.1):
         """``gauss_newton_LSPG`` / ``gauss_newton_ECSW_2D`` (:1935-2005, :2007-2044).
 
@@ -213,8 +226,7 @@ class _RomBase:
             self.jac_time += time.perf_counter() - t0
             t0 = time.perf_counter()
             G, b = self.normal_equations(JV, f)            # normal equations of lstsq(JV, -f)
-            dy = torch.cholesky_solve(b[:, None], torch.linalg.cholesky(G))[:, 0]
-            y = y - dy
+            y = y + self.gn_step(G, b)
             w = V @ y
             self._sync()
             self.ls_time += time.perf_counter() - t0
@@ -342,8 +354,7 @@ class ShardedLspgSolver(_RomBase):
                 Gb[:, :k] = G
                 Gb[:, k] = -b
             self._allreduce(Gb)
-            dy = torch.cholesky_solve(Gb[:, k:].contiguous(), torch.linalg.cholesky(Gb[:, :k]))[:, 0]
-            y = y + dy
+            y = y - self.gn_step(Gb[:, :k].contiguous(), Gb[:, k].contiguous())   # Gb[:, k] holds -b
             w = V @ y
         return y, w, resnorms
 
@@ -445,9 +456,7 @@ class EcswSolver(_RomBase):
             _lib.check(lib.bfd_rom_jv(C.byref(mesh.c), self._w.data_ptr(), V.data_ptr(), k, self._JV.data_ptr(),
                                       self._stream()), lib, "bfd_rom_jv")
             G, b = self.normal_equations(self._JV, self._f)
-            L, _ = torch.linalg.cholesky_ex(G)
-            dy = torch.cholesky_solve(b[:, None], L)[:, 0]
-            self._y.sub_(dy)                                # y += lstsq(JV, -f)
+            self._y.add_(self.gn_step(G, b))                # y += lstsq(JV, -f)
             torch.mv(V, self._y, out=self._w)
             residual_part()
 

@@ -255,6 +255,12 @@ size_t bfd_gram_workspace_bytes(int64_t M, int k);
 int bfd_gram(const double *X, const double *f, int64_t M, int k, double *G, double *b, void *workspace,
              size_t workspace_bytes, void *stream);
 
+/* x = scale * G^-1 b for a symmetric positive definite k x k matrix (row-major, lower triangle
+ * read), k <= 96: Cholesky + two triangular solves in one single-CTA launch (a matrix that is not
+ * positive definite yields NaNs, as silent as the reference's lstsq is about rank).  With bfd_gram
+ * this is the Gauss-Newton step dy = lstsq(JV, -f) of :1994 / :2038 (scale = -1). */
+int bfd_spd_solve(const double *G, const double *b, int k, double scale, double *x, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -176,6 +176,7 @@ static inline void __threadfence_system() { std::atomic_thread_fence(std::memory
 static inline void __threadfence_block() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 
 template <class T> static inline T __ldg(const T *p) { return *p; }
+static inline double rsqrt(double x) { return 1.0 / std::sqrt(x); }
 static inline long long __double_as_longlong(double x) { long long b; memcpy(&b, &x, 8); return b; }
 static inline double __longlong_as_double(long long b) { double x; memcpy(&x, &b, 8); return x; }
 

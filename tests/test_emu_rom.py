@@ -207,3 +207,17 @@ def test_gram_dmma_normal_equations(lib, M, k):
     assert np.allclose(G, X.T @ X, rtol=1e-13, atol=1e-12) and np.array_equal(G, G.T)
     assert np.allclose(b, X.T @ f, rtol=1e-13, atol=1e-12)
     assert lib.bfd_gram(E.ptr(X), E.ptr(f), M, k, E.ptr(G), E.ptr(b), E.ptr(ws), nbytes - 8, None) == -3
+
+
+@pytest.mark.parametrize("k", [1, 2, 7, 33, 95, 96])
+def test_spd_solve_single_cta(lib, k):
+    """bfd_spd_solve (packed Cholesky + triangular solves by one CTA) against numpy.linalg.solve."""
+    rng = np.random.default_rng(k)
+    A = rng.standard_normal((3 * k + 5, k))
+    G = np.ascontiguousarray(A.T @ A)
+    b = rng.standard_normal(k)
+    x = np.full(k, np.nan)
+    assert lib.bfd_spd_solve(E.ptr(G), E.ptr(b), k, -1.0, E.ptr(x), None) == 0
+    want = -np.linalg.solve(G, b)
+    assert np.allclose(x, want, rtol=1e-10, atol=1e-12 * np.abs(want).max())
+    assert lib.bfd_spd_solve(E.ptr(G), E.ptr(b), 97, 1.0, E.ptr(x), None) == -1

@@ -101,6 +101,10 @@ def main():
     _, dmma_ms = timed(lambda: lspg.normal_equations(JV, fres), 5)
     Gd, bd = lspg.normal_equations(JV, fres)
     dmma_diff = float((Gd - JV.T @ JV).abs().max() / (JV.T @ JV).abs().max())
+    _, solve_ms = timed(lambda: lspg.gn_step(Gd, bd), 20)
+    rom_mod.SPD_SOLVE_KERNEL = False
+    _, solve_lib_ms = timed(lambda: lspg.gn_step(Gd, bd), 20)
+    solve_diff = float((lspg.gn_step(Gd, bd) - (rom_mod.__setattr__("SPD_SOLVE_KERNEL", True) or lspg.gn_step(Gd, bd))).abs().max())
     _, vy_ms = timed(lambda: V @ red[1], 5)
     jv_bytes = 8 * 2 * N * k * 2 + N * (5 * 4 + 4 * 8 + 16)        # read V once, write JV, tables + state
     print(json.dumps({
@@ -115,6 +119,7 @@ def main():
         "gram_dmma_kernel": {"ms": dmma_ms, "useful_flop": 2.0 * 2 * N * k * (k + 1), "TFLOPs_useful": 2.0 * 2 * N * k * (k + 1)
                              / dmma_ms / 1e9, "blocks_computed_of_full": 90.0 / 156.0, "max_rel_diff_vs_gemm": dmma_diff,
                              "includes": "b = (JV)^T f"},
+        "spd_solve_kernel": {"ms": solve_ms, "cusolver_potrf_potrs_ms": solve_lib_ms, "max_abs_diff": solve_diff},
         "V_times_y_cublas": {"ms": vy_ms, "GBps": 8 * 2 * N * k / vy_ms / 1e6},
         "host_timers_s": {"jac": lspg.jac_time, "res": lspg.res_time, "ls": lspg.ls_time}}), flush=True)
 
