@@ -146,6 +146,7 @@ class SnapshotSweep:
             stream = self._streams[wid]
             try:
                 with torch.cuda.device(self.device), torch.cuda.stream(stream):
+                    done = torch.cuda.Event(blocking=True)
                     w0_dev = w0_pinned.to(self.device, non_blocking=True)
                     while not errors:
                         try:
@@ -165,7 +166,8 @@ class SnapshotSweep:
                         held = []
 
                         def flush():
-                            stream.synchronize()
+                            done.record(stream)             # blocking-sync event: the thread sleeps, it does not spin
+                            done.synchronize()
                             while held:
                                 i, buf = held.pop(0)
                                 try:
