@@ -1113,10 +1113,8 @@ static int fom_run_impl(const bfd_fom_desc *d, const SlabView &v, void *ws, cons
     // the poll.  A launch issued after everything finished exits at once.  (Slab runs: the
     // counter is rank 0's; ranks may issue different numbers of trailing empty launches.)
     cudaEvent_t ev[2];
-    // blocking-sync events: a waiting host thread sleeps instead of spinning (sweeps run several
-    // host threads per GPU and several GPUs per box)
-    BFD_CUDA(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming | cudaEventBlockingSync));
-    BFD_CUDA(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming | cudaEventBlockingSync));
+    BFD_CUDA(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming));
+    BFD_CUDA(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
     int *h_poll = (int *)h_pinned + 4;   // two 2-int landing zones at h[4..5], h[6..7]
     const long long hard_cap = (long long)d->num_steps * d->max_its + 8;
     long long launched = 0;
@@ -1141,8 +1139,7 @@ static int fom_run_impl(const bfd_fom_desc *d, const SlabView &v, void *ws, cons
         slot ^= 1;
         if (launched > hard_cap) { rc = BFD_ENOTCONVERGED; break; }
     }
-    cudaError_t e = cudaEventRecord(ev[0], st);
-    if (e == cudaSuccess) e = cudaEventSynchronize(ev[0]);
+    cudaError_t e = cudaStreamSynchronize(st);
     if (e != cudaSuccess && rc == BFD_OK) rc = record_cuda_error(e, "fom run sync");
     cudaEventDestroy(ev[0]);
     cudaEventDestroy(ev[1]);

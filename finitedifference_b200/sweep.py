@@ -146,7 +146,6 @@ class SnapshotSweep:
             stream = self._streams[wid]
             try:
                 with torch.cuda.device(self.device), torch.cuda.stream(stream):
-                    done = torch.cuda.Event(blocking=True)
                     w0_dev = w0_pinned.to(self.device, non_blocking=True)
                     while not errors:
                         try:
@@ -166,8 +165,7 @@ class SnapshotSweep:
                         held = []
 
                         def flush():
-                            done.record(stream)             # blocking-sync event: the thread sleeps, it does not spin
-                            done.synchronize()
+                            stream.synchronize()
                             while held:
                                 i, buf = held.pop(0)
                                 try:

@@ -38,7 +38,7 @@ typedef void *cudaStream_t;
 typedef void *cudaEvent_t;
 enum { cudaSuccess = 0 };
 enum { cudaMemcpyDeviceToHost = 0, cudaMemcpyDeviceToDevice = 1, cudaMemcpyHostToDevice = 2 };
-enum { cudaEventBlockingSync = 1, cudaEventDisableTiming = 2 };
+enum { cudaEventDisableTiming = 2 };
 static inline const char *cudaGetErrorName(cudaError_t) { return "emu"; }
 static inline const char *cudaGetErrorString(cudaError_t) { return "emu"; }
 static inline cudaError_t cudaGetLastError() { return cudaSuccess; }
