@@ -24,11 +24,11 @@ from .fom import FomSolver
 from .operators import (get_ops, inviscid_burgers_exact_jac2D, inviscid_burgers_exact_jac2D_ecsw,  # noqa: F401
                         inviscid_burgers_res2D, inviscid_burgers_res2D_alt, inviscid_burgers_res2D_ecsw, make_ddx)
 from .pod import POD  # noqa: F401  (hypernet2D.py:2746)
-from .rom import EcswSolver, LspgSolver, ecsw_training_matrix, generate_augmented_mesh  # noqa: F401
+from .rom import EcswSolver, LspgSolver, ecsw_batch, ecsw_training_matrix, generate_augmented_mesh  # noqa: F401
 
 __all__ = [
     "make_2D_grid", "inviscid_burgers_implicit2D", "inviscid_burgers_implicit2D_batch",
-    "inviscid_burgers_implicit2D_LSPG", "inviscid_burgers_ecsw_fixed", "generate_augmented_mesh",
+    "inviscid_burgers_implicit2D_LSPG", "inviscid_burgers_ecsw_fixed", "inviscid_burgers_ecsw_fixed_batch", "generate_augmented_mesh",
     "compute_ECSW_training_matrix_2D",
     "make_ddx", "get_ops", "inviscid_burgers_res2D", "inviscid_burgers_res2D_alt", "inviscid_burgers_res2D_ecsw",
     "inviscid_burgers_exact_jac2D", "inviscid_burgers_exact_jac2D_ecsw",
@@ -105,6 +105,13 @@ def inviscid_burgers_ecsw_fixed(grid_x, grid_y, weights, w0, dt, num_steps, mu, 
         out += ({"sample_inds": solver.sample_inds, "augmented_sample": solver.augmented_sample,
                  "gn_its": np.array([len(h) for h in hist]), "resnorms": hist},)
     return out
+
+
+def inviscid_burgers_ecsw_fixed_batch(grid_x, grid_y, weights, w0, dt, num_steps, mus, basis, *, device=None):
+    """``inviscid_burgers_ecsw_fixed`` for a list of test parameters (the loops over test mu of
+    run_tests.py:9-10 / run_HPROM_ecsw_joshua.py): the HPROMs run concurrently on one GPU.
+    Returns a list of ``red_coords (k, T+1)`` arrays in the order of ``mus``."""
+    return [red for red, _ in ecsw_batch(grid_x, grid_y, weights, w0, dt, num_steps, mus, basis, device=device)]
 
 
 def compute_ECSW_training_matrix_2D(snaps, prev_snaps, basis, res=None, jac=None, grid_x=None, grid_y=None,

@@ -180,3 +180,20 @@ def test_gram_dmma_equals_library_gemm(M, k, request):
     assert float((b - br).abs().max()) < 1e-12 * scale
     G2, b2 = base.normal_equations(X, f)
     assert torch.equal(G, G2) and torch.equal(b, b2)          # deterministic
+
+
+def test_ecsw_batch_equals_single_runs(h, golden):
+    """Several test parameters iterating concurrently (own solver, stream and graphs each) reproduce the
+    single-parameter drop-in call (to rounding: the batch forms the normal equations with bfd_gram)."""
+    g = golden("ecsw_n24.npz")
+    n, steps = int(g["n"]), int(g["steps"])
+    gx, gy = h.make_2D_grid(0, 100, 0, 100, n, n)
+    w0 = np.ones(2 * n * n)
+    basis = np.ascontiguousarray(g["basis"])
+    mus = [list(g["mu"]), [5.19, 0.026], [4.56, 0.019], [4.3, 0.016], [5.4, 0.029]]
+    batch = h.inviscid_burgers_ecsw_fixed_batch(gx, gy, g["weights"], w0, float(g["dt"]), steps, mus, basis)
+    assert len(batch) == len(mus)
+    assert max(rel(batch[0][:, i], g["red_coords"][:, i]) for i in range(steps + 1)) < TOL
+    for mu, red in zip(mus, batch):
+        single, _ = h.inviscid_burgers_ecsw_fixed(gx, gy, g["weights"], w0, float(g["dt"]), steps, mu, basis)
+        assert red.shape == single.shape and max(rel(red[:, i], single[:, i]) for i in range(steps + 1)) < 1e-12

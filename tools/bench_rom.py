@@ -165,6 +165,20 @@ def main():
         print(json.dumps({"stage": "ecsw_cpu_oracle", "steps": 5, "seconds": cpu_s, "ms_per_step": 200 * cpu_s,
                           "max_rel_diff_reduced_state": diff}), flush=True)
     del ecsw
+    from finitedifference_b200.rom import EcswBatch
+    batch_mus = [[m1, m2] for m1 in (4.3, 4.75, 5.19, 5.45) for m2 in (0.017, 0.021, 0.025, 0.029)]
+    t0 = time.perf_counter()
+    batch = EcswBatch(gx, gy, wts.ravel(), dt, batch_mus, V, device=dev)
+    setup_s = time.perf_counter() - t0
+    batch.run(w0, 2)                                                                      # warm-up
+    t0 = time.perf_counter()
+    out = batch.run(w0, a.ecsw_steps)
+    wall = time.perf_counter() - t0
+    print(json.dumps({"stage": "ecsw_batch", "parameters": len(batch_mus), "steps_each": a.ecsw_steps,
+                      "wall_s": wall, "hprom_steps_per_s": len(batch_mus) * a.ecsw_steps / wall,
+                      "setup_and_capture_s": setup_s,
+                      "gn_residual_evals": sum(len(h) for _, hist in out for h in hist)}), flush=True)
+    del batch
 
     # ---- ECSW training matrix ------------------------------------------------------------
     fom = FomSolver(gx, gy, dt, a.c_snaps + 1, [test_mu], device=dev)
