@@ -32,7 +32,7 @@ DT = 0.05
 NUM_STEPS = 500
 MU1_RANGE = (4.25, 5.5)
 MU2_RANGE = (0.015, 0.03)
-NCU_DRAM_BYTES_PER_CELL_UPDATE = 42.8     # ncu --set full, profiles/r01_fom_full_ncu.md
+NCU_DRAM_BYTES_PER_CELL_UPDATE = 43.1     # ncu --set full, profiles/r01_fom_full_ncu.md
 FP64_INSTR_PER_CELL_UPDATE_K4 = 218       # DFMA/DMUL/DADD issued per cell-update with 4 Newton solves (ncu source page)
 FP64_PEAK_TFLOPS = 34.09                  # measured DFMA peak, profiles/r01_fp64_microbench.txt
 METRIC = "fom_cell_updates_per_s"
@@ -246,7 +246,7 @@ def main():
                 "note": "algorithmic bytes = (48*solves + 32) B per cell-update (SURVEY 8d: one HBM pass per "
                         "Newton sweep). The kernel fuses the sweeps of a time step in registers, so its real DRAM "
                         "traffic is lower (traffic, from ncu) and the binding unit is the FP64 pipe (fp64)",
-                "traffic_source": "profiles/r01_fom_full_ncu.md: dram read+write = 42.8 B per cell-update "
+                "traffic_source": "profiles/r01_fom_full_ncu.md: dram read+write = 43.1 B per cell-update "
                                   "(ncu --set full of this command), scaled to this run's cell-updates per launch",
                 "fp64": {"instr_per_cell_update": FP64_INSTR_PER_CELL_UPDATE_K4,
                          "achieved_tflops": 2e-12 * FP64_INSTR_PER_CELL_UPDATE_K4 * value / world,
