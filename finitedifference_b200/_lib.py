@@ -85,6 +85,8 @@ SIGNATURES = {
     "bfd_rom_residual": (C.c_int, [C.POINTER(RomMesh), _P, _P, _P, _P, _P]),
     "bfd_rom_jv": (C.c_int, [C.POINTER(RomMesh), _P, _P, C.c_int, _P, _P]),
     "bfd_rom_jv_grid": (C.c_int, [C.POINTER(RomMesh), C.c_int, C.c_int, C.c_int, C.c_int, _P, _P, C.c_int, _P, _P]),
+    "bfd_rom_jv_grid_slab": (C.c_int, [C.POINTER(RomMesh), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P,
+                                       C.c_int, _P, _P]),
     "bfd_jac_csr_values": (C.c_int, [C.POINTER(RomMesh), _P, _P, _P]),
     "bfd_ecsw_c_fused": (C.c_int, [C.POINTER(RomMesh), _P, _P, _P, C.c_int, _P, C.c_size_t, _P]),
     "bfd_ecsw_c_grid": (C.c_int, [C.POINTER(RomMesh), C.c_int, C.c_int, _P, _P, _P, C.c_int, _P, C.c_size_t, _P]),

@@ -27,8 +27,16 @@ namespace bfd {
 struct JvGridArgs {
     int nx, ny, k, seg_len, nseg, ngroups;
     const double *cx, *cxl, *cy, *cyd;      // per row i = r*nx + c (bfd_rom_mesh tables)
-    const double *w, *V, *rw;               // state, basis [2N][k], optional residual for the C block
-    double *JV;                             // [2N][k]
+    const double *w, *V, *rw;               // state, basis [2 nP][k] on the P cells, optional residual for the C block
+    double *JV;                             // [2 n_out][k]
+    // Slab view (whole grid: r_lo = 0, r_hi = ny, p_row0 = a_row0 = 0, a_len = ny, wA = w, VA = V).
+    // Owned grid rows [r_lo, r_hi): outputs and coefficient tables are indexed (r - r_lo)*nx + c.
+    // P arrays (w, V) hold grid rows [p_row0, r_hi) in row order: cell (r, c) at (r - p_row0)*nx + c,
+    // v component nP cells further.  A arrays (wA, VA; the :167 operator only) hold the transposed
+    // cells as a column slab: cell (c, r), r in [a_row0, r_hi), at c*a_len + (r - a_row0), v at + nA.
+    int r_lo, r_hi, p_row0, a_row0, a_len;
+    size_t nP, nA, n_out;
+    const double *wA, *VA;
     double *C;                              // CBLOCK: one snapshot's k x N block of the training matrix
     size_t ldc;
 };
@@ -42,8 +50,8 @@ constexpr int kCSeg = 8;                    // columns per segment of the CBLOCK
 template <int R, int MC, bool TRANSPOSED, bool CBLOCK = false>
 __global__ void __launch_bounds__(128) rom_jv_grid_kernel(const JvGridArgs a) {
     BFD_SHARED_ARRAY(double, ctile, [CBLOCK ? 4 : 1][CBLOCK ? kCSeg : 1][CBLOCK ? 32 * MC + 1 : 1]);
-    const int nx = a.nx, ny = a.ny, k = a.k;
-    const size_t N = (size_t)nx * ny;
+    const int nx = a.nx, k = a.k, r_hi = a.r_hi;
+    const size_t nP = a.nP, nA = TRANSPOSED ? a.nA : a.nP, n_out = a.n_out;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int jbase = blockIdx.y * (32 * MC) + lane;
     bool jok[MC];
@@ -55,24 +63,26 @@ __global__ void __launch_bounds__(128) rom_jv_grid_kernel(const JvGridArgs a) {
     }
     const double *__restrict__ V = a.V;
     const double *__restrict__ w = a.w;
+    const double *__restrict__ VA = TRANSPOSED ? a.VA : a.V;
+    const double *__restrict__ wA = TRANSPOSED ? a.wA : a.w;
     const long long ntasks = (long long)a.ngroups * a.nseg;
     for (long long task = (long long)blockIdx.x * 4 + warp; task < ntasks; task += (long long)gridDim.x * 4) {
         const int g = (int)(task / a.nseg), s = (int)(task % a.nseg);
-        const int r0 = g * R, c0 = s * a.seg_len;
+        const int r0 = a.r_lo + g * R, c0 = s * a.seg_len;
         const int c1 = c0 + a.seg_len < nx ? c0 + a.seg_len : nx;
         // left neighbour (own cell of the previous column), per owned row
         double Lu[R][MC], Lv[R][MC], wLu[R], wLv[R];
 #pragma unroll
         for (int rr = 0; rr < R; ++rr) {
             const int r = r0 + rr;
-            const bool ok = c0 > 0 && r < ny;
-            const size_t cell = ok ? (size_t)r * nx + (c0 - 1) : 0;
+            const bool ok = c0 > 0 && r < r_hi;
+            const size_t cell = ok ? (size_t)(r - a.p_row0) * nx + (c0 - 1) : 0;
             wLu[rr] = ok ? w[cell] : 0.0;
-            wLv[rr] = ok ? w[N + cell] : 0.0;
+            wLv[rr] = ok ? w[nP + cell] : 0.0;
 #pragma unroll
             for (int m = 0; m < MC; ++m) {
                 Lu[rr][m] = ok ? V[cell * k + joff[m]] : 0.0;
-                Lv[rr][m] = ok ? V[(N + cell) * k + joff[m]] : 0.0;
+                Lv[rr][m] = ok ? V[(nP + cell) * k + joff[m]] : 0.0;
             }
         }
         for (int c = c0; c < c1; ++c) {
@@ -81,29 +91,31 @@ __global__ void __launch_bounds__(128) rom_jv_grid_kernel(const JvGridArgs a) {
 #pragma unroll
             for (int rr = 0; rr <= R; ++rr) {
                 const int r = r0 - 1 + rr;
-                const bool ok = r >= 0 && r < ny;
-                const size_t cell = !ok ? 0 : TRANSPOSED ? (size_t)c * ny + r : (size_t)r * nx + c;
-                wAu[rr] = ok ? w[cell] : 0.0;
-                wAv[rr] = ok ? w[N + cell] : 0.0;
+                const bool ok = r >= 0 && r < r_hi;
+                const size_t cell = !ok ? 0 : TRANSPOSED ? (size_t)c * a.a_len + (r - a.a_row0)
+                                                         : (size_t)(r - a.p_row0) * nx + c;
+                wAu[rr] = ok ? wA[cell] : 0.0;
+                wAv[rr] = ok ? wA[nA + cell] : 0.0;
 #pragma unroll
                 for (int m = 0; m < MC; ++m) {
-                    Au[rr][m] = ok ? V[cell * k + joff[m]] : 0.0;
-                    Av[rr][m] = ok ? V[(N + cell) * k + joff[m]] : 0.0;
+                    Au[rr][m] = ok ? VA[cell * k + joff[m]] : 0.0;
+                    Av[rr][m] = ok ? VA[(nA + cell) * k + joff[m]] : 0.0;
                 }
             }
 #pragma unroll
             for (int rr = 0; rr < R; ++rr) {
                 const int r = r0 + rr;
-                if (r >= ny) break;
-                const size_t cell = (size_t)r * nx + c;
+                if (r >= r_hi) break;
+                const size_t cell = (size_t)(r - a.r_lo) * nx + c;            // output / coefficient index
                 double Pu[MC], Pv[MC], wPu, wPv;
                 if (TRANSPOSED) {
-                    wPu = w[cell];
-                    wPv = w[N + cell];
+                    const size_t pc = (size_t)(r - a.p_row0) * nx + c;
+                    wPu = w[pc];
+                    wPv = w[nP + pc];
 #pragma unroll
                     for (int m = 0; m < MC; ++m) {
-                        Pu[m] = V[cell * k + joff[m]];
-                        Pv[m] = V[(N + cell) * k + joff[m]];
+                        Pu[m] = V[pc * k + joff[m]];
+                        Pv[m] = V[(nP + pc) * k + joff[m]];
                     }
                 } else {
                     wPu = wAu[rr + 1];
@@ -116,7 +128,7 @@ __global__ void __launch_bounds__(128) rom_jv_grid_kernel(const JvGridArgs a) {
                 // 2x2 blocks of the exact Jacobian (:2719-2732), same grouping as rom_jv_kernel
                 const double pxu = cx * wPu, pxv = cx * wPv, lxu = cxl * wLu[rr], lxv = cxl * wLv[rr];
                 const double ayu = cy * wAu[rr + 1], ayv = cy * wAv[rr + 1], byu = cyd * wAu[rr], byv = cyd * wAv[rr];
-                double *ou = a.JV + cell * k, *ov = a.JV + (N + cell) * k;
+                double *ou = a.JV + cell * k, *ov = a.JV + (n_out + cell) * k;
 #pragma unroll
                 for (int m = 0; m < MC; ++m) {
                     const double vpu = Pu[m], vpv = Pv[m], vlu = Lu[rr][m], vlv = Lv[rr][m];
@@ -124,7 +136,7 @@ __global__ void __launch_bounds__(128) rom_jv_grid_kernel(const JvGridArgs a) {
                     const double ju = vpu + (pxu * vpu - lxu * vlu) + 0.5 * (ayv * vau - byv * vbu) + 0.5 * (ayu * vav - byu * vbv);
                     const double jv = vpv + 0.5 * (pxv * vpu - lxv * vlu) + (ayv * vav - byv * vbv) + 0.5 * (pxu * vpv - lxu * vlv);
                     if (CBLOCK) {
-                        ctile[warp][c - c0][32 * m + lane] = a.rw[cell] * ju + a.rw[N + cell] * jv;
+                        ctile[warp][c - c0][32 * m + lane] = a.rw[cell] * ju + a.rw[n_out + cell] * jv;
                     } else if (jok[m]) {
                         ou[joff[m]] = ju;
                         ov[joff[m]] = jv;
@@ -141,8 +153,8 @@ __global__ void __launch_bounds__(128) rom_jv_grid_kernel(const JvGridArgs a) {
             const int ncol = c1 - c0, j0 = blockIdx.y * (32 * MC);
             for (int e = lane; e < kCSeg * 32 * MC; e += 32) {
                 const int mode = e / kCSeg, cl = e % kCSeg;
-                if (cl < ncol && j0 + mode < k && r0 < ny)
-                    a.C[(size_t)(j0 + mode) * a.ldc + (size_t)r0 * nx + c0 + cl] = ctile[warp][cl][mode];
+                if (cl < ncol && j0 + mode < k && r0 < r_hi)
+                    a.C[(size_t)(j0 + mode) * a.ldc + (size_t)(r0 - a.r_lo) * nx + c0 + cl] = ctile[warp][cl][mode];
             }
             __syncwarp();
         }
@@ -174,9 +186,28 @@ static int launch_cblock(const JvGridArgs &a, int mc, dim3 grid, cudaStream_t st
 
 using namespace bfd;
 
+static int jv_grid_launch(const bfd_rom_mesh *m, int nx, int ny, int transposed, int rows_per_warp, int r_lo, int r_hi,
+                          const double *w, const double *V, const double *wA, const double *VA, int k, double *JV,
+                          void *stream);
+
 extern "C" int bfd_rom_jv_grid(const bfd_rom_mesh *m, int nx, int ny, int transposed, int rows_per_warp,
                                const double *w, const double *V, int k, double *JV, void *stream) {
     if (!m || nx < 1 || ny < 1 || m->nrows != (int64_t)nx * ny || m->ncells != m->nrows) return BFD_EINVAL;
+    return jv_grid_launch(m, nx, ny, transposed, rows_per_warp, 0, ny, w, V, w, V, k, JV, stream);
+}
+
+extern "C" int bfd_rom_jv_grid_slab(const bfd_rom_mesh *m, int nx, int ny, int transposed, int r_lo, int r_hi,
+                                    const double *wP, const double *VP, const double *wA, const double *VA, int k,
+                                    double *JV, void *stream) {
+    if (!m || nx < 1 || ny < 1 || r_lo < 0 || r_hi > ny || r_lo >= r_hi) return BFD_EINVAL;
+    if (m->nrows != (int64_t)nx * (r_hi - r_lo)) return BFD_EINVAL;
+    if (transposed && (!wA || !VA)) return BFD_EINVAL;
+    return jv_grid_launch(m, nx, ny, transposed, 0, r_lo, r_hi, wP, VP, wA, VA, k, JV, stream);
+}
+
+static int jv_grid_launch(const bfd_rom_mesh *m, int nx, int ny, int transposed, int rows_per_warp, int r_lo, int r_hi,
+                          const double *w, const double *V, const double *wA, const double *VA, int k, double *JV,
+                          void *stream) {
     if (!m->cx || !m->cxl || !m->cy || !m->cyd || !w || !V || !JV || k < 1) return BFD_EINVAL;
     if (m->weight) return BFD_EINVAL;                       // weighted rows belong to the sampled mesh
     if (transposed && nx != ny) return BFD_EINVAL;          // :167 permutes a square grid
@@ -185,7 +216,14 @@ extern "C" int bfd_rom_jv_grid(const bfd_rom_mesh *m, int nx, int ny, int transp
     if (const char *e = getenv("BFD_JV_MC")) { const int v = atoi(e); if (v >= 1 && v < mc) mc = v; }   // tuning
     JvGridArgs a{};
     a.nx = nx; a.ny = ny; a.k = k;
-    a.ngroups = (ny + R - 1) / R;
+    a.r_lo = r_lo; a.r_hi = r_hi;
+    a.p_row0 = a.a_row0 = r_lo > 0 ? r_lo - 1 : 0;          // the slab arrays start one row below the owned rows
+    a.a_len = r_hi - a.a_row0;
+    a.nP = (size_t)nx * (r_hi - a.p_row0);
+    a.nA = (size_t)nx * a.a_len;
+    a.n_out = (size_t)nx * (r_hi - r_lo);
+    a.wA = wA; a.VA = VA;
+    a.ngroups = (r_hi - r_lo + R - 1) / R;
     // Short segments: the warps in flight then read neighbouring stretches of the basis, which is
     // what DRAM pages like (measured at 750^2, k = 95: segments of 75 columns 0.44 / 0.59 ms, of
     // 8-16 columns 0.34 / 0.49 ms for the exact / :167 operator); the price is one extra left
@@ -217,6 +255,9 @@ extern "C" int bfd_ecsw_c_grid(const bfd_rom_mesh *m, int nx, int ny, const doub
     a.nseg = (nx + a.seg_len - 1) / a.seg_len;
     a.cx = m->cx; a.cxl = m->cxl; a.cy = m->cy; a.cyd = m->cyd;
     a.w = w; a.V = V; a.rw = r; a.JV = nullptr; a.C = Cblk; a.ldc = ldc;
+    a.r_lo = 0; a.r_hi = ny; a.p_row0 = a.a_row0 = 0; a.a_len = ny;
+    a.nP = a.nA = a.n_out = (size_t)nx * ny;
+    a.wA = w; a.VA = V;
     const long long ntasks = (long long)a.ngroups * a.nseg;
     long long blocks = (ntasks + 3) / 4;
     if (blocks > 148 * 64) blocks = 148 * 64;

@@ -278,9 +278,10 @@ class ShardedLspgSolver(_RomBase):
     Gauss-Newton iteration are the only exchanges, the reduced state ``y`` is replicated and
     every rank takes the same stopping decisions from the same reduced numbers
     (``gauss_newton_LSPG``, hypernet2D.py:1935-2005).  A rank keeps only the basis rows of the
-    state cells its stencils read -- its rows, the row below, and for the :167 operator the
-    transposed cells (a column slab) -- i.e. about 2/world of ``V``; ``w = V y`` is formed locally
-    on exactly those cells, so no halo exchange exists.
+    state cells its stencils read: the *row slab* (its rows and the row below) and, for the :167
+    operator, the *column slab* of the transposed cells -- about 2/world of ``V``; ``w = V y`` is formed
+    locally on exactly those cells, so no halo exchange exists.  ``J V`` walks the slab
+    (``bfd_rom_jv_grid_slab``), the normal equations run on the FP64 tensor cores (``bfd_gram``).
     """
 
     def __init__(self, grid_x, grid_y, dt, mu, basis, rank=None, world=None, group=None, device=None,
@@ -294,32 +295,33 @@ class ShardedLspgSolver(_RomBase):
         from .sharding import shard_range
         gx, gy = np.asarray(grid_x, dtype=np.float64), np.asarray(grid_y, dtype=np.float64)
         nx, ny = gx.size - 1, gy.size - 1
-        self.n_cells, self.mu = nx * ny, list(mu)[:2]
-        block = shard_range(ny, self.rank, self.world)
-        self.row_range = (block.start, block.stop)
-        rows = np.arange(block.start * nx, block.stop * nx, dtype=np.int64)
-        r, c = np.divmod(rows, nx)
-        need = [rows, rows[c >= 1] - 1, rows[r >= 1] - nx]
-        if jacobian == "reference":
-            if nx != ny:
-                raise ValueError("the reference's LSPG operator (hypernet2D.py:167) needs nx == ny")
-            need += [c * ny + r, (c * ny + r - 1)[r >= 1]]
-        elif jacobian != "exact":
+        self.nx, self.ny, self.n_cells, self.mu = nx, ny, nx * ny, list(mu)[:2]
+        if jacobian not in ("exact", "reference"):
             raise ValueError(jacobian)
-        self.rows = rows
-        self.state_cells = np.unique(np.concatenate(need)).astype(np.int64) if rows.size else rows
+        if jacobian == "reference" and nx != ny:
+            raise ValueError("the reference's LSPG operator (hypernet2D.py:167) needs nx == ny")
+        self.transposed = int(jacobian == "reference")
+        block = shard_range(ny, self.rank, self.world)
+        r_lo, r_hi = block.start, block.stop
+        self.row_range = (r_lo, r_hi)
+        row0 = max(r_lo - 1, 0)
+        self.rows = np.arange(r_lo * nx, r_hi * nx, dtype=np.int64)
+        pcells = np.arange(row0 * nx, r_hi * nx, dtype=np.int64)                     # row slab
+        acells = (np.arange(nx, dtype=np.int64)[:, None] * ny + np.arange(row0, r_hi, dtype=np.int64)[None, :]).ravel() \
+            if self.transposed else np.empty(0, dtype=np.int64)                       # column slab
+        self.state_cells = np.union1d(pcells, acells)
         basis = basis.cpu().numpy() if isinstance(basis, torch.Tensor) else np.asarray(basis, dtype=np.float64)
         self.k = basis.shape[1]
-        idx = np.concatenate((self.state_cells, self.n_cells + self.state_cells))
-        own = np.concatenate((rows, self.n_cells + rows))
-        self.V_state = self._dev(basis[idx])            # basis on the state cells [u | v]
-        self.V_own = self._dev(basis[own])              # basis on the owned cells [u | v]: y0 and the snapshots
-        if rows.size:
-            self.res_mesh = MeshTables(gx, gy, dt, self.mu, self.device, rows=rows, state_cells=self.state_cells,
-                                       inlet="grid")
-            self.jac_mesh = self.res_mesh if jacobian == "exact" else \
-                MeshTables(gx, gy, dt, self.mu, self.device, rows=rows, state_cells=self.state_cells,
-                           jacobian="reference", inlet="grid")
+        pick = lambda cells: np.concatenate((cells, self.n_cells + cells))
+        self.nP, self.off = pcells.size, (r_lo - row0) * nx                           # owned cells start at `off` in the row slab
+        self.V_P = self._dev(basis[pick(pcells)])
+        self.V_A = self._dev(basis[pick(acells)]) if self.transposed and self.rows.size else None
+        if self.rows.size:
+            self.mesh = MeshTables(gx, gy, dt, self.mu, self.device, rows=self.rows, state_cells=pcells, inlet="grid")
+
+    def _own(self, t):
+        """The owned cells' [u | v] entries of a row-slab vector / matrix."""
+        return torch.cat((t[self.off:self.nP], t[self.nP + self.off:]))
 
     def _allreduce(self, t):
         if self.world > 1:
@@ -329,18 +331,25 @@ class ShardedLspgSolver(_RomBase):
     def _residual(self, w, wp):
         """(f_local, ||f|| over all ranks)."""
         n2 = torch.zeros(1, dtype=torch.float64, device=self.device)
+        f = torch.empty(2 * self.rows.size, dtype=torch.float64, device=self.device)
         if self.rows.size:
-            f = torch.empty(2 * self.rows.size, dtype=torch.float64, device=self.device)
-            _lib.check(self.lib.bfd_rom_residual(C.byref(self.res_mesh.c), w.data_ptr(), wp.data_ptr(), f.data_ptr(),
+            _lib.check(self.lib.bfd_rom_residual(C.byref(self.mesh.c), w.data_ptr(), wp.data_ptr(), f.data_ptr(),
                                                  n2.data_ptr(), self._stream()), self.lib, "bfd_rom_residual")
-        else:
-            f = torch.empty(0, dtype=torch.float64, device=self.device)
         return f, float(torch.sqrt(self._allreduce(n2)).item())
 
+    def _jv(self, w, wA):
+        JV = torch.empty((2 * self.rows.size, self.k), dtype=torch.float64, device=self.device)
+        _lib.check(self.lib.bfd_rom_jv_grid_slab(C.byref(self.mesh.c), self.nx, self.ny, self.transposed, self.row_range[0],
+                                                 self.row_range[1], w.data_ptr(), self.V_P.data_ptr(),
+                                                 wA.data_ptr() if self.transposed else None,
+                                                 self.V_A.data_ptr() if self.transposed else None, self.k,
+                                                 JV.data_ptr(), self._stream()), self.lib, "bfd_rom_jv_grid_slab")
+        return JV
+
     def _gauss_newton(self, y0, wp, max_its=20, relnorm_cutoff=1e-5, min_delta=0.1):
-        k, V = self.k, self.V_state
+        k = self.k
         y = y0.clone()
-        w = V @ y
+        w = self.V_P @ y
         f, init_norm = self._residual(w, wp)
         resnorms = []
         for it in range(max_its):
@@ -355,13 +364,13 @@ class ShardedLspgSolver(_RomBase):
                 break
             Gb = torch.zeros((k, k + 1), dtype=torch.float64, device=self.device)
             if self.rows.size:
-                JV = self.jv(self.jac_mesh, w, V)
+                JV = self._jv(w, self.V_A @ y if self.transposed else None)
                 G, b = self.normal_equations(JV, f)
                 Gb[:, :k] = G
-                Gb[:, k] = -b
+                Gb[:, k] = b
             self._allreduce(Gb)
-            y = y - self.gn_step(Gb[:, :k].contiguous(), Gb[:, k].contiguous())   # Gb[:, k] holds -b
-            w = V @ y
+            y = y + self.gn_step(Gb[:, :k].contiguous(), Gb[:, k].contiguous())
+            w = self.V_P @ y
         return y, w, resnorms
 
     def run(self, w0, num_steps):
@@ -369,16 +378,16 @@ class ShardedLspgSolver(_RomBase):
         owned cells' [u | v] --, red_coords (T+1, k), per-step resnorm lists)`` on the device."""
         w0 = np.asarray(w0.cpu() if isinstance(w0, torch.Tensor) else w0, dtype=np.float64).ravel()
         own = np.concatenate((self.rows, self.n_cells + self.rows))
-        y = self._allreduce(self.V_own.T @ self._dev(w0[own]))          # :158, summed over the row blocks
-        w = self.V_state @ y                                            # :159 on the cells this rank reads
+        y = self._allreduce(self._own(self.V_P).T @ self._dev(w0[own]))     # :158, summed over the row blocks
+        w = self.V_P @ y                                                   # :159 on the row slab
         snaps = torch.empty((num_steps + 1, 2 * self.rows.size), dtype=torch.float64, device=self.device)
         red = torch.empty((num_steps + 1, self.k), dtype=torch.float64, device=self.device)
-        snaps[0], red[0] = self.V_own @ y, y
+        snaps[0], red[0] = self._own(w), y
         history = []
         for i in range(num_steps):
             y, w, resnorms = self._gauss_newton(y, w)
             history.append(resnorms)
-            snaps[i + 1], red[i + 1] = self.V_own @ y, y
+            snaps[i + 1], red[i + 1] = self._own(w), y                     # :196: the stored snapshot is basis @ y
         return snaps, red, history
 
     def gather_snapshots(self, snaps_own):

@@ -216,6 +216,17 @@ int bfd_rom_jv(const bfd_rom_mesh *mesh, const double *w, const double *V, int k
 int bfd_rom_jv_grid(const bfd_rom_mesh *mesh, int nx, int ny, int transposed, int rows_per_warp,
                     const double *w, const double *V, int k, double *JV, void *stream);
 
+/* bfd_rom_jv_grid on a SLAB of grid rows [r_lo, r_hi) (LSPG rows dealt to the ranks of a process
+ * group): `mesh` lists the owned cells in row order (nrows = nx*(r_hi-r_lo)); the state and basis
+ * come as two slabs that start one grid row below the owned rows, row0 = max(r_lo-1, 0):
+ *   wP, VP : grid rows [row0, r_hi) in row order, [u | v] with nx*(r_hi-row0) cells per component;
+ *   wA, VA : (transposed = 1 only) the transposed cells as a column slab: cell (c, r), r in [row0, r_hi),
+ *            at c*(r_hi-row0) + (r-row0), [u | v] with nx*(r_hi-row0) cells per component.
+ * JV[2*nrows][k]: rows of the owned cells [u | v].  Same arithmetic as bfd_rom_jv_grid. */
+int bfd_rom_jv_grid_slab(const bfd_rom_mesh *mesh, int nx, int ny, int transposed, int r_lo, int r_hi,
+                         const double *wP, const double *VP, const double *wA, const double *VA, int k,
+                         double *JV, void *stream);
+
 /* Values of the Jacobian rows of `mesh` at state w, 12 per row i at vals[12*i ..], in fixed slots
  * whose columns the caller derives from the index tables (N = ncells):
  *   u row i:      (p) (xl) (ja) (jb) (N+ja) (N+jb)

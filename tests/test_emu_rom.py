@@ -221,3 +221,34 @@ def test_spd_solve_single_cta(lib, k):
     want = -np.linalg.solve(G, b)
     assert np.allclose(x, want, rtol=1e-10, atol=1e-12 * np.abs(want).max())
     assert lib.bfd_spd_solve(E.ptr(G), E.ptr(b), 97, 1.0, E.ptr(x), None) == -1
+
+
+@pytest.mark.parametrize("n,k,blocks", [(12, 5, [(0, 12)]), (13, 40, [(0, 5), (5, 6), (6, 13)]), (9, 70, [(0, 1), (1, 9)])])
+def test_grid_walk_jv_on_row_slabs(lib, n, k, blocks):
+    """bfd_rom_jv_grid_slab: the rows of a block of grid rows from slab-local state / basis arrays
+    (row slab starting one row below; column slab of the transposed cells for hypernet2D.py:167)
+    equal the same rows of the whole-grid call."""
+    gx, gy = orc.make_2D_grid(0, 100, 0, 100, n, n)
+    gx = gx + 0.2 * np.cos(gx)
+    rng = np.random.default_rng(n + k)
+    N = n * n
+    w = 1.0 + rng.random(2 * N)
+    V = rng.standard_normal((2 * N, k))
+    for name, transposed in (("exact", 0), ("reference", 1)):
+        whole = run_jv_grid(lib, MeshTables(gx, gy, 0.05, [4.3, 0.021], CPU, jacobian=name), n, n, transposed, 0, w, V)
+        for r_lo, r_hi in blocks:
+            row0 = max(r_lo - 1, 0)
+            own = np.arange(r_lo * n, r_hi * n)
+            pcells = np.arange(row0 * n, r_hi * n)
+            acells = (np.arange(n)[:, None] * n + np.arange(row0, r_hi)[None, :]).ravel()
+            pick = lambda cells: np.concatenate((cells, N + cells))
+            wP, VP = np.ascontiguousarray(w[pick(pcells)]), np.ascontiguousarray(V[pick(pcells)])
+            wA, VA = np.ascontiguousarray(w[pick(acells)]), np.ascontiguousarray(V[pick(acells)])
+            mesh = MeshTables(gx, gy, 0.05, [4.3, 0.021], CPU, rows=own, state_cells=pcells, inlet="grid")
+            JV = np.full((2 * own.size, k), np.nan)
+            assert lib.bfd_rom_jv_grid_slab(C.byref(mesh.c), n, n, transposed, r_lo, r_hi, E.ptr(wP), E.ptr(VP),
+                                            E.ptr(wA) if transposed else None, E.ptr(VA) if transposed else None,
+                                            k, E.ptr(JV), None) == 0
+            assert np.array_equal(JV, whole[pick(own)]), (name, r_lo, r_hi)
+    assert lib.bfd_rom_jv_grid_slab(C.byref(mesh.c), n, n, 1, r_lo, r_hi, E.ptr(wP), E.ptr(VP), None, None, k, E.ptr(JV),
+                                    None) == -1
