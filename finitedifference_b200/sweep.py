@@ -83,6 +83,7 @@ class SnapshotSweep:
         self.n2 = 2 * (self.grid_x.size - 1) * (self.grid_y.size - 1)
         self._pool = None
         self._pool_lock = threading.Lock()
+        self._copy_lock = threading.Lock()
         self._solvers = {}        # (worker, batch) -> FomSolver
         self._stage = {}          # worker -> list of device staging tensors
         self._streams = [torch.cuda.Stream(device=self.device) for _ in range(self.workers)]
@@ -162,31 +163,25 @@ class SnapshotSweep:
                         while len(stage) < len(idx):
                             stage.append(torch.empty((self.n2, self.num_steps + 1), dtype=torch.float64,
                                                      device=self.device))
-                        held = []
-
-                        def flush():
-                            stream.synchronize()
-                            while held:
-                                i, buf = held.pop(0)
-                                try:
-                                    sink(i, mus[i], buf.numpy())
-                                finally:
-                                    self._pool.put(buf)
-
                         for j, i in enumerate(idx):
                             solver.snapshots_device(j, layout=1, out=stage[j])
-                            if out is not None:
-                                dst = out[i] if isinstance(out[i], torch.Tensor) else torch.from_numpy(out[i])
+                            pooled = out is None
+                            if pooled:
+                                dst = self._get_pool().get()
                             else:
-                                pool = self._get_pool()
-                                try:
-                                    dst = pool.get_nowait()
-                                except queue.Empty:
-                                    flush()             # never wait for a buffer while holding one
-                                    dst = pool.get()
-                                held.append((i, dst))
-                            dst.copy_(stage[j], non_blocking=True)
-                        flush()
+                                dst = out[i] if isinstance(out[i], torch.Tensor) else torch.from_numpy(out[i])
+                            try:
+                                # one device-to-host copy at a time per process: a single copy saturates the
+                                # PCIe link, concurrent ones only contend (on boxes where several GPUs share
+                                # the host's ingest bandwidth they make every rank slower)
+                                with self._copy_lock:
+                                    dst.copy_(stage[j], non_blocking=True)
+                                    stream.synchronize()
+                                if pooled:
+                                    sink(i, mus[i], dst.numpy())
+                            finally:
+                                if pooled:
+                                    self._pool.put(dst)
             except BaseException as e:          # noqa: BLE001 - re-raised in the caller's thread
                 errors.append(e)
 
