@@ -275,3 +275,65 @@ extern "C" int bfd_spd_solve(const double *G, const double *b, int k, double sca
     BFD_LAUNCHED();
     return BFD_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// w = V y (basis.dot(y), :1999 / :2042 / :196): M rows of k <= 96 doubles against a k-vector.
+// HBM-bound: 8 M k bytes.  A warp takes 4 consecutive rows (3 KB contiguous, lane = mode, three
+// chunks of 32 modes), keeps y in registers and reduces the four partial sums together: two
+// "give half, keep half" exchanges leave every lane with one row's partial, three more finish
+// it -- 6 shuffles for 4 rows instead of 20.
+// ------------------------------------------------------------------------------------------
+namespace bfd {
+
+template <int MC>
+__global__ void __launch_bounds__(256) basis_times_y_kernel(const double *__restrict__ V, const double *__restrict__ y,
+                                                           long long M, int k, double *__restrict__ w) {
+    const int lane = threadIdx.x & 31;
+    double yr[MC];
+    bool ok[MC];
+#pragma unroll
+    for (int m = 0; m < MC; ++m) {
+        ok[m] = lane + 32 * m < k;
+        yr[m] = ok[m] ? y[lane + 32 * m] : 0.0;
+    }
+    const long long nquads = (M + 3) / 4;
+    const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long q = warp0; q < nquads; q += nwarps) {
+        const long long r0 = q * 4;
+        double a[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const long long r = r0 + i < M ? r0 + i : M - 1;      // tail rows: recomputed, not stored
+            const double *row = V + r * k + lane;
+            double s = 0.0;
+#pragma unroll
+            for (int m = 0; m < MC; ++m) s += (ok[m] ? row[32 * m] : 0.0) * yr[m];
+            a[i] = s;
+        }
+        const bool hi = lane & 16;
+        double r0s = (hi ? a[2] : a[0]) + __shfl_xor_sync(0xffffffffu, hi ? a[0] : a[2], 16);
+        double r1s = (hi ? a[3] : a[1]) + __shfl_xor_sync(0xffffffffu, hi ? a[1] : a[3], 16);
+        const bool mid = lane & 8;
+        double s = (mid ? r1s : r0s) + __shfl_xor_sync(0xffffffffu, mid ? r0s : r1s, 8);
+        s += __shfl_xor_sync(0xffffffffu, s, 4);
+        s += __shfl_xor_sync(0xffffffffu, s, 2);
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        const long long row = r0 + (hi ? 2 : 0) + (mid ? 1 : 0);
+        if ((lane & 7) == 0 && row < M) w[row] = s;
+    }
+}
+
+}  // namespace bfd
+
+extern "C" int bfd_basis_times_y(const double *V, const double *y, int64_t M, int k, double *w, void *stream) {
+    if (!V || !y || !w || M < 1 || k < 1 || k > 96) return BFD_EINVAL;
+    long long blocks = ((M + 3) / 4 + 7) / 8;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    const int grid = (int)BFD_GRID((int)blocks);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (k > 64) BFD_LAUNCH((basis_times_y_kernel<3>), grid, 256, 0, st, V, y, (long long)M, k, w);
+    else if (k > 32) BFD_LAUNCH((basis_times_y_kernel<2>), grid, 256, 0, st, V, y, (long long)M, k, w);
+    else BFD_LAUNCH((basis_times_y_kernel<1>), grid, 256, 0, st, V, y, (long long)M, k, w);
+    BFD_LAUNCHED();
+    return BFD_OK;
+}

@@ -175,6 +175,16 @@ class _RomBase:
                                            self._stream()), self.lib, "bfd_rom_jv")
         return JV
 
+    def basis_times(self, V, y, out=None):
+        """``w = V @ y`` (:1999, :2042): the streaming kernel ``bfd_basis_times_y`` for k <= 96."""
+        M, k = V.shape
+        if k > 96 or M == 0 or not V.is_contiguous():
+            return torch.mv(V, y, out=out) if out is not None else V @ y
+        w = torch.empty(M, dtype=torch.float64, device=self.device) if out is None else out
+        _lib.check(self.lib.bfd_basis_times_y(V.data_ptr(), y.contiguous().data_ptr(), M, k, w.data_ptr(), self._stream()),
+                   self.lib, "bfd_basis_times_y")
+        return w
+
     def normal_equations(self, JV, f):
         """``(G, b) = (JV^T JV, JV^T f)``: the DMMA kernel ``bfd_gram`` for k <= 96, library GEMMs beyond."""
         M, k = JV.shape
@@ -208,7 +218,7 @@ class _RomBase:
         Returns ``(y, w, resnorms)``; the two stopping rules are the reference's, in its order.
         """
         y = y0.clone()
-        w = V @ y
+        w = self.basis_times(V, y)
         f, init_norm = self.residual(res_mesh, w, wp)
         resnorms = []
         for it in range(max_its):
@@ -230,7 +240,7 @@ class _RomBase:
             t0 = time.perf_counter()
             G, b = self.normal_equations(JV, f)            # normal equations of lstsq(JV, -f)
             y = y + self.gn_step(G, b)
-            w = V @ y
+            w = self.basis_times(V, y)
             self._sync()
             self.ls_time += time.perf_counter() - t0
         return y, w, resnorms
@@ -257,7 +267,7 @@ class LspgSolver(_RomBase):
         V = self.V
         w0 = w0 if isinstance(w0, torch.Tensor) else self._dev(np.asarray(w0, dtype=np.float64).ravel())
         y = V.T @ w0                                        # :158
-        w = V @ y                                           # :159
+        w = self.basis_times(V, y)                          # :159
         snaps = torch.empty((num_steps + 1, V.shape[0]), dtype=torch.float64, device=self.device)
         red = torch.empty((num_steps + 1, V.shape[1]), dtype=torch.float64, device=self.device)
         snaps[0], red[0] = w, y
@@ -349,7 +359,7 @@ class ShardedLspgSolver(_RomBase):
     def _gauss_newton(self, y0, wp, max_its=20, relnorm_cutoff=1e-5, min_delta=0.1):
         k = self.k
         y = y0.clone()
-        w = self.V_P @ y
+        w = self.basis_times(self.V_P, y)
         f, init_norm = self._residual(w, wp)
         resnorms = []
         for it in range(max_its):
@@ -364,13 +374,13 @@ class ShardedLspgSolver(_RomBase):
                 break
             Gb = torch.zeros((k, k + 1), dtype=torch.float64, device=self.device)
             if self.rows.size:
-                JV = self._jv(w, self.V_A @ y if self.transposed else None)
+                JV = self._jv(w, self.basis_times(self.V_A, y) if self.transposed else None)
                 G, b = self.normal_equations(JV, f)
                 Gb[:, :k] = G
                 Gb[:, k] = b
             self._allreduce(Gb)
             y = y + self.gn_step(Gb[:, :k].contiguous(), Gb[:, k].contiguous())
-            w = self.V_P @ y
+            w = self.basis_times(self.V_P, y)
         return y, w, resnorms
 
     def run(self, w0, num_steps):
@@ -379,7 +389,7 @@ class ShardedLspgSolver(_RomBase):
         w0 = np.asarray(w0.cpu() if isinstance(w0, torch.Tensor) else w0, dtype=np.float64).ravel()
         own = np.concatenate((self.rows, self.n_cells + self.rows))
         y = self._allreduce(self._own(self.V_P).T @ self._dev(w0[own]))     # :158, summed over the row blocks
-        w = self.V_P @ y                                                   # :159 on the row slab
+        w = self.basis_times(self.V_P, y)                                  # :159 on the row slab
         snaps = torch.empty((num_steps + 1, 2 * self.rows.size), dtype=torch.float64, device=self.device)
         red = torch.empty((num_steps + 1, self.k), dtype=torch.float64, device=self.device)
         snaps[0], red[0] = self._own(w), y
@@ -472,7 +482,7 @@ class EcswSolver(_RomBase):
                                       self._stream()), lib, "bfd_rom_jv")
             G, b = self.normal_equations(self._JV, self._f)
             self._y.add_(self.gn_step(G, b))                # y += lstsq(JV, -f)
-            torch.mv(V, self._y, out=self._w)
+            self.basis_times(V, self._y, out=self._w)
             residual_part()
 
         side = torch.cuda.Stream(device=dev)

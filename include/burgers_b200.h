@@ -272,6 +272,10 @@ int bfd_gram(const double *X, const double *f, int64_t M, int k, double *G, doub
  * this is the Gauss-Newton step dy = lstsq(JV, -f) of :1994 / :2038 (scale = -1). */
 int bfd_spd_solve(const double *G, const double *b, int k, double scale, double *x, void *stream);
 
+/* w[M] = V y for a row-major basis V[M][k], k <= 96 (basis.dot(y) of :1999, :2042, :196): HBM-bound
+ * streaming product, four rows per warp. */
+int bfd_basis_times_y(const double *V, const double *y, int64_t M, int k, double *w, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

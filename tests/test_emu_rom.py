@@ -252,3 +252,15 @@ def test_grid_walk_jv_on_row_slabs(lib, n, k, blocks):
             assert np.array_equal(JV, whole[pick(own)]), (name, r_lo, r_hi)
     assert lib.bfd_rom_jv_grid_slab(C.byref(mesh.c), n, n, 1, r_lo, r_hi, E.ptr(wP), E.ptr(VP), None, None, k, E.ptr(JV),
                                     None) == -1
+
+
+@pytest.mark.parametrize("M,k", [(1, 1), (7, 5), (64, 32), (101, 33), (250, 64), (333, 95), (40, 96)])
+def test_basis_times_y(lib, M, k):
+    """bfd_basis_times_y (four rows per warp, joint shuffle reduction) against NumPy."""
+    rng = np.random.default_rng(M + k)
+    V = np.ascontiguousarray(rng.standard_normal((M, k)))
+    y = rng.standard_normal(k)
+    w = np.full(M + 2, np.nan)
+    assert lib.bfd_basis_times_y(E.ptr(V), E.ptr(y), M, k, E.ptr(w), None) == 0
+    assert np.allclose(w[:M], V @ y, rtol=1e-13, atol=1e-13) and np.isnan(w[M:]).all()
+    assert lib.bfd_basis_times_y(E.ptr(V), E.ptr(y), M, 97, E.ptr(w), None) == -1

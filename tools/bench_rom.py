@@ -106,6 +106,8 @@ def main():
     _, solve_lib_ms = timed(lambda: lspg.gn_step(Gd, bd), 20)
     solve_diff = float((lspg.gn_step(Gd, bd) - (rom_mod.__setattr__("SPD_SOLVE_KERNEL", True) or lspg.gn_step(Gd, bd))).abs().max())
     _, vy_ms = timed(lambda: V @ red[1], 5)
+    _, vyk_ms = timed(lambda: lspg.basis_times(V, red[1]), 5)
+    vy_diff = float((lspg.basis_times(V, red[1]) - V @ red[1]).abs().max())
     jv_bytes = 8 * 2 * N * k * 2 + N * (5 * 4 + 4 * 8 + 16)        # read V once, write JV, tables + state
     print(json.dumps({
         "stage": "lspg", "steps": a.lspg_steps, "gn_residual_evals": its, "gn_solves": solves,
@@ -121,6 +123,8 @@ def main():
                              "includes": "b = (JV)^T f"},
         "spd_solve_kernel": {"ms": solve_ms, "cusolver_potrf_potrs_ms": solve_lib_ms, "max_abs_diff": solve_diff},
         "V_times_y_cublas": {"ms": vy_ms, "GBps": 8 * 2 * N * k / vy_ms / 1e6},
+        "basis_times_y_kernel": {"ms": vyk_ms, "GBps": 8 * 2 * N * k / vyk_ms / 1e6, "frac_of_hbm_peak": 8 * 2 * N * k / vyk_ms / 1e6 / hbm,
+                                 "max_abs_diff_vs_gemv": vy_diff},
         "host_timers_s": {"jac": lspg.jac_time, "res": lspg.res_time, "ls": lspg.ls_time}}), flush=True)
 
     if a.cpu:
