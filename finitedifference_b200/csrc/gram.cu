@@ -16,6 +16,7 @@
 //     small kernel adds the partials in a fixed order (deterministic: replicas and ranks agree
 //     bit for bit) and mirrors the upper triangle.
 #include "wavefront.cuh"
+#include <stdlib.h>
 
 namespace bfd {
 
@@ -300,14 +301,23 @@ __global__ void __launch_bounds__(256) basis_times_y_kernel(const double *__rest
     const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
     for (long long q = warp0; q < nquads; q += nwarps) {
         const long long r0 = q * 4;
-        double a[4];
+        // all 4 x MC loads go out before the first product: with the loads of a row issued next to
+        // their DFMAs the compiler reuses three registers and only 768 B per warp are in flight
+        // (3.6 TB/s instead of the 6.8 TB/s a read-only stream reaches on this part)
+        double v[4][MC];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const long long r = r0 + i < M ? r0 + i : M - 1;      // tail rows: recomputed, not stored
             const double *row = V + r * k + lane;
+#pragma unroll
+            for (int m = 0; m < MC; ++m) v[i][m] = ok[m] ? __ldg(row + 32 * m) : 0.0;
+        }
+        double a[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
             double s = 0.0;
 #pragma unroll
-            for (int m = 0; m < MC; ++m) s += (ok[m] ? row[32 * m] : 0.0) * yr[m];
+            for (int m = 0; m < MC; ++m) s += v[i][m] * yr[m];
             a[i] = s;
         }
         const bool hi = lane & 16;
@@ -323,17 +333,108 @@ __global__ void __launch_bounds__(256) basis_times_y_kernel(const double *__rest
     }
 }
 
+// The main kernel: the 4 rows of a quad are 4k contiguous doubles starting on a 16-byte boundary.
+// Every warp streams its quads through a private 3-stage shared-memory ring with 16-byte cp.async
+// copies, so the bytes in flight do not depend on how the compiler schedules register loads (the
+// register version above keeps 768 B per warp in flight: ptxas interleaves loads and DFMAs to save
+// registers, and the kernel stops at 3.6 TB/s where a read-only stream reaches 6.8 TB/s).  Which
+// row and which mode an element belongs to depends only on (lane, pair), not on the quad, so the
+// matching y values and row numbers are looked up once, before the loop.
+constexpr int kVyWarps = 4, kVyStages = 3, kVyStageDoubles = 4 * 96;
+
+template <int NP>                       // 16-byte pairs per lane: ceil(2k / 32)
+__global__ void __launch_bounds__(32 * kVyWarps) basis_times_y_async_kernel(const double *__restrict__ V,
+                                                                           const double *__restrict__ y, long long nquads,
+                                                                           int k, double *__restrict__ w) {
+    BFD_SHARED_ARRAY(double, ring, [kVyWarps][kVyStages][kVyStageDoubles]);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double yv[NP][2];
+    int rid[NP][2];
+#pragma unroll
+    for (int i = 0; i < NP; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int e = 2 * (lane + 32 * i) + j;
+            const bool ok = e < 4 * k;
+            const int row = ok ? e / k : 4;
+            rid[i][j] = row;
+            yv[i][j] = ok ? y[e - row * k] : 0.0;
+        }
+    const saddr mine = smem_addr(&ring[warp][0][0]);
+    const long long warp0 = (long long)blockIdx.x * kVyWarps + warp, nwarps = (long long)gridDim.x * kVyWarps;
+    auto issue = [&](long long q, int st) {
+        if (q < nquads) {
+            const double *base = V + q * 4 * k;
+#pragma unroll
+            for (int i = 0; i < NP; ++i) {
+                const int p = lane + 32 * i;
+                if (2 * p < 4 * k) cp_async16(mine + (saddr)((st * kVyStageDoubles + 2 * p) * 8), base + 2 * p);
+            }
+        }
+        cp_async_commit();
+    };
+    for (int s = 0; s < kVyStages - 1; ++s) issue(warp0 + s * nwarps, s);
+    int it = 0;
+    for (long long q = warp0; q < nquads; q += nwarps, ++it) {
+        cp_async_wait_pending<kVyStages - 2>();
+        __syncwarp();                                   // every lane's copies of this quad have landed; last quad's reads are done
+        issue(q + (kVyStages - 1) * nwarps, (it + kVyStages - 1) % kVyStages);
+        const saddr sb = mine + (saddr)((it % kVyStages) * kVyStageDoubles * 8);
+        double a[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+        for (int i = 0; i < NP; ++i) {
+            const int p = lane + 32 * i;
+            double v0 = 0.0, v1 = 0.0;
+            if (2 * p < 4 * k) lds2(sb + (saddr)(2 * p * 8), v0, v1);
+            const double p0 = v0 * yv[i][0], p1 = v1 * yv[i][1];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) a[r] += (rid[i][0] == r ? p0 : 0.0) + (rid[i][1] == r ? p1 : 0.0);
+        }
+        const bool hi = lane & 16;
+        double r0s = (hi ? a[2] : a[0]) + __shfl_xor_sync(0xffffffffu, hi ? a[0] : a[2], 16);
+        double r1s = (hi ? a[3] : a[1]) + __shfl_xor_sync(0xffffffffu, hi ? a[1] : a[3], 16);
+        const bool mid = lane & 8;
+        double s = (mid ? r1s : r0s) + __shfl_xor_sync(0xffffffffu, mid ? r0s : r1s, 8);
+        s += __shfl_xor_sync(0xffffffffu, s, 4);
+        s += __shfl_xor_sync(0xffffffffu, s, 2);
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        if ((lane & 7) == 0) w[q * 4 + (hi ? 2 : 0) + (mid ? 1 : 0)] = s;
+    }
+}
+
 }  // namespace bfd
 
-extern "C" int bfd_basis_times_y(const double *V, const double *y, int64_t M, int k, double *w, void *stream) {
-    if (!V || !y || !w || M < 1 || k < 1 || k > 96) return BFD_EINVAL;
+static int basis_times_y_rows(const double *V, const double *y, long long M, int k, double *w, cudaStream_t st) {
     long long blocks = ((M + 3) / 4 + 7) / 8;
     if (blocks > 148 * 8) blocks = 148 * 8;
     const int grid = (int)BFD_GRID((int)blocks);
-    cudaStream_t st = (cudaStream_t)stream;
-    if (k > 64) BFD_LAUNCH((basis_times_y_kernel<3>), grid, 256, 0, st, V, y, (long long)M, k, w);
-    else if (k > 32) BFD_LAUNCH((basis_times_y_kernel<2>), grid, 256, 0, st, V, y, (long long)M, k, w);
-    else BFD_LAUNCH((basis_times_y_kernel<1>), grid, 256, 0, st, V, y, (long long)M, k, w);
+    if (k > 64) BFD_LAUNCH((basis_times_y_kernel<3>), grid, 256, 0, st, V, y, M, k, w);
+    else if (k > 32) BFD_LAUNCH((basis_times_y_kernel<2>), grid, 256, 0, st, V, y, M, k, w);
+    else BFD_LAUNCH((basis_times_y_kernel<1>), grid, 256, 0, st, V, y, M, k, w);
     BFD_LAUNCHED();
+    return BFD_OK;
+}
+
+extern "C" int bfd_basis_times_y(const double *V, const double *y, int64_t M, int k, double *w, void *stream) {
+    if (!V || !y || !w || M < 1 || k < 1 || k > 96) return BFD_EINVAL;
+    cudaStream_t st = (cudaStream_t)stream;
+    static const char *variant = getenv("BFD_VY_VARIANT");                  // tuning: "rows" = 8-byte loads per row
+    const long long nquads = (variant && variant[0] == 'r') || ((uintptr_t)V & 15) ? 0 : M / 4;
+    if (nquads > 0) {
+        long long blocks = (nquads + kVyWarps - 1) / kVyWarps;
+        if (blocks > 148 * 5) blocks = 148 * 5;             // 89 registers, 36.9 KB of shared memory: 5 CTAs per SM
+        const int grid = (int)BFD_GRID((int)blocks);
+        switch ((2 * k + 31) / 32) {
+        case 1: BFD_LAUNCH((basis_times_y_async_kernel<1>), grid, 32 * kVyWarps, 0, st, V, y, nquads, k, w); break;
+        case 2: BFD_LAUNCH((basis_times_y_async_kernel<2>), grid, 32 * kVyWarps, 0, st, V, y, nquads, k, w); break;
+        case 3: BFD_LAUNCH((basis_times_y_async_kernel<3>), grid, 32 * kVyWarps, 0, st, V, y, nquads, k, w); break;
+        case 4: BFD_LAUNCH((basis_times_y_async_kernel<4>), grid, 32 * kVyWarps, 0, st, V, y, nquads, k, w); break;
+        case 5: BFD_LAUNCH((basis_times_y_async_kernel<5>), grid, 32 * kVyWarps, 0, st, V, y, nquads, k, w); break;
+        default: BFD_LAUNCH((basis_times_y_async_kernel<6>), grid, 32 * kVyWarps, 0, st, V, y, nquads, k, w); break;
+        }
+        BFD_LAUNCHED();
+    }
+    const long long done = nquads * 4;
+    if (done < M) return basis_times_y_rows(V + done * k, y, M - done, k, w + done, st);   // tail rows (or everything)
     return BFD_OK;
 }
