@@ -121,19 +121,20 @@ def run_reference_arm(args, rank, world):
     if rank != 0:
         return
     times = []
+    n = args.grid
     for i in range(args.warmup + args.steps):
-        b = cpu_baseline(sample_steps=1)
+        b = cpu_baseline(sample_steps=1, n=n)
         if i >= args.warmup:
             times.append(b["seconds"])
     total = sum(times)
-    value = GRID_N * GRID_N * len(times) / total
+    value = n * n * len(times) / total
     b["value"] = value
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": f"FOM {GRID_N}x{GRID_N}, dt={DT}: one time step of one mu per bench step "
-                                   "(bounded sample of the 500-step sweep)", "grid": GRID_N,
+            "config": {"workload": f"FOM {n}x{n}, dt={DT}: one time step of one mu per bench step "
+                                   "(bounded sample of the 500-step sweep)", "grid": n,
                        "cpu_count": os.cpu_count()},
             "cpu_baseline": {k: b[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
