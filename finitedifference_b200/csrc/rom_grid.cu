@@ -85,23 +85,54 @@ __global__ void __launch_bounds__(128) rom_jv_grid_kernel(const JvGridArgs a) {
                 Lv[rr][m] = ok ? V[(nP + cell) * k + joff[m]] : 0.0;
             }
         }
-        for (int c = c0; c < c1; ++c) {
-            // A rows r0-1 .. r0+R-1 of the y-difference at this column
+        // One column's operands: A rows r0-1 .. r0+R-1 of the y-difference and (the :167 operator
+        // only) the own rows.  The next column is loaded at the END of a step, right after the stores
+        // (measured: the :167 operator 0.49 -> 0.44 ms against loading at the top of the step; loading
+        // it BEFORE the arithmetic of the current column -- a register prefetch -- was slower: 0.53 ms,
+        // 158-242 registers).
+        struct Col {
             double Au[R + 1][MC], Av[R + 1][MC], wAu[R + 1], wAv[R + 1];
+            double Pu[TRANSPOSED ? R : 1][MC], Pv[TRANSPOSED ? R : 1][MC], wPu[TRANSPOSED ? R : 1], wPv[TRANSPOSED ? R : 1];
+        };
+        auto load_col = [&](int c, Col &d) {
 #pragma unroll
             for (int rr = 0; rr <= R; ++rr) {
                 const int r = r0 - 1 + rr;
                 const bool ok = r >= 0 && r < r_hi;
                 const size_t cell = !ok ? 0 : TRANSPOSED ? (size_t)c * a.a_len + (r - a.a_row0)
                                                          : (size_t)(r - a.p_row0) * nx + c;
-                wAu[rr] = ok ? wA[cell] : 0.0;
-                wAv[rr] = ok ? wA[nA + cell] : 0.0;
+                d.wAu[rr] = ok ? wA[cell] : 0.0;
+                d.wAv[rr] = ok ? wA[nA + cell] : 0.0;
 #pragma unroll
                 for (int m = 0; m < MC; ++m) {
-                    Au[rr][m] = ok ? VA[cell * k + joff[m]] : 0.0;
-                    Av[rr][m] = ok ? VA[(nA + cell) * k + joff[m]] : 0.0;
+                    d.Au[rr][m] = ok ? VA[cell * k + joff[m]] : 0.0;
+                    d.Av[rr][m] = ok ? VA[(nA + cell) * k + joff[m]] : 0.0;
                 }
             }
+            if (TRANSPOSED) {
+#pragma unroll
+                for (int rr = 0; rr < R; ++rr) {
+                    const int r = r0 + rr;
+                    const bool ok = r < r_hi;
+                    const size_t pc = ok ? (size_t)(r - a.p_row0) * nx + c : 0;
+                    d.wPu[rr] = ok ? w[pc] : 0.0;
+                    d.wPv[rr] = ok ? w[nP + pc] : 0.0;
+#pragma unroll
+                    for (int m = 0; m < MC; ++m) {
+                        d.Pu[rr][m] = ok ? V[pc * k + joff[m]] : 0.0;
+                        d.Pv[rr][m] = ok ? V[(nP + pc) * k + joff[m]] : 0.0;
+                    }
+                }
+            }
+        };
+        Col cur;
+        load_col(c0, cur);
+        for (int c = c0; c < c1; ++c) {
+            const bool more = c + 1 < c1;
+            const auto &Au = cur.Au;
+            const auto &Av = cur.Av;
+            const auto &wAu = cur.wAu;
+            const auto &wAv = cur.wAv;
 #pragma unroll
             for (int rr = 0; rr < R; ++rr) {
                 const int r = r0 + rr;
@@ -109,14 +140,10 @@ __global__ void __launch_bounds__(128) rom_jv_grid_kernel(const JvGridArgs a) {
                 const size_t cell = (size_t)(r - a.r_lo) * nx + c;            // output / coefficient index
                 double Pu[MC], Pv[MC], wPu, wPv;
                 if (TRANSPOSED) {
-                    const size_t pc = (size_t)(r - a.p_row0) * nx + c;
-                    wPu = w[pc];
-                    wPv = w[nP + pc];
+                    wPu = cur.wPu[rr];
+                    wPv = cur.wPv[rr];
 #pragma unroll
-                    for (int m = 0; m < MC; ++m) {
-                        Pu[m] = V[pc * k + joff[m]];
-                        Pv[m] = V[(nP + pc) * k + joff[m]];
-                    }
+                    for (int m = 0; m < MC; ++m) { Pu[m] = cur.Pu[rr][m]; Pv[m] = cur.Pv[rr][m]; }
                 } else {
                     wPu = wAu[rr + 1];
                     wPv = wAv[rr + 1];
@@ -147,6 +174,7 @@ __global__ void __launch_bounds__(128) rom_jv_grid_kernel(const JvGridArgs a) {
                 wLu[rr] = wPu;
                 wLv[rr] = wPv;
             }
+            if (more) load_col(c + 1, cur);
         }
         if (CBLOCK) {
             __syncwarp();
@@ -211,7 +239,7 @@ static int jv_grid_launch(const bfd_rom_mesh *m, int nx, int ny, int transposed,
     if (!m->cx || !m->cxl || !m->cy || !m->cyd || !w || !V || !JV || k < 1) return BFD_EINVAL;
     if (m->weight) return BFD_EINVAL;                       // weighted rows belong to the sampled mesh
     if (transposed && nx != ny) return BFD_EINVAL;          // :167 permutes a square grid
-    const int R = rows_per_warp == 4 ? 4 : rows_per_warp == 2 ? 2 : rows_per_warp == 1 ? 1 : (transposed ? 2 : 1);   // measured at 750^2, k = 95: 2 rows beat 4 (registers -> occupancy)
+    const int R = rows_per_warp == 4 ? 4 : rows_per_warp == 2 ? 2 : 1;   // measured at 750^2, k = 95: 1 row per warp is fastest for both operators (0.34 / 0.44 ms), 4 rows slowest (registers)
     int mc = k > 64 ? 3 : k > 32 ? 2 : 1;
     if (const char *e = getenv("BFD_JV_MC")) { const int v = atoi(e); if (v >= 1 && v < mc) mc = v; }   // tuning
     JvGridArgs a{};
