@@ -1,0 +1,105 @@
+"""Non-negative least squares for the ECSW weights where the training matrix already is: in HBM
+(SURVEY.md 8f item 2).
+
+The reference trains the ECSW weights with ``scipy.optimize.nnls(c, c.sum(axis=1))`` on 20 column
+blocks of the training matrix ``C`` (run_HPROM_ecsw_joshua.py:83-86, joblib workers on the host;
+``C`` is 4 750 x 562 500 doubles = 21 GB on the fine grid).  This module restates the published
+algorithm -- Lawson & Hanson, *Solving Least Squares Problems* (1974), ch. 23, the active-set method
+behind both SciPy's ``nnls`` and MATLAB's ``lsqnonneg`` -- on torch tensors, so that the large
+products (``A^T A`` once per block, ``A^T (b - A x)`` per iteration) are library GEMM / GEMV calls on
+the device; nothing here is a hand-written kernel.  The passive-set least-squares problems are solved
+through the Gram matrix ``(A^T A)[P, P]`` (Cholesky; ``lstsq`` on ``A[:, P]`` when it is not positive
+definite).  SciPy is not pinned by the reference (no requirements file); the tests compare with the
+SciPy installed in this image (1.18) on problems with a unique solution, and check the KKT conditions
+where the solution is not unique (more columns than rows, the reference's case: the active set is
+then rounding-sensitive).
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from .fom import _require_cuda
+
+
+def nnls_tensor(A: torch.Tensor, b: torch.Tensor, maxiter: int | None = None):
+    """``argmin ||A x - b||_2, x >= 0`` on A's device; returns ``(x, rnorm, iterations)``."""
+    if A.ndim != 2 or b.ndim != 1 or A.shape[0] != b.shape[0]:
+        raise ValueError(f"incompatible shapes {tuple(A.shape)} and {tuple(b.shape)}")
+    A, b = A.to(torch.float64), b.to(torch.float64)
+    m, n = A.shape
+    dev = A.device
+    x = torch.zeros(n, dtype=torch.float64, device=dev)
+    if n == 0:
+        return x, float(torch.linalg.norm(b)), 0
+    maxiter = 3 * n if not maxiter else int(maxiter)
+    AtA, Atb = A.T @ A, A.T @ b
+    tol = 10.0 * np.finfo(np.float64).eps * float(A.abs().sum(dim=0).max()) * max(m, n)     # lsqnonneg's tolerance
+    passive = torch.zeros(n, dtype=torch.bool, device=dev)
+    w = Atb.clone()                                      # A^T (b - A x) at x = 0
+    its = 0
+
+    def solve_passive():
+        idx = torch.nonzero(passive)[:, 0]
+        G = AtA[idx][:, idx]
+        L, info = torch.linalg.cholesky_ex(G)
+        if int(info) == 0:
+            z = torch.cholesky_solve(Atb[idx][:, None], L)[:, 0]
+        else:                                            # dependent columns: minimum-norm least squares
+            z = torch.linalg.lstsq(A[:, idx], b[:, None]).solution[:, 0]
+        s = torch.zeros_like(x)
+        s[idx] = z
+        return s
+
+    while True:
+        cand = torch.where(passive, torch.full_like(w, -np.inf), w)
+        j = int(torch.argmax(cand))
+        if bool(passive.all()) or float(cand[j]) <= tol:
+            break
+        if its >= maxiter:
+            raise RuntimeError("Maximum number of iterations reached.")
+        its += 1
+        passive[j] = True
+        s = solve_passive()
+        while bool((s[passive] <= 0).any()):            # step back to the boundary of the feasible set
+            bad = torch.nonzero(passive & (s <= 0))[:, 0]
+            ratios = x[bad] / (x[bad] - s[bad])
+            kmin = int(torch.argmin(ratios))
+            x = torch.clamp(x + float(ratios[kmin]) * (s - x), min=0.0)
+            x[bad[kmin]] = 0.0                          # the variable that hit its bound leaves the passive set
+            passive &= x > 0
+            x = torch.where(passive, x, torch.zeros_like(x))
+            if not bool(passive.any()):
+                s = torch.zeros_like(x)
+                break
+            s = solve_passive()
+        x = s
+        w = Atb - AtA @ x
+    return x, float(torch.linalg.norm(A @ x - b)), its
+
+
+def nnls(A, b, *, maxiter=None, device=None):
+    """``scipy.optimize.nnls`` signature: returns ``(x, rnorm)`` as NumPy / float; runs on the GPU."""
+    dev = _require_cuda(device if device is not None else (A.device if isinstance(A, torch.Tensor) and A.is_cuda else None))
+    At = A if isinstance(A, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(A, dtype=np.float64))
+    bt = b if isinstance(b, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(b, dtype=np.float64).ravel())
+    with torch.cuda.device(dev):
+        x, rnorm, _ = nnls_tensor(At.to(dev), bt.to(dev), maxiter)
+    return x.cpu().numpy(), rnorm
+
+
+def ecsw_weights(C, blocks=20, *, maxiter=None, device=None):
+    """The reference's block-wise training (run_HPROM_ecsw_joshua.py:83-86): ``np.array_split(C, blocks,
+    axis=1)``, ``nnls(c, c.sum(axis=1))`` per block, weights concatenated.  ``C``: NumPy array or CUDA
+    tensor ``(k*n_snaps, n_cells)``; returns the NumPy weight vector ``(n_cells,)``."""
+    dev = _require_cuda(device if device is not None else (C.device if isinstance(C, torch.Tensor) and C.is_cuda else None))
+    n = C.shape[1]
+    bounds = np.cumsum([0] + [len(p) for p in np.array_split(np.arange(n), blocks)])
+    out = []
+    with torch.cuda.device(dev):
+        for lo, hi in zip(bounds[:-1], bounds[1:]):
+            c = C[:, lo:hi]
+            c = (c if isinstance(c, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(c, dtype=np.float64))).to(dev)
+            x, _, _ = nnls_tensor(c, c.sum(dim=1), maxiter)
+            out.append(x.cpu().numpy())
+    return np.hstack(out)
