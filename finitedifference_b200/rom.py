@@ -29,7 +29,7 @@ from .fom import _require_cuda
 
 GRAM_KERNEL_MIN_ROWS = 65536
 SPD_SOLVE_KERNEL = True      # False: cuSOLVER potrf + potrs through torch (comparison)
-JV_ROWS_PER_WARP = 0     # grid rows a warp of bfd_rom_jv_grid owns: 0 = library default, 2 or 4 (tuning)
+JV_ROWS_PER_WARP = 0     # grid rows a warp of bfd_rom_jv_grid owns: 0 = library default, 1, 2 or 4 (tuning); 9 = cp.async ring variant
 
 
 def generate_augmented_mesh(grid_x, grid_y, sample_inds):
