@@ -14,7 +14,7 @@ LIB_PATH = os.environ.get("BFD_LIB") or os.path.join(HERE, "_burgers_b200.so")  
 
 BFD_OK = 0
 ERRORS = {-1: "BFD_EINVAL", -2: "BFD_ECUDA", -3: "BFD_EWORKSPACE", -4: "BFD_ETIMEOUT",
-          -5: "BFD_ENOTCONVERGED"}
+          -5: "BFD_ENOTCONVERGED", -6: "BFD_ETOOBIG"}
 
 
 class FomDesc(C.Structure):
@@ -92,6 +92,7 @@ SIGNATURES = {
     "bfd_ecsw_c_grid": (C.c_int, [C.POINTER(RomMesh), C.c_int, C.c_int, _P, _P, _P, C.c_int, _P, C.c_size_t, _P]),
     "bfd_gram_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int]),
     "bfd_gram": (C.c_int, [_P, _P, C.c_int64, C.c_int, _P, _P, _P, C.c_size_t, _P]),
+    "bfd_gram_static": (C.c_int, [_P, _P, C.c_int64, C.c_int, _P, _P, _P]),
     "bfd_spd_solve": (C.c_int, [_P, _P, C.c_int, C.c_double, _P, _P]),
     "bfd_basis_times_y": (C.c_int, [_P, _P, C.c_int64, C.c_int, _P, _P]),
     "bfd_ecsw_c_block": (C.c_int, [C.c_int64, C.c_int, _P, _P, _P, C.c_size_t, _P]),
@@ -128,5 +129,5 @@ def get_lib() -> C.CDLL:
 
 def check(rc: int, lib: C.CDLL, what: str) -> None:
     if rc != BFD_OK:
-        detail = lib.bfd_last_cuda_error().decode() if rc == -2 else ""
+        detail = lib.bfd_last_cuda_error().decode() if rc in (-2, -6) else ""
         raise BurgersError(f"{what} failed: {ERRORS.get(rc, rc)} {detail}")

@@ -202,6 +202,66 @@ extern "C" int bfd_gram(const double *X, const double *f, int64_t M, int k, doub
 }
 
 // ------------------------------------------------------------------------------------------
+// bfd_gram_static: the same normal equations for callers that cannot allocate (CUDA graph capture,
+// tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The partial sums live in a file-scope device array of
+// fixed size instead of a caller-sized workspace: BFD_GRAM_STATIC_PARTS partials (one CTA per SM)
+// of 96 x 104 doubles = 11.3 MiB, held by every GPU that loads the library until the process
+// exits.  In HOST code the array's name is only a stand-in for the symbol, not a device address:
+// the address is looked up once per device with cudaGetSymbolAddress (that device current) and
+// passed to the kernels like any other pointer.  Nothing has to start at zero: every CTA
+// overwrites each entry of its partial that gram_reduce_kernel reads.  All calls share the one
+// array, so calls that overlap on the GPU (different streams, no ordering between them) race.
+// ------------------------------------------------------------------------------------------
+namespace bfd {
+static __device__ __align__(256) double g_gram_static_scratch[(size_t)BFD_GRAM_STATIC_PARTS * 96 * kGramLd];
+constexpr int kMaxDevices = 64;
+static double *g_gram_static_ptr[kMaxDevices];       // device address of the array on each device, 0 = not looked up yet
+
+static int gram_static_scratch(double **out) {
+    int dev = 0;
+    BFD_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) {
+        snprintf(g_cuda_error, sizeof(g_cuda_error), "bfd_gram_static: device ordinal %d not in [0, %d)", dev, kMaxDevices);
+        return BFD_ETOOBIG;
+    }
+    double *p = __atomic_load_n(&g_gram_static_ptr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {                                        // threads that race here look up the same address
+        BFD_CUDA(cudaGetSymbolAddress((void **)&p, g_gram_static_scratch));
+        if (!p) return BFD_ECUDA;
+        __atomic_store_n(&g_gram_static_ptr[dev], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return BFD_OK;
+}
+}  // namespace bfd
+
+extern "C" int bfd_gram_static(const double *X, const double *f, int64_t M, int k, double *G, double *b, void *stream) {
+    if (!X || !f || !G || !b || M < 1 || k < 1) return BFD_EINVAL;
+    if (M > (int64_t)BFD_GRAM_STATIC_MAX_ROWS || k > 96) {
+        snprintf(g_cuda_error, sizeof(g_cuda_error),
+                 "bfd_gram_static: M = %lld, k = %d beyond the fixed scratch's maximum (M <= %lld, k <= 96); "
+                 "use bfd_gram with a caller-sized workspace", (long long)M, k, (long long)BFD_GRAM_STATIC_MAX_ROWS);
+        return BFD_ETOOBIG;
+    }
+    double *scratch = nullptr;
+    const int rc = gram_static_scratch(&scratch);
+    if (rc != BFD_OK) return rc;
+    GramArgs a{};
+    a.X = X; a.f = f; a.M = M; a.k = k;
+    a.ntiles = (int)((M + kGramRows - 1) / kGramRows);
+    a.partial = scratch;
+    int grid = a.ntiles < BFD_GRAM_STATIC_PARTS ? a.ntiles : BFD_GRAM_STATIC_PARTS;
+    grid = (int)BFD_GRID(grid);
+    cudaStream_t st = (cudaStream_t)stream;
+    BFD_LAUNCH(gram_partial_kernel, grid, 32 * kGramWarps, 0, st, a);
+    BFD_LAUNCHED();
+    BFD_LAUNCH(gram_reduce_kernel, (k * (k + 1) + 31) / 32, dim3(32, 8), 0, st, (const double *)scratch, grid, k, G, b);
+    BFD_LAUNCHED();
+    return BFD_OK;
+}
+
+// ------------------------------------------------------------------------------------------
 // G dy = b for the k x k normal equations (k <= 96): Cholesky factorisation and the triangular
 // solves by ONE CTA, thread i owning row i of the packed factor in shared memory.  Replaces the
 // LAPACK solve inside numpy.linalg.lstsq (:1994, :2038).  A library potrf + potrs on a 95 x 95

@@ -13,7 +13,7 @@ int record_cuda_error(cudaError_t e, const char *where) {
 }
 }  // namespace bfd
 
-extern "C" int bfd_abi_version(void) { return 4; }
+extern "C" int bfd_abi_version(void) { return 5; }
 extern "C" const char *bfd_last_cuda_error(void) { return bfd::g_cuda_error; }
 extern "C" uint64_t bfd_launch_count(void) { return bfd::g_launches; }
 

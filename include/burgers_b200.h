@@ -31,6 +31,7 @@ extern "C" {
 #define BFD_EWORKSPACE (-3)   /* workspace too small */
 #define BFD_ETIMEOUT (-4)     /* a wavefront hand-off timed out on the device */
 #define BFD_ENOTCONVERGED (-5)
+#define BFD_ETOOBIG (-6)      /* size beyond a fixed-capacity entry point's stated maximum, see bfd_last_cuda_error() */
 
 /* Library / device identification. */
 int bfd_abi_version(void);
@@ -266,6 +267,21 @@ int bfd_ecsw_c_grid(const bfd_rom_mesh *mesh, int nx, int ny, const double *w, c
 size_t bfd_gram_workspace_bytes(int64_t M, int k);
 int bfd_gram(const double *X, const double *f, int64_t M, int k, double *G, double *b, void *workspace,
              size_t workspace_bytes, void *stream);
+
+/* bfd_gram without a workspace argument and without any allocation, for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * This entry point has NO counterpart in the reference.
+ * The partial sums go to a fixed device array inside the library
+ * (BFD_GRAM_STATIC_PARTS x 96 x 104 doubles = 11.3 MiB per GPU that loads the library, held until
+ * the process exits), one CTA per SM.  Limits: M <= BFD_GRAM_STATIC_MAX_ROWS, k <= 96; anything
+ * larger returns BFD_ETOOBIG with the reason in bfd_last_cuda_error().  Calls no cudaMalloc /
+ * cudaFree / allocating library routine.  All calls share the one array: calls that overlap on
+ * the GPU (two streams without an ordering between them) race -- serialise them.  Nothing needs
+ * clearing between calls (every entry read is overwritten first).  Same G and b as bfd_gram up to
+ * the summation order of the partials (fewer, longer partials: agreement ~1e-15 relative). */
+#define BFD_GRAM_STATIC_PARTS 148
+#define BFD_GRAM_STATIC_MAX_ROWS (1 << 21)
+int bfd_gram_static(const double *X, const double *f, int64_t M, int k, double *G, double *b, void *stream);
 
 /* x = scale * G^-1 b for a symmetric positive definite k x k matrix (row-major, lower triangle
  * read), k <= 96: Cholesky + two triangular solves in one single-CTA launch (a matrix that is not

@@ -25,6 +25,9 @@
 #define __noinline__
 #define __launch_bounds__(...)
 #define __restrict__
+#ifndef __align__
+#define __align__(n) __attribute__((aligned(n)))
+#endif
 
 struct dim3 {
     unsigned x, y, z;
@@ -50,6 +53,9 @@ static inline cudaError_t cudaEventRecord(cudaEvent_t, cudaStream_t) { return cu
 static inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return cudaSuccess; }
 static inline cudaError_t cudaEventDestroy(cudaEvent_t) { return cudaSuccess; }
 static inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }
+static inline cudaError_t cudaGetDevice(int *d) { *d = 0; return cudaSuccess; }
+// a "device" array is a host array here, so its address is the symbol's own
+template <class T> static inline cudaError_t cudaGetSymbolAddress(void **p, T &sym) { *p = (void *)&sym; return cudaSuccess; }
 
 namespace emu {
 

@@ -23,7 +23,7 @@ def test_build_and_symbols():
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in include/burgers_b200.h but not exported"
     assert sorted(_lib.SIGNATURES) == declared, "ctypes signatures out of sync with the header"
-    assert lib.bfd_abi_version() == 4
+    assert lib.bfd_abi_version() == 5
 
 
 def test_bad_arguments_are_reported_not_thrown():
