@@ -158,6 +158,8 @@ def main():
     ap.add_argument("--e2e-group", type=int, default=2, help="samples a sweep worker advances together")
     ap.add_argument("--e2e-workers", type=int, default=3, help="sweep worker threads / streams")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--kernel", default="tile", choices=["tile", "legacy"],
+                    help="FOM sweep kernel: fom_tile_kernel (default) or the round-1 fom_chunk_kernel")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -189,7 +191,7 @@ def main():
     gx, gy = make_2D_grid(0, 100, 0, 100, n, n)
 
     # size the batch to the HBM actually free
-    skw = dict(chunk_steps=args.chunk_steps, strict=not args.non_strict)
+    skw = dict(chunk_steps=args.chunk_steps, strict=not args.non_strict, kernel=args.kernel)
     one = _lib.fom_desc(n, n, 1, T, chunk_steps=args.chunk_steps)
     per_mu = lib.bfd_fom_workspace_bytes(C.byref(one))
     free, _total = torch.cuda.mem_get_info(dev)

@@ -22,13 +22,13 @@ class FomDesc(C.Structure):
     _fields_ = [("nx", C.c_int32), ("ny", C.c_int32), ("batch", C.c_int32),
                 ("num_steps", C.c_int32), ("max_its", C.c_int32), ("chunk_steps", C.c_int32),
                 ("newton_hint", C.c_int32), ("strict", C.c_int32), ("uniform_y", C.c_int32),
-                ("reserved", C.c_int32), ("rel_tol", C.c_double)]
+                ("kernel", C.c_int32), ("rel_tol", C.c_double)]
 
 
 def fom_desc(nx, ny, batch, num_steps, max_its=100, rel_tol=1e-12, chunk_steps=0, newton_hint=0,
-             strict=True, uniform_y=False):
+             strict=True, uniform_y=False, kernel=0):
     return FomDesc(int(nx), int(ny), int(batch), int(num_steps), int(max_its), int(chunk_steps),
-                   int(newton_hint), int(bool(strict)), int(bool(uniform_y)), 0, float(rel_tol))
+                   int(newton_hint), int(bool(strict)), int(bool(uniform_y)), int(kernel), float(rel_tol))
 
 
 FOM_KMAX = 6

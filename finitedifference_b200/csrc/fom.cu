@@ -33,6 +33,7 @@
 // step is one contiguous line of HBM.  Strips are chained left to right through
 // self-validating records in global memory (wavefront.cuh).
 #include "wavefront.cuh"
+#include <stdlib.h>
 
 namespace bfd {
 
@@ -107,6 +108,7 @@ static int check_desc(const bfd_fom_desc *d) {
     if (d->chunk_steps < 0 || d->chunk_steps > BFD_FOM_MAX_CHUNK) return BFD_EINVAL;
     if (d->newton_hint < 0 || d->newton_hint > kKMax) return BFD_EINVAL;
     if (!(d->rel_tol < 1.0)) return BFD_EINVAL;
+    if (d->kernel != 0 && d->kernel != 1) return BFD_EINVAL;
     return BFD_OK;
 }
 
@@ -178,6 +180,8 @@ struct FomArgs {
     size_t edge_stride_strip, edge_stride_mu, pool_stride_mu;
     // slab runs (whole grid: strip0 = 0, ns_global = ssl.nstrips, the rest unused)
     int strip0, ns_global, launch_index, slab;
+    int variant;        // 0: fom_tile_kernel (warp per strip and time step), 1: fom_chunk_kernel (levels split over warps)
+    int kcap;           // Newton solves the variant fuses into one pass at most
     unsigned *ticket;   // virtual block id dispenser of THIS rank (glob may be rank 0's)
     double *halo;       // [batch][chunk][ny][kRecDoubles] records consumed by this rank's first strip
     double *next_halo;  // the same buffer of the rank on the right (peer-mapped), or null
@@ -201,6 +205,7 @@ static FomArgs fom_args(const bfd_fom_desc *d, const FomLayout &L, void *ws, con
     a.partial = (double *)(h + L.off_partial);
     a.ticket = &((FomGlobal *)(b + L.off_global))->ticket;
     a.strip0 = v.strip0; a.ns_global = v.ns_global; a.launch_index = 0; a.slab = v.slab ? 1 : 0;
+    a.variant = d->kernel; a.kcap = d->kernel == 0 ? 4 : kKMax;     // kTileKMax (fom_tile.cuh)
     a.halo = v.strip0 > 0 ? (double *)(b + L.off_halo) : nullptr;
     a.next_halo = v.next_halo;
     a.trace = (unsigned long long *)(b + L.off_trace);
@@ -699,7 +704,7 @@ __device__ bool validate_step(const FomArgs &a, int m, int i, int kb, int K, dou
     return rec.status == kStepNotConverged || (rec.status == kStepEarly && a.strict && rec.kconv > 0);
 }
 
-__device__ __forceinline__ int clampk(int k) { return k < 1 ? 1 : (k > kKMax ? kKMax : k); }
+__device__ __forceinline__ int clampk(int k, int cap) { return k < 1 ? 1 : (k > cap ? cap : k); }
 
 // Turn the verdicts of a segment (attempts i0 .. i0+n-1 of this launch, time steps t0 ..) into
 // the sample's next state.  Run by the last strip of the sample to finish the segment.
@@ -726,6 +731,7 @@ __device__ void commit_segment(const FomArgs &a, int m, int t0, int i0, int n, i
         const int kb = ii ? 0 : kbase;
         int K = ii ? k_spec : k_first;
         if (K > a.max_its - kb) K = a.max_its - kb;
+        if (K > a.kcap) K = a.kcap;
         int *its = a.its + (size_t)m * a.num_steps + t;
         double *rel = a.relnorm + (size_t)m * a.num_steps + t;
         switch (rec.status) {
@@ -736,6 +742,7 @@ __device__ void commit_segment(const FomArgs &a, int m, int t0, int i0, int n, i
                 *its = kb + K + 1; *rel = rec.rel; knext = kb + rec.kconv; ++t;
             } else {                              // the reference returns x_kconv: redo with that count
                 new_kbase = 0; new_kfirst = rec.kconv; stop = true; ++redo;
+                knext = rec.kconv;                // ... and expect it of the steps that follow
             }
             break;
         default:                                  // not converged: further sweeps in place
@@ -743,8 +750,8 @@ __device__ void commit_segment(const FomArgs &a, int m, int t0, int i0, int n, i
             break;
         }
     }
-    if (!stop) { ctl->kbase = 0; ctl->k_first = clampk(knext); ctl->k_spec = clampk(knext); }
-    else { ctl->kbase = new_kbase; ctl->k_first = new_kfirst; }
+    if (!stop) { ctl->kbase = 0; ctl->k_first = clampk(knext, a.kcap); ctl->k_spec = clampk(knext, a.kcap); }
+    else { ctl->kbase = new_kbase; ctl->k_first = new_kfirst; if (new_kbase == 0) ctl->k_spec = clampk(knext, a.kcap); }
     ctl->t = t;
     ctl->under = under;
     if (redo) { ctl->redone += redo; atomicAdd(&a.glob->redone, redo); }
@@ -955,6 +962,8 @@ __global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk
 
 }  // namespace bfd
 
+#include "fom_tile.cuh"
+
 namespace bfd {
 
 // natural (u|v, row-major) -> skewed strip layout, into every sample's slot 0
@@ -1005,7 +1014,7 @@ __global__ void fom_reset_kernel(const FomArgs a, int control) {
     }
     if (g < a.batch) {
         FomCtl c;
-        c.t = 0; c.kbase = 0; c.k_first = a.hint; c.k_spec = a.hint;
+        c.t = 0; c.kbase = 0; c.k_first = a.hint < a.kcap ? a.hint : a.kcap; c.k_spec = c.k_first;
         c.gate = 0; c.arrive = 0; c.redone = 0; c.epoch = 0; c.init_norm = 0.0;
         c.exits = 0; c.under = 0; c.pad1[0] = c.pad1[1] = 0.0;
         a.ctl[g] = c;
@@ -1086,6 +1095,14 @@ static int fom_set_initial_impl(const bfd_fom_desc *d, const SlabView &v, void *
 
 static int launch_chunk(const FomArgs &a, cudaStream_t st) {
     const int grid = a.batch * a.ssl.nstrips;
+    if (a.variant == 0) {
+        void (*kernel)(const FomArgs) =
+            a.slab ? (a.uniform_y ? fom_tile_kernel<true, true> : fom_tile_kernel<false, true>)
+                   : (a.uniform_y ? fom_tile_kernel<true, false> : fom_tile_kernel<false, false>);
+        BFD_LAUNCH_CORESIDENT(kernel, grid, 32 * kTileDepth, 0, st, a);
+        BFD_LAUNCHED();
+        return BFD_OK;
+    }
     const int block = 32 * (kWarpsPerStrip + 1);
     void (*kernel)(const FomArgs) =
         a.slab ? (a.uniform_y ? fom_chunk_kernel<true, true> : fom_chunk_kernel<false, true>)
@@ -1122,6 +1139,9 @@ static int fom_run_impl(const bfd_fom_desc *d, const SlabView &v, void *ws, cons
     bool finished = false;
     while (!finished && rc == BFD_OK) {
         a.launch_index = (int)launched;
+#ifdef BFD_EMULATE
+        if (getenv("BFD_EMU_DEBUG")) fprintf(stderr, "launch %lld: t %d kbase %d k_first %d k_spec %d gate %x\n", launched, a.ctl[0].t, a.ctl[0].kbase, a.ctl[0].k_first, a.ctl[0].k_spec, a.ctl[0].gate);
+#endif
         rc = launch_chunk(a, st);
         ++launched;
         if (rc != BFD_OK) break;

@@ -41,9 +41,10 @@ def hat_basis(n, k=95, nodes=24, length=100.0):
             for i in range(nodes):
                 B[comp * N:(comp + 1) * N, j] = np.outer(ylv[lv], hats[i]).ravel()
                 j += 1
-    Q, _ = np.linalg.qr(B[:, :k])
-    # fix the signs so the basis does not depend on LAPACK's Householder conventions
-    Q *= np.sign(Q[np.abs(Q).argmax(axis=0), np.arange(Q.shape[1])])[None, :]
+    Q, R = np.linalg.qr(B[:, :k])
+    # the QR factorisation with a positive diagonal of R is unique: no dependence on LAPACK's
+    # Householder sign conventions or on the number of threads
+    Q *= np.sign(np.diag(R))[None, :]
     return np.ascontiguousarray(Q)
 
 

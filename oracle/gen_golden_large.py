@@ -167,9 +167,9 @@ def main():
         np.savez_compressed(os.path.join(OUT, "fom_n250_T500_train.npz"), n=250, mu=MU_B, dt=DT, steps=500,
                             norms=np.linalg.norm(S, axis=0), newton_its=c)
     elif args.stage == "hat250":
-        lspg_hat(ref, 250, 3, "lspg_hat_n250.npz")
+        lspg_hat(ref, 250, 6, "lspg_hat_n250.npz")
     elif args.stage == "hat750":
-        lspg_hat(ref, 750, 2, "lspg_hat_n750.npz")
+        lspg_hat(ref, 750, 4, "lspg_hat_n750.npz")
     elif args.stage == "rom250":
         rom250(ref, args.scratch)
     else:

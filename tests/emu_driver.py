@@ -17,14 +17,14 @@ def ptr(a):
 
 
 def fom_run(lib, grid_x, grid_y, w0, dt, num_steps, mus, max_its=100, rel_tol=1e-12, chunk_steps=0,
-            newton_hint=0, strict=True, uniform_y=None, stats=None):
+            newton_hint=0, strict=True, uniform_y=None, stats=None, kernel=0):
     """Returns (snaps[batch, 2N, T+1], its[batch, T], relnorm[batch, T])."""
     mus = np.atleast_2d(np.asarray(mus, dtype=np.float64))
     nx, ny, B = grid_x.size - 1, grid_y.size - 1, mus.shape[0]
     coefs = [np.ascontiguousarray(a) for a in stencil_coefficients(grid_x, grid_y, dt)]
     if uniform_y is None:
         uniform_y = is_uniform(coefs[2], coefs[3])
-    d = _lib.fom_desc(nx, ny, B, num_steps, max_its, rel_tol, chunk_steps, newton_hint, strict, uniform_y)
+    d = _lib.fom_desc(nx, ny, B, num_steps, max_its, rel_tol, chunk_steps, newton_hint, strict, uniform_y, kernel)
     nbytes = lib.bfd_fom_workspace_bytes(C.byref(d))
     assert nbytes > 0
     ws = np.zeros(nbytes // 8 + 1, dtype=np.float64)

@@ -48,3 +48,13 @@ def test_no_cpu_fallback_without_gpu():
     gx, gy = h.make_2D_grid(0, 100, 0, 100, 8, 8)
     with pytest.raises(_lib.BurgersError):
         h.inviscid_burgers_implicit2D(gx, gy, np.ones(128), 0.05, 1, [4.75, 0.02])
+
+
+def test_training_matrix_rejects_foreign_callables():
+    """res / jac other than the functions the device path evaluates raise instead of being ignored."""
+    import pytest
+    from finitedifference_b200 import hypernet2D as h
+    with pytest.raises(ValueError, match="res="):
+        h.compute_ECSW_training_matrix_2D(None, None, None, lambda *a: 0, None)
+    with pytest.raises(ValueError, match="jac="):
+        h.compute_ECSW_training_matrix_2D(None, None, None, h.inviscid_burgers_res2D, h.inviscid_burgers_res2D)

@@ -125,3 +125,31 @@ def test_jacobian_is_derivative_of_residual():
 
 def test_snapshot_file_name():
     assert orc.param_to_snap_fn([4.25, 0.015]) == "param_snaps/mu1_4.25+mu2_0.015.npy"
+
+
+def test_fom_long_trajectory_first_steps(golden):
+    """The 500-step fixture of the coarse config's parameters at 64^2: the oracle over its first 60 steps."""
+    g = golden("fom_n64_T500.npz")
+    n, T = int(g["n"]), 60
+    gx, gy = grid(n)
+    snaps, hist = orc.fom_trajectory(gx, gy, np.ones(2 * n * n), float(g["dt"]), T, list(g["mu"]), return_info=True)
+    assert [len(h) for h in hist] == list(g["newton_its"][:T])
+    assert np.max(np.abs(np.linalg.norm(snaps, axis=0) / g["norms"][:T + 1] - 1)) < 1e-13
+    assert rel_l2_cols(snaps[::int(g["dof_stride"])], g["dof_sample"][:, :T + 1]).max() < 1e-12
+    ts = int(g["t_stride"])
+    assert rel_l2_cols(snaps[:, ::ts], g["t_sample"][:, :T // ts + 1]).max() < 1e-12
+
+
+def test_lspg_k95_at_the_coarse_grid(golden):
+    """LSPG with k = 95 at 250^2 (analytic hat basis, oracle/fixtures.py) against the reference."""
+    from oracle import fixtures as fx
+    g = golden("lspg_hat_n250.npz")
+    n, steps = int(g["n"]), 2
+    gx, gy = grid(n)
+    V = fx.hat_basis(n, int(g["k"]))
+    assert np.max(np.abs(V[::int(g["stride"])] - g["basis_sample"])) < 1e-13
+    snaps, times, red, hist = orc.lspg_trajectory(gx, gy, np.ones(2 * n * n), float(g["dt"]), steps, list(g["mu"]), V,
+                                                  return_info=True)
+    assert [len(h) for h in hist] == list(g["gn_its"][:steps])
+    assert rel_l2_cols(red, g["red_coords"][:, :steps + 1]).max() < 1e-10
+    assert rel_l2_cols(snaps[::int(g["stride"])], g["sample"][:, :steps + 1]).max() < 1e-10
