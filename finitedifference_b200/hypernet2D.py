@@ -25,11 +25,13 @@ from .operators import (get_ops, inviscid_burgers_exact_jac2D, inviscid_burgers_
                         inviscid_burgers_res2D, inviscid_burgers_res2D_alt, inviscid_burgers_res2D_ecsw, make_ddx)
 from .nnls import ecsw_weights, nnls  # noqa: F401  (scipy.optimize.nnls at run_HPROM_ecsw_joshua.py:83)
 from .pod import POD  # noqa: F401  (hypernet2D.py:2746)
-from .rom import EcswSolver, LspgSolver, ecsw_batch, ecsw_training_matrix, generate_augmented_mesh  # noqa: F401
+from .rom import (EcswSolver, LspgSolver, ManifoldEcswSolver, ecsw_batch, ecsw_training_matrix,  # noqa: F401
+                  generate_augmented_mesh)
 
 __all__ = [
     "make_2D_grid", "inviscid_burgers_implicit2D", "inviscid_burgers_implicit2D_batch",
     "inviscid_burgers_implicit2D_LSPG", "inviscid_burgers_ecsw_fixed", "inviscid_burgers_ecsw_fixed_batch", "generate_augmented_mesh",
+    "inviscid_burgers_rnm2D_ecsw", "inviscid_burgers_manifold_ecsw", "ManifoldEcswSolver",
     "compute_ECSW_training_matrix_2D",
     "make_ddx", "get_ops", "inviscid_burgers_res2D", "inviscid_burgers_res2D_alt", "inviscid_burgers_res2D_ecsw",
     "inviscid_burgers_exact_jac2D", "inviscid_burgers_exact_jac2D_ecsw",
@@ -113,6 +115,71 @@ def inviscid_burgers_ecsw_fixed_batch(grid_x, grid_y, weights, w0, dt, num_steps
     run_tests.py:9-10 / run_HPROM_ecsw_joshua.py): the HPROMs run concurrently on one GPU.
     Returns a list of ``red_coords (k, T+1)`` arrays in the order of ``mus``."""
     return [red for red, _ in ecsw_batch(grid_x, grid_y, weights, w0, dt, num_steps, mus, basis, device=device)]
+
+
+def inviscid_burgers_manifold_ecsw(grid_x, grid_y, weights, y0, dt, num_steps, mu, decode, decode_jac, *, device=None,
+                                   max_its=20, relnorm_cutoff=1e-5, min_delta=0.1, return_info=False):
+    """Sampled-mesh HPROM with a caller-supplied decoder: the common core of the reference's manifold
+    ROMs (``inviscid_burgers_rnm2D_ecsw`` :556-674, ``_pod_rbf_2D_global_ecsw`` :973-1111,
+    ``_pod_gp_2D_ecsw`` :1113-1275).  ``decode(y) -> (2 n_aug,)`` and ``decode_jac(y) -> (2 n_aug, q)`` are
+    callables on CUDA tensors (entries ``ManifoldEcswSolver.idx`` of the full state); ``max_its=10``
+    reproduces ``gauss_newton_pod_rbf_ecsw`` (:2293).  Returns ``(red_coords (q, T+1), (num_its, jac_time,
+    res_time, ls_time))``."""
+    import torch
+    solver = ManifoldEcswSolver(grid_x, grid_y, weights, dt, mu, device=device)
+    y0 = y0 if isinstance(y0, torch.Tensor) else torch.from_numpy(np.asarray(y0, dtype=np.float64))
+    red, hist = solver.run(y0.to(solver.device), int(num_steps), decode, decode_jac, max_its=max_its,
+                           relnorm_cutoff=relnorm_cutoff, min_delta=min_delta)
+    out = (np.ascontiguousarray(red.T.double().cpu().numpy()),
+           (sum(len(h) for h in hist), solver.jac_time, solver.res_time, solver.ls_time))
+    if return_info:
+        out += ({"gn_its": np.array([len(h) for h in hist]), "resnorms": hist, "idx": solver.idx,
+                 "sample_inds": solver.sample_inds, "augmented_sample": solver.augmented_sample},)
+    return out
+
+
+def inviscid_burgers_rnm2D_ecsw(grid_x, grid_y, w0, dt, num_steps, mu, rnm, ref, basis, basis2, weights, *,
+                                device=None, return_info=False):
+    """Neural-manifold HPROM, reference hypernet2D.py:556-674, same positional signature: the state is
+    ``basis @ y + basis2 @ rnm(cat(y, mu))``.  As in the reference the decoder and ``y`` are float32
+    (``dtype=torch.float``, :592-596, :2214) and the decoder Jacobian comes from forward-mode autodiff
+    (``functorch.jacfwd``, :613); residual, ``J @ dW/dy``, normal equations and the solve are float64
+    kernels.  ``ref`` is unused there and here.  Returns ``(red_coords (q, T+1), (num_its, jac_time,
+    res_time, ls_time))``."""
+    import torch
+    solver = ManifoldEcswSolver(grid_x, grid_y, weights, dt, mu, device=device)
+    dev = solver.device
+    f32 = dict(dtype=torch.float32, device=dev)
+    tmu = torch.tensor(list(mu)[:2], **f32)
+    B1 = torch.as_tensor(basis).to(**f32)
+    B2 = torch.as_tensor(basis2).to(**f32)
+    net = rnm.to(dev)
+    w0t = torch.as_tensor(np.asarray(w0, dtype=np.float64).ravel()).to(**f32)
+    y0 = B1.T @ w0t                                                      # :593
+    idx = torch.from_numpy(solver.idx).to(dev)
+    V, Vbar = B1[idx].contiguous(), B2[idx].contiguous()                 # :601-602
+
+    def decode32(x):
+        return V @ x + Vbar @ net(torch.cat((x, tmu)))                   # :603-605
+
+    def decode(x):
+        with torch.no_grad():
+            return decode32(x)
+
+    jac = torch.func.jacfwd(decode32)                                    # :613
+
+    def decode_jac(x):
+        return jac(x).detach()
+
+    def update(y, dy):
+        return y + dy.to(torch.float32)                                  # :2214
+
+    red, hist = solver.run(y0, int(num_steps), decode, decode_jac, update=update)
+    out = (np.ascontiguousarray(red.T.double().cpu().numpy()),
+           (sum(len(h) for h in hist), solver.jac_time, solver.res_time, solver.ls_time))
+    if return_info:
+        out += ({"gn_its": np.array([len(h) for h in hist]), "resnorms": hist},)
+    return out
 
 
 _RES_NAMES = ("inviscid_burgers_res2D", "inviscid_burgers_res2D_alt")

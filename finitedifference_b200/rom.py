@@ -129,6 +129,17 @@ class MeshTables:
         self.c = _lib.RomMesh(self.nrows, self.ncells, *[x.data_ptr() for x in self._t[:11]], wptr)
 
 
+def _check_finite(norm, what):
+    """The Gauss-Newton step comes from the k x k normal equations; a rank-deficient or hopelessly
+    ill-conditioned J V (fewer sampled rows than modes, dependent basis columns, zero weights) makes
+    them singular.  The reference's ``lstsq`` returns a minimum-norm step there; here that case is an
+    error, not a silent NaN trajectory."""
+    if not np.isfinite(norm):
+        raise _lib.BurgersError(f"{what}: non-finite residual norm -- the normal equations of the Gauss-Newton step "
+                                "were singular (rank-deficient J V: fewer sampled rows than modes, dependent basis "
+                                "columns or zero weights)")
+
+
 class _RomBase:
     def __init__(self, device=None, _backend=None):
         # _backend = (library, torch device): the CPU test-suite passes the SIMT-emulated build of
@@ -212,21 +223,39 @@ class _RomBase:
                    self.lib, "bfd_spd_solve")
         return dy
 
+    def gn_step_min_norm(self, G, b):
+        """Minimum-norm ``dy`` of a singular system ``G dy = -b`` (what ``lstsq(JV, -f)`` returns for a
+        rank-deficient ``JV``): eigen-decomposition of G, eigenvalues below ``k eps max`` dropped."""
+        lam, Q = torch.linalg.eigh(G)
+        keep = lam > lam.max() * G.shape[0] * np.finfo(np.float64).eps
+        return -(Q[:, keep] @ ((Q[:, keep].T @ b) / lam[keep]))
+
     def gauss_newton(self, res_mesh, jac_mesh, V, y0, wp, max_its=20, relnorm_cutoff=1e-5, min_delta=0.1):
         """``gauss_newton_LSPG`` / ``gauss_newton_ECSW_2D`` (:1935-2005, :2007-2044).
 
-        Returns ``(y, w, resnorms)``; the two stopping rules are the reference's, in its order.
+        Returns ``(y, w, resnorms)``; the two stopping rules are the reference's, in its order.  A
+        Cholesky step that produced a non-finite iterate (singular normal equations) is retaken as
+        the minimum-norm step; if that is not finite either the solver raises.
         """
         y = y0.clone()
         w = self.basis_times(V, y)
         f, init_norm = self.residual(res_mesh, w, wp)
+        _check_finite(init_norm, "gauss_newton")
         resnorms = []
+        retry = None
         for it in range(max_its):
             t0 = time.perf_counter()
             if it == 0:
                 resnorm = init_norm          # the reference evaluates the same residual twice (:1964, :1970)
             else:
-                f, resnorm = self.residual(res_mesh, w, wp)
+                f_new, resnorm = self.residual(res_mesh, w, wp)
+                if not np.isfinite(resnorm) and retry is not None:
+                    y_prev, G, b = retry
+                    y = y_prev + self.gn_step_min_norm(G, b)
+                    w = self.basis_times(V, y)
+                    f_new, resnorm = self.residual(res_mesh, w, wp)
+                _check_finite(resnorm, "gauss_newton")
+                f = f_new
             self.res_time += time.perf_counter() - t0
             resnorms.append(resnorm)
             if resnorm / init_norm < relnorm_cutoff:
@@ -239,6 +268,7 @@ class _RomBase:
             self.jac_time += time.perf_counter() - t0
             t0 = time.perf_counter()
             G, b = self.normal_equations(JV, f)            # normal equations of lstsq(JV, -f)
+            retry = (y, G, b)
             y = y + self.gn_step(G, b)
             w = self.basis_times(V, y)
             self._sync()
@@ -516,6 +546,7 @@ class EcswSolver(_RomBase):
                 self.res_time += time.perf_counter() - t0
                 self.graph_kernel_launches += 1             # rom_residual_kernel
                 init_norm = float(np.sqrt(self._h_n2[0].item()))
+                _check_finite(init_norm, "EcswSolver")
                 resnorms = [init_norm]                      # resnorms[0] is the same evaluation as init_norm
                 for _ in range(max_its - 1):
                     if resnorms[-1] / init_norm < relnorm_cutoff:
@@ -528,6 +559,7 @@ class EcswSolver(_RomBase):
                     self.ls_time += time.perf_counter() - t0
                     self.graph_kernel_launches += 2         # rom_jv_kernel, rom_residual_kernel
                     resnorms.append(float(np.sqrt(self._h_n2[0].item())))
+                    _check_finite(resnorms[-1], "EcswSolver")
                 else:
                     # max_its evaluations without a stop: the reference still takes its last step (:2024-2043)
                     if not (resnorms[-1] / init_norm < relnorm_cutoff or
@@ -585,7 +617,9 @@ class EcswBatch:
 
         def norm(i):
             self.events[i].synchronize()
-            return float(np.sqrt(S[i]._h_n2[0].item()))
+            r = float(np.sqrt(S[i]._h_n2[0].item()))
+            _check_finite(r, f"EcswBatch (parameter {i})")
+            return r
 
         def stop(r, init):
             return r[-1] / init < relnorm_cutoff or (len(r) > 1 and abs((r[-2] - r[-1]) / r[-2]) < min_delta)
@@ -668,3 +702,85 @@ def ecsw_training_matrix(snaps, prev_snaps, basis, grid_x, grid_y, dt, mu, devic
                                                  blk.data_ptr(), n_cells, base._stream()),
                        base.lib, "bfd_ecsw_c_fused")
     return Cmat if out_device else Cmat.cpu().numpy()
+
+
+class ManifoldEcswSolver(_RomBase):
+    """Sampled-mesh HPROM with a caller-supplied DECODER.
+
+    The reference's manifold ROMs -- ``inviscid_burgers_rnm2D_ecsw`` (:556-674, neural decoder),
+    ``inviscid_burgers_pod_rbf_2D_global_ecsw`` (:973-1111) and ``inviscid_burgers_pod_gp_2D_ecsw``
+    (:1113-1275) with their solvers ``gauss_newton_rnm_ecsw`` (:2167-2217), ``gauss_newton_pod_rbf_ecsw``
+    (:2293), ``gauss_newton_pod_gp_ecsw`` (:2382) -- all iterate on reduced coordinates ``y`` with
+    ``w = decode(y)`` on the augmented sample and the Gauss-Newton matrix ``J(w) @ d decode / d y``;
+    residual and Jacobian are the same ``res2D_ecsw`` / ``exact_jac2D_ecsw`` the linear HPROM uses.
+    Here the decoder and its Jacobian are callables on torch tensors living on the device:
+
+        decode(y)      -> (2 n_aug,) float64 CUDA tensor  [u of augmented cells | v of augmented cells]
+        decode_jac(y)  -> (2 n_aug, q) float64 CUDA tensor (row-major)
+
+    and the sampled residual (``bfd_rom_residual``), ``J(w) @ (d decode / d y)`` (``bfd_rom_jv``: the
+    decoder Jacobian takes the place of ``V_red``), the normal equations and the q x q solve are the
+    kernels of ``EcswSolver``.  ``idx`` holds the state entries the decoder must produce (:599).
+    """
+
+    def __init__(self, grid_x, grid_y, weights, dt, mu, device=None):
+        super().__init__(device)
+        weights = np.asarray(weights, dtype=np.float64).ravel()
+        self.sample_inds = np.where(weights != 0)[0].astype(np.int64)
+        self.augmented_sample = generate_augmented_mesh(grid_x, grid_y, self.sample_inds)
+        n_cells = weights.size
+        self.sample_weights = np.concatenate((weights, weights))[self.sample_inds]           # :584
+        self.idx = np.concatenate((self.augmented_sample, n_cells + self.augmented_sample))   # :599
+        self.mu = list(mu)[:2]
+        self.mesh = MeshTables(grid_x, grid_y, dt, self.mu, self.device, rows=self.sample_inds,
+                               state_cells=self.augmented_sample, weight=self.sample_weights)
+
+    def gauss_newton(self, y0, wp, decode, decode_jac, max_its=20, relnorm_cutoff=1e-5, min_delta=0.1,
+                     update=None):
+        """``gauss_newton_rnm_ecsw`` (:2167-2217): returns ``(y, w, resnorms)``.  ``update(y, dy)`` lets the
+        caller apply the step in its own precision (the reference keeps ``y`` in float32)."""
+        y = y0.clone()
+        w = decode(y).to(torch.float64).contiguous()
+        f, init_norm = self.residual(self.mesh, w, wp)
+        _check_finite(init_norm, "ManifoldEcswSolver")
+        resnorms = []
+        for it in range(max_its):
+            t0 = time.perf_counter()
+            if it > 0:
+                f, resnorm = self.residual(self.mesh, w, wp)
+                _check_finite(resnorm, "ManifoldEcswSolver")
+            else:
+                resnorm = init_norm
+            self.res_time += time.perf_counter() - t0
+            resnorms.append(resnorm)
+            if resnorm / init_norm < relnorm_cutoff:
+                break
+            if len(resnorms) > 1 and abs((resnorms[-2] - resnorms[-1]) / resnorms[-2]) < min_delta:
+                break
+            t0 = time.perf_counter()
+            Vq = decode_jac(y).to(torch.float64).contiguous()
+            JV = self.jv(self.mesh, w, Vq)
+            self._sync()
+            self.jac_time += time.perf_counter() - t0
+            t0 = time.perf_counter()
+            G, b = self.normal_equations(JV, f)
+            dy = self.gn_step(G, b)
+            y = update(y, dy) if update is not None else y + dy
+            w = decode(y).to(torch.float64).contiguous()
+            self._sync()
+            self.ls_time += time.perf_counter() - t0
+        return y, w, resnorms
+
+    def run(self, y0, num_steps, decode, decode_jac, **gn_kw):
+        """Time stepping of the manifold HPROM (:640-672).  Returns ``(red_coords (T+1, q) tensor, per-step
+        resnorm lists)``."""
+        y = y0.clone()
+        red = [y.clone()]
+        wp = decode(y).to(torch.float64).contiguous()
+        history = []
+        for _ in range(num_steps):
+            y, w, resnorms = self.gauss_newton(y, wp, decode, decode_jac, **gn_kw)
+            history.append(resnorms)
+            red.append(y.clone())
+            wp = w
+        return torch.stack(red), history

@@ -15,6 +15,7 @@ Fixtures (all float64 / int64, ``np.savez_compressed``):
   lspg_n24.npz       POD basis, LSPG trajectory, per-step GN iteration counts
   ecsw_n24.npz       NNLS weights, sample/augmented index sets, HPROM reduced coordinates
   ecswC_n12.npz      ECSW training matrix
+  manifold_n24.npz   neural-manifold HPROM (inviscid_burgers_rnm2D_ecsw) with a seeded MLP decoder
   fom_n250.npz, fom_n750.npz   (--large) per-snapshot norms + strided samples
 """
 import argparse
@@ -176,6 +177,43 @@ def gen_training_matrix(ref):
                         snaps=S, basis=basis, C=C)
 
 
+def manifold_decoder(q=6, nbar=4, seed=0):
+    """The tiny seeded decoder network of the manifold-HPROM fixture (float32, as the reference's)."""
+    import torch
+    torch.manual_seed(seed)
+    net = torch.nn.Sequential(torch.nn.Linear(q + 2, 10), torch.nn.ELU(), torch.nn.Linear(10, nbar))
+    with torch.no_grad():
+        net[2].weight.mul_(0.05)
+        net[2].bias.mul_(0.05)
+    return net
+
+
+def gen_manifold(ref):
+    """inviscid_burgers_rnm2D_ecsw (hypernet2D.py:556-674) on the 24^2 ECSW fixture's weights and basis,
+    with four further POD modes as the second basis and a seeded MLP as the decoder network."""
+    import torch
+    g = np.load(os.path.join(OUT, "ecsw_n24.npz"))
+    n, steps, dt, mu = int(g["n"]), 8, float(g["dt"]), [4.75, 0.02]
+    gx, gy, w0 = grid_and_w0(ref, n)
+    train = [[4.25, 0.015], [5.5, 0.03], [4.25, 0.0225]]
+    with quiet():
+        S = [ref.inviscid_burgers_implicit2D(gx, gy, w0, dt, 12, m) for m in train]
+    u, _ = ref.POD(np.hstack(S), method="svd")
+    q = g["basis"].shape[1]
+    assert np.allclose(np.abs(u[:, :q].T @ g["basis"]), np.eye(q), atol=1e-8)
+    basis2 = np.ascontiguousarray(u[:, q:q + 4])
+    net = manifold_decoder(q, 4)
+    counts, restore = record_counts(ref, "gauss_newton_rnm_ecsw")
+    with quiet():
+        red, times = ref.inviscid_burgers_rnm2D_ecsw(gx, gy, w0, dt, steps, mu, net, None,
+                                                     torch.tensor(g["basis"], dtype=torch.float),
+                                                     torch.tensor(basis2, dtype=torch.float), g["weights"])
+    restore()
+    np.savez_compressed(os.path.join(OUT, "manifold_n24.npz"), n=n, mu=mu, dt=dt, steps=steps, basis=g["basis"],
+                        basis2=basis2, weights=g["weights"], red_coords=red, gn_its=np.array(counts), num_its=times[0],
+                        **{"net_" + k.replace(".", "_"): v.numpy() for k, v in net.state_dict().items()})
+
+
 def gen_large(ref, n, steps, mu, stride):
     gx, gy, w0 = grid_and_w0(ref, n)
     counts, restore = record_counts(ref, "newton_raphson")
@@ -199,6 +237,7 @@ def main():
     gen_fom(ref, 48, 10, [4.25, 0.015])
     gen_lspg_ecsw(ref)
     gen_training_matrix(ref)
+    gen_manifold(ref)
     if args.large:
         gen_large(ref, 250, 3, [5.19, 0.026], 7)
         gen_large(ref, 750, 2, [4.75, 0.02], 61)

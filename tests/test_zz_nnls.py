@@ -42,6 +42,23 @@ def test_reference_shaped_problem_kkt(m, n, seed):
     kkt(A, b, x, 1e-8 * np.abs(A).sum())
 
 
+def rank_deficient_problem(seed=11, m=25, n=120):
+    """Duplicated and linearly combined columns, more columns than rows, exact solution x = 1."""
+    rng = np.random.default_rng(seed)
+    base = rng.standard_normal((m, n // 3)) * rng.random(n // 3)
+    A = np.hstack([base, base, 0.5 * base + 0.5 * np.roll(base, 1, axis=1)])
+    return A, A.sum(axis=1)
+
+
+def test_rank_deficient_blocks_terminate_with_kkt():
+    """Dependent passive columns (the Cholesky of the passive Gram matrix breaks down): the
+    minimum-norm branch, no cycling, optimality conditions hold."""
+    A, b = rank_deficient_problem()
+    x, rnorm, its = N.nnls_tensor(torch.from_numpy(A), torch.from_numpy(b), maxiter=9999999999)
+    assert rnorm <= 1e-8 * np.linalg.norm(b) and its < 10 * A.shape[1]
+    kkt(A, b, x.numpy(), 1e-7 * np.abs(A).sum())
+
+
 def test_edge_cases():
     A = np.array([[1.0, 0.0], [1.0, 0.0], [0.0, 1.0]])
     x, r, _ = N.nnls_tensor(torch.from_numpy(A), torch.tensor([2.0, 1.0, 1.0], dtype=torch.float64))
@@ -64,6 +81,10 @@ def test_device_path_and_block_training():
     x, r = N.nnls(A, b)
     xs, rs = scipy_nnls(A, b)
     assert np.allclose(x, xs, rtol=1e-8, atol=1e-10) and abs(r - rs) < 1e-9
+    Ad, bd = rank_deficient_problem()                      # dependent columns on the device path
+    xd, rd = N.nnls(Ad, bd, maxiter=9999999999)
+    assert rd <= 1e-8 * np.linalg.norm(bd)
+    kkt(Ad, bd, xd, 1e-7 * np.abs(Ad).sum())
     C = rng.standard_normal((24, 300)) * rng.random(300)
     wts = N.ecsw_weights(C, blocks=5)
     assert wts.shape == (300,) and (wts >= 0).all()
