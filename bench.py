@@ -158,8 +158,8 @@ def main():
     ap.add_argument("--e2e-group", type=int, default=2, help="samples a sweep worker advances together")
     ap.add_argument("--e2e-workers", type=int, default=3, help="sweep worker threads / streams")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--kernel", default="tile", choices=["tile", "legacy"],
-                    help="FOM sweep kernel: fom_tile_kernel (default) or the round-1 fom_chunk_kernel")
+    ap.add_argument("--kernel", default="chunk", choices=["chunk", "tile"],
+                    help="FOM sweep kernel: fom_chunk_kernel (default) or fom_tile_kernel (warp per strip and time step)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

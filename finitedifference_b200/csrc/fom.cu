@@ -180,7 +180,7 @@ struct FomArgs {
     size_t edge_stride_strip, edge_stride_mu, pool_stride_mu;
     // slab runs (whole grid: strip0 = 0, ns_global = ssl.nstrips, the rest unused)
     int strip0, ns_global, launch_index, slab;
-    int variant;        // 0: fom_tile_kernel (warp per strip and time step), 1: fom_chunk_kernel (levels split over warps)
+    int variant;        // 0: fom_chunk_kernel (levels split over warps), 1: fom_tile_kernel (warp per strip and time step)
     int kcap;           // Newton solves the variant fuses into one pass at most
     unsigned *ticket;   // virtual block id dispenser of THIS rank (glob may be rank 0's)
     double *halo;       // [batch][chunk][ny][kRecDoubles] records consumed by this rank's first strip
@@ -205,7 +205,7 @@ static FomArgs fom_args(const bfd_fom_desc *d, const FomLayout &L, void *ws, con
     a.partial = (double *)(h + L.off_partial);
     a.ticket = &((FomGlobal *)(b + L.off_global))->ticket;
     a.strip0 = v.strip0; a.ns_global = v.ns_global; a.launch_index = 0; a.slab = v.slab ? 1 : 0;
-    a.variant = d->kernel; a.kcap = d->kernel == 0 ? 4 : kKMax;     // kTileKMax (fom_tile.cuh)
+    a.variant = d->kernel; a.kcap = d->kernel == 1 ? 4 : kKMax;     // kTileKMax (fom_tile.cuh)
     a.halo = v.strip0 > 0 ? (double *)(b + L.off_halo) : nullptr;
     a.next_halo = v.next_halo;
     a.trace = (unsigned long long *)(b + L.off_trace);
@@ -1095,7 +1095,7 @@ static int fom_set_initial_impl(const bfd_fom_desc *d, const SlabView &v, void *
 
 static int launch_chunk(const FomArgs &a, cudaStream_t st) {
     const int grid = a.batch * a.ssl.nstrips;
-    if (a.variant == 0) {
+    if (a.variant == 1) {
         void (*kernel)(const FomArgs) =
             a.slab ? (a.uniform_y ? fom_tile_kernel<true, true> : fom_tile_kernel<false, true>)
                    : (a.uniform_y ? fom_tile_kernel<true, false> : fom_tile_kernel<false, false>);

@@ -1,20 +1,28 @@
 // fom_tile_kernel: the FOM sweep with one WARP per (strip, time step) and kTileDepth consecutive time
 // steps of a strip in flight inside one CTA.  Included by fom.cu (shares FomArgs, the verdict /
-// commit logic and the strip-to-strip hand-off records with fom_chunk_kernel, which stays as the
-// `legacy` variant).
+// commit logic and the strip-to-strip hand-off records with fom_chunk_kernel).  Selectable variant
+// (bfd_fom_desc.kernel = 1); fom_chunk_kernel stays the default because it is 6 % faster on B200
+// (37.2 vs 34.5-35.2 G cell-updates/s at the bench's shape) -- what was tried and measured is in
+// profiles/r02_notes.md and DESIGN.md 4.1b.
 //
-// Why (profiles/r02_notes.md): fom_chunk_kernel splits the K+1 Newton levels of a time step between
-// four warps and a data-movement warp that meet at one CTA barrier per wavefront step.  ncu: every
-// scheduler holds 5 warps that each issue once per ~10.6 cycles (barrier 2.6, fixed-latency waits 2.4,
-// shared-memory scoreboard 1.1 per issue), FP64 pipe 51 % busy; the register file (96 x 160 x 4) admits
-// no more warps.  A variant with ALL levels in one warp (5 independent dependency chains per lane)
-// reached 64 % of that kernel's throughput with a single compute warp per scheduler.  So: give every
-// warp all levels of a time step (no level hand-off, no CTA barrier, no data-movement warp: 405 -> ~300
-// instructions per strip-step), and get the warps from TIME instead of from levels -- warp d of a CTA
-// advances time steps t = d, d + D, d + 2D, ... of its strip, each trailing its predecessor by a few
-// rows.  The iterate x_{t+1} a warp produces goes to the snapshot pool in HBM; the warp that advances
-// step t+1 fetches it from there a few rows later (an L2 hit: the strip's state never comes back from
-// DRAM between the time steps of a launch) as soon as the producer's row counter allows.
+// Why it was built: fom_chunk_kernel splits the K+1 Newton levels of a time step between four warps
+// and a data-movement warp that meet at one CTA barrier per wavefront step.  ncu: every scheduler
+// holds 5 warps (one of each role: the warp slots of a 5-warp CTA are dealt round-robin to the four
+// schedulers, tools/warp_slot_probe.cu) that each issue once per ~10.6 cycles (barrier 2.6, fixed-
+// latency waits 2.4, shared-memory scoreboard 1.1 per issue), FP64 pipe 51 % busy; the register file
+// (96 x 160 x 4) admits no more warps.  A variant with ALL levels in one warp reached 64 % of that
+// kernel's throughput with a single compute warp per scheduler.  So: give every warp all levels of a
+// time step (no level hand-off, no CTA barrier, no data-movement warp) and get the warps from TIME
+// instead of from levels -- warp d of a CTA advances time steps t = d, d + D, d + 2D, ... of its strip,
+// each trailing its predecessor by a few rows.  The iterate x_{t+1} a warp produces goes to the
+// snapshot pool; the warp that advances step t+1 fetches it from there a few rows later as soon as
+// the producer's row counter allows.
+// What the measurements said: the warps do issue twice as often (5.4 cycles per instruction), but a
+// strip-step costs 480-500 instructions instead of 405 (the hand-off and prefetch code of the data-
+// movement warp now runs in every warp, ~120; 55-60 register moves for the level pipeline at the 168-
+// register cap) and ptxas emits the five independent levels one after the other (fixed-latency waits
+// 1.7-2.2 per issue), so three warps per scheduler keep the FP64 pipe 47-48 % busy -- no better than
+// five single-level warps with a barrier.
 //
 //   * level-0 input: a ring of kTRing slot-rows (u | v, 512 B each) per warp, filled kTPf - 1 rows
 //     ahead by 16-byte cp.async copies; rows of a time step produced in this segment are gated by the
@@ -25,7 +33,7 @@
 //   * left neighbour inside the strip: the double-buffered exchange rows of fom_chunk_kernel (slot l+1
 //     written by lane l, slot l read by lane l one step later), one __syncwarp per step;
 //   * strip-to-strip hand-off: the same self-validating 16-byte records in global memory, moved by
-//     lanes < NPR of the same warp (piece p by lane p): copied into a shared-memory ring kAhead rows
+//     lanes < NPR of the same warp (piece p by lane p): copied into a shared-memory ring kTAhead rows
 //     early, dropped into the halo slot 0 one step early, lane 31's slot 32 sent on the step after;
 //   * Newton bookkeeping (speculated solve count, device-side verdict, stop / restart inside the
 //     launch) unchanged; at most kTileKMax solves are fused per pass, a step that needs more gets
@@ -48,7 +56,10 @@ constexpr int kTWarpBytes = kTXchgBytes + kTRingBytes + kTEdgeBytes;
 constexpr int kTWpOffset = 4 * 2 * kXRow;               // CONT (K = 1) keeps the previous snapshot's ring in the unused exchange rows
 static_assert(kTWpOffset + kTRingBytes <= kTXchgBytes, "the wp ring of continuation passes fits the spare exchange rows");
 static_assert(kTileDepth * kTWarpBytes + 256 <= 48 * 1024, "static shared memory of a CTA");
-static_assert(kAhead + 2 <= kTEdgeRing, "rows in flight plus the row in use must fit the ring");
+constexpr int kTAhead = 8;                    // rows copied into the hand-off ring ahead of their use
+constexpr int kTStartRow = 24;                // a strip starts a time step when its left neighbour has finished this row
+constexpr int kTPublish = 4;                  // the row counter is published every kTPublish rows
+static_assert(kTAhead + 2 <= kTEdgeRing, "rows in flight plus the row in use must fit the ring");
 
 struct TileIo {
     const double *xin;    // level-0 iterate when read from HBM: snapshot t, or the partly converged slot t+1 (CONT)
@@ -65,6 +76,7 @@ struct TileIo {
     double cx, cxl, src;
     bool colok, inlet, in_remote, out_remote;
     int *error;
+    unsigned long long *wait_ns;   // trace: time spent waiting for the left strip's start distance
 };
 
 #ifdef BFD_EMULATE
@@ -73,25 +85,41 @@ struct TileIo {
 #define BFD_TRACE_SPIN(spins, ...) do { } while (0)
 #endif
 #ifndef BFD_EMULATE
+__device__ __forceinline__ void start_pause() { __nanosleep(400); }
 __device__ __forceinline__ int ld_shared_volatile(const volatile int *p) { return *p; }
 #else
+inline void start_pause() { std::this_thread::yield(); }
 inline int ld_shared_volatile(const volatile int *p) { std::this_thread::yield(); return __atomic_load_n((const int *)p, __ATOMIC_ACQUIRE); }
 #endif
 
+// A value the compiler must keep in a register instead of recomputing it where it is used (under
+// register pressure it rematerialises shared-window addresses with S2R SR_CgaCtaId + arithmetic in
+// every wavefront step: profiles/r02_notes.md).
+#ifndef BFD_EMULATE
+__device__ __forceinline__ unsigned keep_reg(unsigned v) { asm volatile("" : "+r"(v)); return v; }
+__device__ __forceinline__ int keep_reg(int v) { asm volatile("" : "+r"(v)); return v; }
+#else
+inline saddr keep_reg(saddr v) { return v; }
+inline int keep_reg(int v) { return v; }
+#endif
+
 // All K+1 levels of one trapezoidal time step of one strip, by one warp.  Arithmetic identical to
-// sweep_part (same operations in the same order: bit-identical results).
+// sweep_part up to exact power-of-two rescalings (the 0.5 factors ride on the iterate): the same bits.
 template <int K, bool CONT, bool UNI>
 __device__ __forceinline__ void tile_step(const TileIo &io) {
     constexpr int NPR = 2 * K + 1 + (CONT ? 1 : 0);
     constexpr int W = 32;
     static_assert(NPR <= kTPieces && K <= kTileKMax, "exchange rows");
-    const int lane = io.lane, ny = io.ny;
+    const int lane = keep_reg(io.lane), ny = io.ny;
     const int last_row = ny + kSkew - 1;   // last slot-row holding cells
     const int nsteps = ny + kSkew + K;
     const bool colok = io.colok;
     const bool gated = io.gated, publish = io.publish;
+    const saddr io_xchg = keep_reg(io.xchg), io_ring = keep_reg(io.ring), io_edge_ring = keep_reg(io.edge_ring);
 
-    const double cx = io.cx, cxl = io.cxl, hcx = 0.5 * io.cx, hcxl = 0.5 * io.cxl, ncxl = -io.cxl;
+    // 0.5 factors ride on the iterate (hu = u/2, hv = v/2, hpm = (v du + u dv)/2) and signs on the FMA
+    // operands: five column / row constants in registers instead of eleven, the same bits
+    const double cx = io.cx, cxl = io.cxl;
     const double src = io.src;
     double cyU = 0.0, cydU = 0.0;
     if (UNI) { cyU = __ldg(io.cy + (ny > 1 ? 1 : 0)); cydU = __ldg(io.cyd + (ny > 1 ? 1 : 0)); }
@@ -103,8 +131,8 @@ __device__ __forceinline__ void tile_step(const TileIo &io) {
     double xu[K + 1], xv[K + 1], Au[K + 1], Av[K + 1], Cy[K + 1], Cyd[K + 1], nrm[K + 1];
 #pragma unroll
     for (int k = 0; k <= K; ++k) { xu[k] = xv[k] = Au[k] = Av[k] = 0.0; Cy[k] = cyU; Cyd[k] = cydU; nrm[k] = 0.0; }
-    const saddr xc_own = io.xchg + (saddr)((lane + 1) * 16);
-    const saddr xc_left = io.xchg + (saddr)(lane * 16);
+    const saddr xc_own = io_xchg + (saddr)((lane + 1) * 16);
+    const saddr xc_left = io_xchg + (saddr)(lane * 16);
     auto xc_piece = [](int p, int buf) { return (saddr)((p * 2 + buf) * kXRow); };
 
     // ---- strip-to-strip hand-off: lane p moves piece p of the row records (see dma_part) --------
@@ -112,8 +140,8 @@ __device__ __forceinline__ void tile_step(const TileIo &io) {
     const int lvl = special ? 0 : (lane >> 1);
     const bool take = lane < NPR && io.strip > 0, give = lane < NPR && io.strip < io.nstrips - 1;
     const bool in_remote = io.in_remote, out_remote = io.out_remote;
-    const saddr px = io.xchg + (saddr)((lane < NPR ? lane : 0) * 2 * kXRow);     // piece `lane`, buffer 0
-    const saddr ering = io.edge_ring + (saddr)((lane < NPR ? lane : 0) * 16);
+    const saddr px = io_xchg + (saddr)((lane < NPR ? lane : 0) * 2 * kXRow);     // piece `lane`, buffer 0
+    const saddr ering = io_edge_ring + (saddr)((lane < NPR ? lane : 0) * 16);
     auto ering_row = [&](int r) { return ering + (saddr)((r & (kTEdgeRing - 1)) * kTEdgeRowBytes); };
     double *gin = io.edge_in + 2 * lane - (ptrdiff_t)lvl * kRecDoubles;                       // row consumed by the call for step -1
     double *gout = io.edge_out + 2 * lane - (ptrdiff_t)(2 + kSkew + lvl) * kRecDoubles;      // row sent by that call
@@ -122,19 +150,21 @@ __device__ __forceinline__ void tile_step(const TileIo &io) {
 
     if (io.strip > 0) {
         // start distance: not before the strip on the left is kStartRow rows into this time step
-        const int rw = kStartRow < ny ? kStartRow : ny - 1;
+        const int rw = kTStartRow < ny ? kTStartRow : ny - 1;
         const double *gw = io.edge_in + (size_t)rw * kRecDoubles + 2 * ((NPR - 1) & ~1);
         unsigned spins = 0;
+        const unsigned long long tw0 = global_timer_ns();
         for (;;) {
             double a = 0.0, b = 0.0;
             if (lane == 0) { if (in_remote) ld_sys2(gw, a, b); else ld_volatile2(gw, a, b); }
             if (__all_sync(0xffffffffu, !(is_sentinel(a) || is_sentinel(b)))) break;
             if (++spins > kSpinLimit) { err = BFD_ETIMEOUT; break; }
-            spin_pause();
+            start_pause();                                   // a waiting warp must not eat the issue slots of the running ones
         }
+        if (lane == 0) *io.wait_ns = global_timer_ns() - tw0;
         if (take) {
 #pragma unroll
-            for (int r = 0; r < kAhead; ++r)
+            for (int r = 0; r < kTAhead; ++r)
                 if (r < ny) cp_async16(ering_row(r), io.edge_in + 2 * lane + (size_t)r * kRecDoubles);
         }
     }
@@ -156,7 +186,7 @@ __device__ __forceinline__ void tile_step(const TileIo &io) {
             }
             sts2(px + (saddr)(wbuf * kXRow), va, vb);
             st_weak2(gin, sentinel_value(), sentinel_value());       // re-arm for the next launch
-            if (rc + kAhead < ny) cp_async16(ering_row(rc + kAhead), gin + (size_t)kAhead * kRecDoubles);
+            if (rc + kTAhead < ny) cp_async16(ering_row(rc + kTAhead), gin + (size_t)kTAhead * kRecDoubles);
         }
         if (give && (unsigned)ro < (unsigned)ny) {
             double a, b;
@@ -168,10 +198,10 @@ __device__ __forceinline__ void tile_step(const TileIo &io) {
     };
 
     // ---- level-0 input ring ------------------------------------------------------------------
-    const saddr ring_lane = io.ring + (saddr)(lane * 8);
-    const saddr ring_cp = io.ring + (saddr)(lane * 16);
-    const saddr wp_lane = io.xchg + (saddr)(kTWpOffset + lane * 8);
-    const saddr wp_cp = io.xchg + (saddr)(kTWpOffset + lane * 16);
+    const saddr ring_lane = io_ring + (saddr)(lane * 8);
+    const saddr ring_cp = io_ring + (saddr)(lane * 16);
+    const saddr wp_lane = io_xchg + (saddr)(kTWpOffset + lane * 8);
+    const saddr wp_cp = io_xchg + (saddr)(kTWpOffset + lane * 16);
     const int in_base = io.in_base, out_base = io.out_base;
     int prod_seen = 0;                                       // cached row counter of the input's producer
     const double *gsrc = io.xin + lane, *gsrcp = io.xwp + lane;   // lane l copies doubles 2l, 2l+1 of a slot-row (u | v: 64 doubles)
@@ -227,7 +257,7 @@ __device__ __forceinline__ void tile_step(const TileIo &io) {
                 const saddr dp = wp_lane + (saddr)((srow & (kTRing - 1)) * 512);
                 up = lds(dp); vp = lds(dp + 256);
             } else { up = xu[0]; vp = xv[0]; }
-            if (io.inlet) lb_next = __ldg(io.lbc + (s + 1 < ny ? s + 1 : ny - 1));
+            if (io.strip == 0) { if (io.inlet) lb_next = __ldg(io.lbc + (s + 1 < ny ? s + 1 : ny - 1)); }   // warp-uniform outer test
             if (!UNI) {
                 Cy[0] = cy_next; Cyd[0] = cyd_next;
                 const int r = s + 1 - lane;
@@ -236,83 +266,103 @@ __device__ __forceinline__ void tile_step(const TileIo &io) {
             }
         }
 
+        // The K+1 levels of a step are independent of one another.  With one loop over the levels the
+        // compiler emitted them one after the other (serial DFMA chains, fixed-latency waits 2.2 per
+        // issue, ncu r02_tile_v2); so the step is written in two phases: the residuals of ALL levels
+        // first (2 (K+1) independent FMA chains side by side), then the K block solves.
+        double LF[K + 1], LG[K + 1];
 #pragma unroll
-        for (int k = K; k >= 0; --k) {
+        for (int k = K; k >= 0; --k) lds2(xc_left + xc_piece(2 * k, rbuf), LF[k], LG[k]);
+
+        {   // level 0 only: previous-snapshot parts and the level-independent terms Au, Av of row s - lane
+            const int rk = s - lane;
+            const bool top = EP ? (rk <= 0) : false;
+            const double cy = UNI ? cyU : Cy[0], cyd = UNI ? cydU : Cyd[0];
+            const double hup = 0.5 * up, hvp = 0.5 * vp;
+            const double Fp = hup * up, Gp = hup * vp, Hp = hvp * vp;
+            double DGp = CONT ? qGp : prev[0].Gh, DHp = CONT ? qHp : prev[0].Hh;
+            if (EP) { DGp = top ? 0.0 : DGp; DHp = top ? 0.0 : DHp; }
+            double lFp = LF[0], lGp = LG[0];
+            if (CONT) lds2(xc_left + xc_piece(2 * K + 1, rbuf), lFp, lGp);
+            double au = fma(cx, Fp, -up);
+            au = fma(cy, Gp, au); au = fma(-cxl, lFp, au); au = fma(-cyd, DGp, au);
+            au = (au - src) - lb;
+            double av = fma(cy, Hp, -vp);
+            av = fma(cx, Gp, av); av = fma(-cyd, DHp, av); av = fma(-cxl, lGp, av);
+            Au[0] = au; Av[0] = av;
+            if (CONT) {
+                qGp = Gp; qHp = Hp;
+                sts2(xc_own + xc_piece(2 * K + 1, wbuf), Fp, Gp);
+            }
+        }
+
+        double ru[K + 1], rv[K + 1];
+#pragma unroll
+        for (int k = K; k >= 0; --k) {                         // phase 1: residual rows of every level
             const int rk = s - lane - k;
             const bool rowok = EP ? (unsigned)rk < (unsigned)ny : true;
             const bool valid = rowok && colok;
             const bool top = EP ? (rk <= 0) : false;
             const double cy = UNI ? cyU : Cy[k], cyd = UNI ? cydU : Cyd[k];
-            const double hcy = 0.5 * cy, hcyd = 0.5 * cyd, ncyd = -cyd;
-
-            double LF, LG, Lpu = 0.0, Lpm = 0.0;
-            lds2(xc_left + xc_piece(2 * k, rbuf), LF, LG);
-            if (k < K) lds2(xc_left + xc_piece(2 * k + 1, rbuf), Lpu, Lpm);
-
-            if (k == 0) {
-                const double hup = 0.5 * up, hvp = 0.5 * vp;
-                const double Fp = hup * up, Gp = hup * vp, Hp = hvp * vp;
-                double DGp = CONT ? qGp : prev[0].Gh, DHp = CONT ? qHp : prev[0].Hh;
-                if (EP) { DGp = top ? 0.0 : DGp; DHp = top ? 0.0 : DHp; }
-                double lFp = LF, lGp = LG;
-                if (CONT) lds2(xc_left + xc_piece(2 * K + 1, rbuf), lFp, lGp);
-                double au = fma(cx, Fp, -up);
-                au = fma(cy, Gp, au); au = fma(ncxl, lFp, au); au = fma(ncyd, DGp, au);
-                au = (au - src) - lb;
-                double av = fma(cy, Hp, -vp);
-                av = fma(cx, Gp, av); av = fma(ncyd, DHp, av); av = fma(ncxl, lGp, av);
-                Au[0] = au; Av[0] = av;
-                if (CONT) {
-                    qGp = Gp; qHp = Hp;
-                    sts2(xc_own + xc_piece(2 * K + 1, wbuf), Fp, Gp);
-                }
-            }
-
             const double u = xu[k], v = xv[k];
             const double hu = 0.5 * u, hv = 0.5 * v;
             const double Fh = hu * u, Gh = hu * v, Hh = hv * v;
             double DG = prev[k].Gh, DH = prev[k].Hh;
             if (EP) { DG = top ? 0.0 : DG; DH = top ? 0.0 : DH; }
-            double ru = Au[k] + u;
-            ru = fma(cx, Fh, ru); ru = fma(cy, Gh, ru); ru = fma(ncxl, LF, ru); ru = fma(ncyd, DG, ru);
-            double rv = Av[k] + v;
-            rv = fma(cy, Hh, rv); rv = fma(cx, Gh, rv); rv = fma(ncyd, DH, rv); rv = fma(ncxl, LG, rv);
-            const double r2 = fma(rv, rv, ru * ru);
+            double a = Au[k] + u;
+            a = fma(cx, Fh, a); a = fma(cy, Gh, a); a = fma(-cxl, LF[k], a); a = fma(-cyd, DG, a);
+            double b = Av[k] + v;
+            b = fma(cy, Hh, b); b = fma(cx, Gh, b); b = fma(-cyd, DH, b); b = fma(-cxl, LG[k], b);
+            ru[k] = a; rv[k] = b;
+            const double r2 = fma(b, b, a * a);
             nrm[k] += EP ? (valid ? r2 : 0.0) : r2;
             sts2(xc_own + xc_piece(2 * k, wbuf), Fh, Gh);
             prev[k].Gh = Gh; prev[k].Hh = Hh;
+        }
 
-            if (k < K) {
-                double Dpm = prev[k].pm, Dpvv = prev[k].pvv;
-                if (EP) { Dpm = top ? 0.0 : Dpm; Dpvv = top ? 0.0 : Dpvv; }
-                const double bu_ = fma(hcyd, Dpm, fma(cxl, Lpu, ru));
-                const double bv_ = fma(cyd, Dpvv, fma(hcxl, Lpm, rv));
-                const double d00 = fma(cx, u, fma(hcy, v, 1.0));
-                const double d11 = fma(cy, v, fma(hcx, u, 1.0));
-                const double d01 = hcy * u, d10 = hcx * v;
-                const double inv = rcp_fast(fma(d00, d11, -(d01 * d10)));
-                const double du = fma(d11, bu_, -(d01 * bv_)) * inv;
-                const double dv = fma(d00, bv_, -(d10 * bu_)) * inv;
-                const double pu = u * du, pm = fma(v, du, u * dv);
-                prev[k].pm = pm; prev[k].pvv = v * dv;
-                sts2(xc_own + xc_piece(2 * k + 1, wbuf), pu, pm);
-                const double nu = u - du, nv = v - dv;
-                if (k == K - 1) {
-                    if (!EP || (so >= 0 && so <= last_row)) {
-                        const double ou = EP ? (valid ? nu : 0.0) : nu, ov = EP ? (valid ? nv : 0.0) : nv;
-                        double *o = io.xout + (size_t)so * (2 * W);
-                        o[0] = ou; o[W] = ov;
-                    }
+        double Lpu[K], Lhpm[K];
+#pragma unroll
+        for (int k = K - 1; k >= 0; --k) lds2(xc_left + xc_piece(2 * k + 1, rbuf), Lpu[k], Lhpm[k]);
+#pragma unroll
+        for (int k = K - 1; k >= 0; --k) {                     // phase 2: the 2x2 block solves
+            const int rk = s - lane - k;
+            const bool rowok = EP ? (unsigned)rk < (unsigned)ny : true;
+            const bool valid = rowok && colok;
+            const bool top = EP ? (rk <= 0) : false;
+            const double cy = UNI ? cyU : Cy[k], cyd = UNI ? cydU : Cyd[k];
+            const double u = xu[k], v = xv[k];
+            const double hu = 0.5 * u, hv = 0.5 * v;
+            double Dhpm = prev[k].pm, Dpvv = prev[k].pvv;        // prev[k].pm holds (v du + u dv) / 2
+            if (EP) { Dhpm = top ? 0.0 : Dhpm; Dpvv = top ? 0.0 : Dpvv; }
+            const double bu_ = fma(cyd, Dhpm, fma(cxl, Lpu[k], ru[k]));
+            const double bv_ = fma(cyd, Dpvv, fma(cxl, Lhpm[k], rv[k]));
+            const double d00 = fma(cx, u, fma(cy, hv, 1.0));
+            const double d11 = fma(cy, v, fma(cx, hu, 1.0));
+            const double d01 = cy * hu, d10 = cx * hv;
+            const double inv = rcp_fast(fma(d00, d11, -(d01 * d10)));
+            const double du = fma(d11, bu_, -(d01 * bv_)) * inv;
+            const double dv = fma(d00, bv_, -(d10 * bu_)) * inv;
+            const double pu = u * du, hpm = fma(hv, du, hu * dv);
+            prev[k].pm = hpm; prev[k].pvv = v * dv;
+            sts2(xc_own + xc_piece(2 * k + 1, wbuf), pu, hpm);
+            const double nu = u - du, nv = v - dv;
+            if (k == K - 1) {
+                if (!EP || (so >= 0 && so <= last_row)) {
+                    const double ou = EP ? (valid ? nu : 0.0) : nu, ov = EP ? (valid ? nv : 0.0) : nv;
+                    double *o = io.xout + (size_t)so * (2 * W);
+                    o[0] = ou; o[W] = ov;
                 }
-                xu[k + 1] = nu; xv[k + 1] = nv;
-                Au[k + 1] = Au[k]; Av[k + 1] = Av[k];
-                if (!UNI) { Cy[k + 1] = Cy[k]; Cyd[k + 1] = Cyd[k]; }
             }
+            xu[k + 1] = nu; xv[k + 1] = nv;
+            Au[k + 1] = Au[k]; Av[k + 1] = Av[k];
+            if (!UNI) { Cy[k + 1] = Cy[k]; Cyd[k + 1] = Cyd[k]; }
         }
         cp_async_wait_pending<kTPf - 2>();
         __syncwarp();
         // rows 0 .. so of x_{t+1} are in the pool: the warp that advances the next time step may fetch them
-        if (publish && lane == 0 && so >= 0 && so <= last_row) { __threadfence_block(); *io.prod_out = out_base + so + 1; }
+        if (publish && ((so & (kTPublish - 1)) == kTPublish - 1 || so == last_row) && so >= 0 && so <= last_row) {
+            if (lane == 0) { __threadfence_block(); *io.prod_out = out_base + so + 1; }
+        }
     };
 
     const int head_end = nsteps < kSkew + K + 1 ? nsteps : kSkew + K + 1;
@@ -452,6 +502,7 @@ __global__ void __launch_bounds__(32 * kTileDepth, 4) fom_tile_kernel(const FomA
             io.out_base = (ii / D) * NR;
             unsigned long long *tr = a.trace + ((size_t)(m * a.chunk + att) * nstrips + j) * 3;
             if (lane == 0) { tr[0] = global_timer_ns(); tr[2] = 0; }
+            io.wait_ns = tr + 2;
             if (kb) {
                 tile_step<1, true, UNI>(io);
             } else {

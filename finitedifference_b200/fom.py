@@ -53,7 +53,7 @@ class FomSolver:
     """
 
     def __init__(self, grid_x, grid_y, dt, num_steps, mus, device=None, max_its=100, rel_tol=1e-12,
-                 strict=True, chunk_steps=0, newton_hint=0, kernel="tile"):
+                 strict=True, chunk_steps=0, newton_hint=0, kernel="chunk"):
         self.lib = _lib.get_lib()
         self.device = _require_cuda(device)
         self.grid_x = np.asarray(grid_x, dtype=np.float64)
@@ -65,7 +65,7 @@ class FomSolver:
         self.uniform_y = is_uniform(cy, cyd)
         self.desc = _lib.fom_desc(self.nx, self.ny, self.batch, self.num_steps, max_its, rel_tol,
                                   chunk_steps, newton_hint, strict, self.uniform_y,
-                                  kernel={"tile": 0, "legacy": 1}[kernel])
+                                  kernel={"chunk": 0, "tile": 1}[kernel])
         nbytes = self.lib.bfd_fom_workspace_bytes(C.byref(self.desc))
         if nbytes == 0:
             raise _lib.BurgersError("invalid FOM description")

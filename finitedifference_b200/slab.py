@@ -51,7 +51,7 @@ class FomSlab:
     """This rank's slab of one FOM trajectory batch (usually a single mu)."""
 
     def __init__(self, grid_x, grid_y, dt, num_steps, mus, rank, world, device=None, max_its=100, rel_tol=1e-12,
-                 strict=True, chunk_steps=0, newton_hint=0, lib=None, host_memory=False, kernel="tile"):
+                 strict=True, chunk_steps=0, newton_hint=0, lib=None, host_memory=False, kernel="chunk"):
         self.lib = lib or _lib.get_lib()
         self.host_memory = host_memory                      # emulator tests: NumPy buffers, no CUDA
         self.device = torch.device("cpu") if host_memory else _require_cuda(device)
@@ -66,7 +66,7 @@ class FomSlab:
         cx, cxl, cy, cyd = stencil_coefficients(gx, gy, float(dt))
         src, lbc = parameter_terms(gx, gy, float(dt), self.mus)
         self.desc = _lib.fom_desc(self.nx, self.ny, self.batch, self.num_steps, max_its, rel_tol, chunk_steps,
-                                  newton_hint, strict, is_uniform(cy, cyd), kernel={"tile": 0, "legacy": 1}[kernel])
+                                  newton_hint, strict, is_uniform(cy, cyd), kernel={"chunk": 0, "tile": 1}[kernel])
         self.slab = _lib.FomSlab(self.rank, self.world, self.strips[0], self.strips[1], None, None)
         self.nbytes = self.lib.bfd_fom_slab_workspace_bytes(C.byref(self.desc), C.byref(self.slab))
         if self.nbytes == 0:

@@ -64,9 +64,10 @@ typedef struct bfd_fom_desc {
                                 them (a step whose speculated solve count was too high is redone);
                                 0: such a step keeps its further-converged iterate */
     int32_t uniform_y;       /* 1: cy[r] and cyd[r>0] are one value (held in a register) */
-    int32_t kernel;          /* 0 (default): fom_tile_kernel, one warp per strip and time step, three time steps of a
-                                strip in flight per CTA; 1: fom_chunk_kernel, the Newton levels of a step split over the
-                                warps of a CTA (round-1 kernel, kept for comparison).  Same results bit for bit. */
+    int32_t kernel;          /* 0 (default): fom_chunk_kernel, the Newton levels of a step split over the warps of a
+                                CTA; 1: fom_tile_kernel, one warp per strip and time step with all levels in registers,
+                                three time steps of a strip in flight per CTA (no CTA barrier, no data-movement warp;
+                                measured 6 % slower on B200, kept selectable: DESIGN.md 4.1b).  Same results. */
     double rel_tol;          /* relnorm_cutoff, < 1; the reference passes 1e-12 (:123) */
 } bfd_fom_desc;
 

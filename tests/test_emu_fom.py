@@ -24,16 +24,21 @@ def rel_err(a, b):
     (20, 20, [[4.4, 0.016]], dict(newton_hint=6)),                 # over-speculated: the step is redone
     (40, 72, [[4.75, 0.02]], {}),                                  # tall enough for the unmasked main phases (ny > 52)
     (40, 72, [[4.75, 0.02]], dict(newton_hint=1, chunk_steps=2)),  # ... of the continuation pass too
+    (40, 40, [[5.19, 0.026], [4.3, 0.03]], dict(chunk_steps=5, kernel=1)),        # fom_tile_kernel: 3 time steps in flight per strip
+    (70, 33, [[5.0, 0.02]], dict(uniform_y=False, kernel=1)),                     # ... ragged last strip, cy[] path
+    (33, 20, [[5.0, 0.02]], dict(newton_hint=1, chunk_steps=4, kernel=1)),        # ... continuation passes
+    (40, 72, [[4.75, 0.02]], dict(newton_hint=6, kernel=1)),                      # ... capped at 4 fused solves, redo, main phase
 ])
 def test_emulated_fom_matches_oracle(lib, nx, ny, mus, kw):
     gx, gy = orc.make_2D_grid(0, 100, 0, 100, nx, ny)
     w0 = np.ones(2 * nx * ny)
     stats = {}
-    snaps, its, rel = E.fom_run(lib, gx, gy, w0, 0.05, 3, mus, stats=stats, **kw)
+    steps = 5 if kw.get("kernel") else 3
+    snaps, its, rel = E.fom_run(lib, gx, gy, w0, 0.05, steps, mus, stats=stats, **kw)
     if "newton_hint" in kw:
         assert stats["redone"] >= 1
     for m, mu in enumerate(mus):
-        ref, hist = orc.fom_trajectory(gx, gy, w0, 0.05, 3, mu, return_info=True)
+        ref, hist = orc.fom_trajectory(gx, gy, w0, 0.05, steps, mu, return_info=True)
         assert its[m].tolist() == [len(h) for h in hist]
         assert rel_err(snaps[m], ref) < 1e-13
         assert np.all(rel[m] < 1e-12)

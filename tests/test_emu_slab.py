@@ -55,6 +55,8 @@ def run_group(lib, n_x, n_y, steps, mu, world, **kw):
     (3, 96, dict(newton_hint=1)),                       # under-speculation: continuation passes across ranks
     (2, 64, dict(newton_hint=6)),                       # over-speculation: strict redo across ranks
     (2, 64, dict(chunk_steps=1)),                       # one step per launch: the launch hand-shake every step
+    (2, 72, dict(kernel="tile")),                       # fom_tile_kernel across ranks (peer records, system-scope control)
+    (3, 96, dict(kernel="tile", newton_hint=1)),
 ])
 def test_slabs_match_oracle(lib, world, n_x, kw):
     n_y, steps, mu = 12, 3, [4.75, 0.02]

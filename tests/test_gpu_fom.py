@@ -133,3 +133,16 @@ def test_snapshot_cache_is_reference_compatible(h, tmp_path):
     assert np.array_equal(a[:, :4], b)
     on_disk = np.load(os.path.join(folder, "mu1_4.25+mu2_0.015.npy"))
     assert on_disk.shape == (2 * n * n, 5) and on_disk.flags.c_contiguous
+
+
+@pytest.mark.parametrize("n,steps,kw", [(64, 20, {}), (100, 7, dict(chunk_steps=2, newton_hint=1)), (250, 12, {})])
+def test_tile_kernel_equals_chunk_kernel(h, n, steps, kw):
+    """fom_tile_kernel (one warp per strip and time step, bfd_fom_desc.kernel = 1) against the default
+    fom_chunk_kernel: same Newton counts, same snapshots (the arithmetic differs only by exact
+    power-of-two rescalings); at most 4 solves are fused per pass, further ones are continuation passes."""
+    gx, gy = h.make_2D_grid(0, 100, 0, 100, n, n)
+    w0 = np.ones(2 * n * n)
+    a, ia = h.inviscid_burgers_implicit2D(gx, gy, w0, 0.05, steps, [5.19, 0.026], return_info=True, **kw)
+    b, ib = h.inviscid_burgers_implicit2D(gx, gy, w0, 0.05, steps, [5.19, 0.026], return_info=True, kernel="tile", **kw)
+    assert list(ia["newton_its"]) == list(ib["newton_its"])
+    assert rel_err(b, a) < 1e-14
