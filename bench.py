@@ -17,9 +17,7 @@ pinned host memory) inside the timed region.
 import argparse
 import json
 import os
-import subprocess
 import sys
-import threading
 import time
 
 import numpy as np
@@ -32,64 +30,29 @@ DT = 0.05
 NUM_STEPS = 500
 MU1_RANGE = (4.25, 5.5)
 MU2_RANGE = (0.015, 0.03)
-NCU_DRAM_BYTES_PER_CELL_UPDATE = 43.1     # ncu --set full, profiles/r01_fom_full_ncu.md
-FP64_INSTR_PER_CELL_UPDATE_K4 = 218       # DFMA/DMUL/DADD issued per cell-update with 4 Newton solves (ncu source page)
-FP64_PEAK_TFLOPS = 34.09                  # measured DFMA peak, profiles/r01_fp64_microbench.txt
 METRIC = "fom_cell_updates_per_s"
 UNIT = "cell-updates/s"
+# Constants read off one ncu capture of the sweep kernel (profiles/r02_fom_chunk_ncu.md).  They describe the
+# kernel SOURCE they were profiled on: the line carries `stale: true` when the sources' hash has moved on.
+NCU_PROFILED_SHA = "unset"                # sha256 of csrc/{fom.cu,wavefront.cuh,common.cuh} at profiling time, first 16 hex digits
+NCU_DRAM_BYTES_PER_CELL_UPDATE = 43.1     # dram__bytes_read.sum + dram__bytes_write.sum per cell-update
+NCU_FP64_INSTR_PER_CELL_UPDATE = 218.0    # smsp__inst_executed_pipe_fp64.sum per cell-update (warp instructions x 32 / cells), 4 solves
+CPU_SECONDS_PER_CELL_UPDATE = 65e-6       # one core, first time step (5 solves) at 750^2: 36.5 s / 562 500 cells (r01)
+
+
+def kernel_source_sha():
+    import hashlib
+    h = hashlib.sha256()
+    for f in ("fom.cu", "wavefront.cuh", "common.cuh"):
+        with open(os.path.join(ROOT, "finitedifference_b200", "csrc", f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
 
 
 def mu_lattice(count, rank=0, world=1):
     """`count` samples per rank (weak scaling) on a lattice of the training range, split contiguously."""
     from finitedifference_b200 import sharding
     return sharding.shard_mus(sharding.mu_lattice(count * world, MU1_RANGE, MU2_RANGE), rank, world)
-
-
-class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
-
-    def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
-
-    def __enter__(self):
-        try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
-            self.thread.start()
-        except OSError:
-            self.proc = None
-        return self
-
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
-
-    def __exit__(self, *exc):
-        if self.proc:
-            self.proc.terminate()
-            self.thread.join(timeout=2)
-
-    def summary(self):
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            try:
-                sm.append(float(r[0])); mx.append(float(r[1]))
-            except (ValueError, IndexError):
-                continue
-            for name, val in zip(names, r[3:7]):
-                if val.lower().startswith("active"):
-                    reasons.add(name)
-        if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        busy = sorted(sm)[len(sm) // 2:]          # upper half = samples under load
-        return {"sm_mhz": float(np.median(busy)), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
-                "samples": len(sm)}
 
 
 def algorithmic_bytes(its, cells):
@@ -100,43 +63,87 @@ def algorithmic_bytes(its, cells):
     return int((cells * (32 + 48 * (its - 1))).sum())
 
 
-def cpu_baseline(sample_steps=1, n=GRID_N):
-    """The oracle (a NumPy/SciPy port of the reference: sparse Jacobian + SuperLU) on the host."""
+def workload_config(n, T, B, extra=None):
+    cfg = {"workload": f"FOM parameter sweep, {n}x{n} grid, dt={DT}, {T} steps, {B} mu per GPU "
+                       f"(lattice over mu1 {MU1_RANGE} x mu2 {MU2_RANGE}), Newton rel tol 1e-12",
+           "grid": n, "num_steps": T, "mu_per_gpu": B}
+    cfg.update(extra or {})
+    return cfg
+
+
+# ---- the reference's CPU path (oracle port: sparse Jacobian + SuperLU, as the reference does) -------------
+def _cpu_band(job):
+    """One time step of one mu on a band of `rows` grid rows of the n-column fine grid (same dx, dy, dt)."""
+    n, rows, mu = job
+    for v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[v] = "1"
     from oracle import burgers_oracle as orc
-    gx, gy = orc.make_2D_grid(0, 100, 0, 100, n, n)
-    w0 = np.ones(2 * n * n)
+    gx, gy = orc.make_2D_grid(0, 100, 0, 100.0 * rows / n, n, rows)
     t0 = time.perf_counter()
-    _, hist = orc.fom_trajectory(gx, gy, w0, DT, sample_steps, [4.75, 0.02], return_info=True)
-    el = time.perf_counter() - t0
-    return {"value": n * n * sample_steps / el, "unit": UNIT, "cores": 1, "kind": "port",
-            "sample": f"first {sample_steps} time step(s) of one mu on the {n}x{n} grid, "
-                      f"{sum(len(h) for h in hist)} residual evaluations, {el:.1f} s "
-                      "(SuperLU spsolve is single-threaded)",
-            "seconds": el}
+    _, hist = orc.fom_trajectory(gx, gy, np.ones(2 * n * rows), DT, 1, mu, return_info=True)
+    return time.perf_counter() - t0, sum(len(h) for h in hist)
+
+
+def cpu_sample(n, rows, procs, pool=None):
+    """`procs` parameter samples advanced one time step concurrently, one process per host core (the sweep
+    is embarrassingly parallel over mu; SuperLU itself is single-threaded).  Returns the record."""
+    import multiprocessing as mp
+    mus = [[MU1_RANGE[0] + (MU1_RANGE[1] - MU1_RANGE[0]) * (i + 0.5) / procs, 0.02] for i in range(procs)]
+    own = pool is None
+    if own:
+        pool = mp.get_context("fork").Pool(procs)
+    try:
+        t0 = time.perf_counter()
+        res = pool.map(_cpu_band, [(n, rows, m) for m in mus], chunksize=1)
+        wall = time.perf_counter() - t0
+    finally:
+        if own:
+            pool.close()
+    evals = [r[1] for r in res]
+    return {"value": procs * n * rows / wall, "unit": UNIT, "cores": procs, "kind": "port", "seconds": wall,
+            "sample": f"first time step of {procs} mu in parallel (one process per core, {os.cpu_count()} logical CPUs) on a "
+                      f"{n} x {rows} band of the {n} x {n} grid (same dx, dy, dt), {min(evals)}-{max(evals)} residual "
+                      f"evaluations each, {wall:.1f} s wall; the reference's own path: sparse Jacobian + SuperLU spsolve",
+            "solves_per_step": float(np.mean(evals)) - 1.0}
+
+
+def cpu_rows(n, procs, seconds):
+    """Band height that takes about `seconds` per step with `procs` processes sharing the host's memory system."""
+    per_cell = CPU_SECONDS_PER_CELL_UPDATE * (1.0 + 0.04 * procs)
+    return int(max(8, min(n, seconds / (n * per_cell))))
+
+
+def host_cores():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
 
 
 def run_reference_arm(args, rank, world):
-    """--impl reference: the reference algorithm's CPU path (oracle port) on the host cores.
-    Each step is a bounded sample of the workload: one time step of one mu on the fine grid."""
+    """--impl reference: the reference algorithm's CPU path (oracle port) on all host cores.  A bench step is a
+    bounded sample of the workload, sized so that warm-up + timed steps end within ~150 s."""
     if rank != 0:
         return
-    times = []
-    n = args.grid
-    for i in range(args.warmup + args.steps):
-        b = cpu_baseline(sample_steps=1, n=n)
-        if i >= args.warmup:
-            times.append(b["seconds"])
-    total = sum(times)
-    value = n * n * len(times) / total
-    b["value"] = value
+    import multiprocessing as mp
+    n, procs = args.grid, host_cores()
+    total = args.warmup + args.steps
+    rows = cpu_rows(n, procs, 150.0 / max(total, 1))
+    pool = mp.get_context("fork").Pool(procs)
+    try:
+        recs = [cpu_sample(n, rows, procs, pool) for _ in range(total)][args.warmup:]
+    finally:
+        pool.close()
+    secs = sum(r["seconds"] for r in recs)
+    value = procs * n * rows * len(recs) / secs
+    b = dict(recs[-1], value=value)
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic",
-            "config": {"workload": f"FOM {n}x{n}, dt={DT}: one time step of one mu per bench step "
-                                   "(bounded sample of the 500-step sweep)", "grid": n,
-                       "cpu_count": os.cpu_count()},
-            "cpu_baseline": {k: b[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / len(recs),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(n, args.num_steps, args.mu_per_gpu, {
+                "sample": f"each bench step = one time step of {procs} mu on a {n} x {rows} band (bounded sample of the "
+                          f"{args.num_steps}-step sweep, normalised per cell-update)", "cpu_count": os.cpu_count()}),
+            "cpu_baseline": {k: b[k] for k in ("value", "unit", "cores", "kind", "sample", "solves_per_step")},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -158,6 +165,7 @@ def main():
     ap.add_argument("--e2e-group", type=int, default=2, help="samples a sweep worker advances together")
     ap.add_argument("--e2e-workers", type=int, default=3, help="sweep worker threads / streams")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-records", action="store_true", help="skip the LSPG / ECSW / training-matrix / slab sub-records")
     ap.add_argument("--kernel", default="chunk", choices=["chunk", "tile"],
                     help="FOM sweep kernel: fom_chunk_kernel (default) or fom_tile_kernel (warp per strip and time step)")
     args = ap.parse_args()
@@ -177,6 +185,8 @@ def main():
     import torch
     import torch.distributed as dist
     from finitedifference_b200 import _lib
+    from tools import records as R
+    ClockSampler = R.ClockSampler
     from finitedifference_b200.fom import FomSolver
     from finitedifference_b200.discretisation import make_2D_grid
 
@@ -231,33 +241,37 @@ def main():
     redone = solver.steps_redone
     value = world * B * cells * T * args.steps / (total_ms * 1e-3)
 
-    # roofline of the sweep kernel (the only kernel inside run()): algorithmic bytes / device time
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except OSError:
-        pass
-    peak = float(peaks.get("hbm_gbs", 6650.0))
+    # roofline of the sweep kernel (the only kernel inside run()).  Its binding unit is the FP64 pipe: the
+    # Newton sweeps of a step are fused in registers, so DRAM sees 43 B per cell-update instead of the
+    # 48 K + 32 B of one HBM pass per sweep (kept below as hbm_model, SURVEY 8d's accounting).
+    peaks = R.peaks()
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     abytes = algorithmic_bytes(its, cells)
-    achieved = abytes / (float(np.mean(run_ms)) * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+    run_s = float(np.mean(run_ms)) * 1e-3
+    hbm_achieved = abytes / run_s / 1e9
+    dfma_peak = R.dfma_peak_tflops(dev, lib)
+    dgemm_peak = R.dgemm_peak_tflops(dev)
+    solves = float(its.mean()) - 1.0
+    fp64_instr = NCU_FP64_INSTR_PER_CELL_UPDATE * (11.0 + 46.0 * solves + 17.0) / (11.0 + 46.0 * 4 + 17.0)   # scaled to this run's solves
+    fp64_tflops = 2e-12 * fp64_instr * (B * cells * T) / run_s
+    sha = kernel_source_sha()
+    stale = sha != NCU_PROFILED_SHA
+    roofline = {"bound": "fp64", "achieved": fp64_tflops, "peak": dfma_peak, "unit": "TFLOP/s", "frac": fp64_tflops / dfma_peak,
                 "traffic": NCU_DRAM_BYTES_PER_CELL_UPDATE * cells * T * B / max(sweeps, 1),
-                "kernel": "fom_chunk_kernel",
-                "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6.65 TB/s",
-                "algorithmic_bytes_per_step": abytes, "launches_per_step": sweeps,
-                "avg_launch_us": 1e3 * float(np.mean(run_ms)) / max(sweeps, 1),
-                "note": "algorithmic bytes = (48*solves + 32) B per cell-update (SURVEY 8d: one HBM pass per "
-                        "Newton sweep). The kernel fuses the sweeps of a time step in registers, so its real DRAM "
-                        "traffic is lower (traffic, from ncu) and the binding unit is the FP64 pipe (fp64)",
-                "traffic_source": "profiles/r01_fom_full_ncu.md: dram read+write = 43.1 B per cell-update "
-                                  "(ncu --set full of this command), scaled to this run's cell-updates per launch",
-                "fp64": {"instr_per_cell_update": FP64_INSTR_PER_CELL_UPDATE_K4,
-                         "achieved_tflops": 2e-12 * FP64_INSTR_PER_CELL_UPDATE_K4 * value / world,
-                         "peak_tflops": FP64_PEAK_TFLOPS, "frac": 2e-12 * FP64_INSTR_PER_CELL_UPDATE_K4 * value
-                         / world / FP64_PEAK_TFLOPS,
-                         "source": "profiles/r01_fp64_microbench.txt (DFMA peak measured on this pool) and the "
-                                   "SASS count of FP64 instructions per cell-update at 4 solves"},
-                "steps_redone": redone}
+                "kernel": "fom_chunk_kernel" if args.kernel == "chunk" else "fom_tile_kernel",
+                "peak_source": "bfd_probe_dfma in this run (DFMA issue rate, 8 chains x 32 warps per SM, best of 6)",
+                "achieved_source": f"{NCU_FP64_INSTR_PER_CELL_UPDATE} FP64 warp-instruction lanes per cell-update at 4 solves (ncu "
+                                   "smsp__inst_executed_pipe_fp64, profiles/r02_fom_chunk_ncu.md), scaled to this run's "
+                                   f"{solves:.3f} solves per step, x 2 flop, x cell-updates / device time of run()",
+                "traffic_source": f"{NCU_DRAM_BYTES_PER_CELL_UPDATE} B of DRAM traffic per cell-update (same capture), per launch",
+                "ncu_constants": {"profiled_sha": NCU_PROFILED_SHA, "current_sha": sha, "stale": stale},
+                "launches_per_step": sweeps, "avg_launch_us": 1e6 * run_s / max(sweeps, 1), "steps_redone": redone,
+                "dgemm_peak_tflops": dgemm_peak,
+                "hbm_model": {"bound": "hbm", "achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s",
+                              "frac": hbm_achieved / hbm_peak, "algorithmic_bytes_per_step": abytes,
+                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6.65 TB/s",
+                              "note": "(48*solves + 32) B per cell-update, one HBM pass per Newton sweep (SURVEY 8d); exceeds 1 "
+                                      "because the fused kernel does not make those passes"}}
 
     # end to end through the public sweep API: host w0 in, every (2N, T+1) snapshot array out to pinned
     # host memory (finitedifference_b200/sweep.py: groups of samples on worker streams, the copies of
@@ -286,7 +300,7 @@ def main():
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    e2e_reps = max(1, min(args.steps, 2))
+    e2e_reps = max(1, min(args.steps, 3))
     t0 = time.perf_counter()
     for _ in range(e2e_reps):
         seen.clear()
@@ -308,26 +322,39 @@ def main():
                   "(2N, T+1) trajectory copied to pinned host memory and handed to the sink"}
     del sweep
 
+    # ---- configs [3] and [4]: timed sub-records (tools/records.py), each with its own clocks ----------------
+    torch.cuda.empty_cache()
+    records = {}
+    if not args.no_records:
+        P = R.prepare(dev) if rank == 0 else None
+        if rank == 0:
+            records["setup"] = {k: P[k] for k in ("fom_ms", "pod_ms", "n_snapshots", "train_steps")}
+            records["lspg"] = R.lspg_record(P, dev, lib, gpu_index=local_rank)
+            records["training_matrix"], records["nnls"], weights = R.training_and_weights(P, dev, lib, gpu_index=local_rank)
+            records["ecsw"] = R.ecsw_record(P, dev, lib, weights, gpu_index=local_rank)
+        if world > 1:
+            records["lspg_sharded"] = R.lspg_sharded_record(P, dev, rank, world, dist, gpu_index=local_rank)
+        P = None
+        torch.cuda.empty_cache()
+        records["slab"] = R.slab_record(dev, rank, world, dist, gpu_index=local_rank)
+
     if rank == 0:
         cb = None
         if not args.no_cpu_baseline and world == 1:       # the CPU arm is timed at N = 1 only
-            cb = cpu_baseline(sample_steps=1, n=n)
-            cb = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            procs = host_cores()
+            cb = cpu_sample(n, cpu_rows(n, procs, 20.0), procs)
+            cb = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "solves_per_step")}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": f"FOM parameter sweep, {n}x{n} grid, dt={DT}, {T} steps, "
-                                       f"{B} mu per GPU (lattice over mu1 {MU1_RANGE} x mu2 {MU2_RANGE}), "
-                                       "Newton rel tol 1e-12",
-                           "grid": n, "num_steps": T, "mu_per_gpu": B, "chunk_steps": args.chunk_steps or 50,
-                           "strict": not args.non_strict,
-                           "l2": f"working set {B * per_mu / 2**30:.1f} GiB of snapshots per GPU, far larger than L2; "
-                                 "no flush needed", "newton_its_mean": float(its.mean()),
-                           "max_relnorm": float(rel.max())},
+                "config": workload_config(n, T, B, {
+                    "chunk_steps": args.chunk_steps or 50, "strict": not args.non_strict, "kernel": args.kernel,
+                    "l2": f"working set {B * per_mu / 2**30:.1f} GiB of snapshots per GPU, far larger than L2; no flush needed",
+                    "newton_its_mean": float(its.mean()), "max_relnorm": float(rel.max())}),
                 "mu_snapshots_per_s": world * B * T * args.steps / (total_ms * 1e-3),
                 "mu_trajectories_per_s": world * B * args.steps / (total_ms * 1e-3),
                 "roofline": roofline, "cpu_baseline": cb, "e2e": e2e, "gpu_launches": int(launches),
-                "clocks": clocks.summary(), "wall_s_timed": wall}
+                "clocks": clocks.summary(), "wall_s_timed": wall, "records": records}
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:

@@ -96,6 +96,7 @@ SIGNATURES = {
     "bfd_spd_solve": (C.c_int, [_P, _P, C.c_int, C.c_double, _P, _P]),
     "bfd_basis_times_y": (C.c_int, [_P, _P, C.c_int64, C.c_int, _P, _P]),
     "bfd_ecsw_c_block": (C.c_int, [C.c_int64, C.c_int, _P, _P, _P, C.c_size_t, _P]),
+    "bfd_probe_dfma": (C.c_int, [_P, C.c_int, C.c_int, _P]),
     "bfd_residual": (C.c_int, [C.c_int, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
 }
 

@@ -84,3 +84,28 @@ extern "C" int bfd_residual(int nx, int ny, const double *cx, const double *cxl,
     BFD_LAUNCHED();
     return BFD_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// FP64 pipe probe: the DFMA issue rate of THIS device, measured in the run that reports a fraction
+// of it (bench.py's roofline of the FOM sweep kernel, whose binding unit is the FP64 pipe).  Eight
+// independent chains per thread, 32 warps per SM.  The caller times the launch with events;
+// flop = 2 * 8 * iters * threads.  Measurement aid: no counterpart in the reference.
+// ------------------------------------------------------------------------------------------
+namespace bfd {
+__global__ void __launch_bounds__(1024) dfma_probe_kernel(double *sink, int iters, double a, double b) {
+    double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+#pragma unroll 4
+    for (int i = 0; i < iters; ++i) {
+        x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+        x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+    }
+    sink[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+}
+}  // namespace bfd
+
+extern "C" int bfd_probe_dfma(double *sink, int blocks, int iters, void *stream) {
+    if (!sink || blocks < 1 || iters < 1) return BFD_EINVAL;
+    BFD_LAUNCH(dfma_probe_kernel, BFD_GRID(blocks), 1024, 0, (cudaStream_t)stream, sink, iters, 0.999999, 1e-6);
+    BFD_LAUNCHED();
+    return BFD_OK;
+}

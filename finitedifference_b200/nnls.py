@@ -53,11 +53,19 @@ class _PassiveFactor:
         self._grow(int(j))
 
     def keep(self, mask):
-        """Drop the passive columns whose mask entry is False."""
-        kept = [j for j in self.idx if bool(mask[j])]
-        self.idx, self.L, self.ok = [], self.AtA.new_zeros((0, 0)), True
-        for j in kept:
-            self._grow(j)
+        """Drop the passive columns whose mask entry is False: one Cholesky of what is left."""
+        m = mask.cpu().numpy()                                # one copy, not one synchronisation per column
+        self.idx = [j for j in self.idx if m[j]]
+        self.ok = True
+        if not self.idx:
+            self.L = self.AtA.new_zeros((0, 0))
+            return
+        idx = torch.tensor(self.idx, dtype=torch.long, device=self.AtA.device)
+        G = self.AtA[idx][:, idx]
+        L, info = torch.linalg.cholesky_ex(G)
+        if int(info) != 0 or not bool((torch.diagonal(L) ** 2 > 1e-14 * torch.diagonal(G)).all()):
+            self.ok = False
+        self.L = L
 
 
 def nnls_tensor(A: torch.Tensor, b: torch.Tensor, maxiter: int | None = None):

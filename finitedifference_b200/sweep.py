@@ -30,6 +30,36 @@ from . import _lib
 from .fom import FomSolver, _require_cuda
 
 
+def _parse_cpulist(text):
+    cpus = set()
+    for part in text.strip().split(","):
+        lo, _, hi = part.partition("-")
+        if lo.strip().isdigit():
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def _topo_affinity(index):
+    """(cpus, numa node) of GPU `index` from NVML (what ``nvidia-smi topo -m`` prints as CPU / NUMA affinity);
+    (set(), None) when the driver does not know either."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(int(index))
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
+        try:
+            node = pynvml.nvmlDeviceGetNumaNodeId(h)
+        except Exception:                                  # noqa: BLE001 - older NVML
+            node = None
+        if len(cpus) >= (os.cpu_count() or 0):             # "all CPUs" carries no information
+            return set(), node
+        return cpus, (node if node is not None else -1)
+    except Exception:                                      # noqa: BLE001 - NVML missing or refusing: no binding
+        return set(), None
+
+
 def bind_host_to_gpu_node(device=None):
     """Restrict this process to the CPU cores of the NUMA node the GPU's PCIe root hangs off, so
     that pinned buffers (first touch) and the worker threads live next to the link they feed.
@@ -42,12 +72,16 @@ def bind_host_to_gpu_node(device=None):
         devid = torch.cuda.get_device_properties(dev).pci_device_id
         path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{devid:02x}.0/numa_node"
         node = int(open(path).read().strip())
-        if node < 0:
-            return None
         cpus = set()
-        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
-            lo, _, hi = part.partition("-")
-            cpus.update(range(int(lo), int(hi or lo) + 1))
+        if node < 0:
+            # virtual machines often report no node for the device: ask the driver for the GPU's CPU affinity
+            cpus, node = _topo_affinity(dev.index if dev.index is not None else torch.cuda.current_device())
+            if not cpus:
+                return None
+        else:
+            for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
         cpus &= os.sched_getaffinity(0)
         if not cpus:
             return None
@@ -163,8 +197,10 @@ class SnapshotSweep:
                         while len(stage) < len(idx):
                             stage.append(torch.empty((self.n2, self.num_steps + 1), dtype=torch.float64,
                                                      device=self.device))
+                        exported = torch.cuda.Event()
                         for j, i in enumerate(idx):
                             solver.snapshots_device(j, layout=1, out=stage[j])
+                            exported.record(stream)
                             pooled = out is None
                             if pooled:
                                 dst = self._get_pool().get()
@@ -174,6 +210,7 @@ class SnapshotSweep:
                                 # one device-to-host copy at a time per process: a single copy saturates the
                                 # PCIe link, concurrent ones only contend (on boxes where several GPUs share
                                 # the host's ingest bandwidth they make every rank slower)
+                                exported.synchronize()       # the export kernel is not part of what is serialised
                                 with self._copy_lock:
                                     dst.copy_(stage[j], non_blocking=True)
                                     stream.synchronize()

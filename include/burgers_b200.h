@@ -125,6 +125,11 @@ int bfd_residual(int nx, int ny, const double *cx, const double *cxl, const doub
                  const double *cyd, const double *src, const double *lbc, const double *w,
                  const double *wp, double *r, double *norm2, void *stream);
 
+/* DFMA issue-rate probe (measurement aid for bench.py's FP64 roofline; no counterpart in the reference):
+ * `blocks` CTAs of 1024 threads run 8 independent chains of `iters` DFMAs each and write one double per
+ * thread to sink[blocks * 1024].  flop = 2 * 8 * iters * blocks * 1024; the caller times the launch. */
+int bfd_probe_dfma(double *sink, int blocks, int iters, void *stream);
+
 /* ------------------------------------------------------------------------------------------
  * One grid over several GPUs: slab decomposition along x (second row).
  *

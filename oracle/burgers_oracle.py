@@ -417,6 +417,76 @@ def ecsw_trajectory(grid_x, grid_y, weights, w0, dt, num_steps, mu, basis, retur
     return out + (sample_inds, aug, history) if return_info else out
 
 
+def gauss_newton_manifold_ecsw(func, jac, y0, decode, decode_jac, weight, max_its=20, relnorm_cutoff=1e-5,
+                               min_delta=0.1):
+    """``gauss_newton_rnm_ecsw`` (hypernet2D.py:2167-2217): Gauss-Newton on reduced coordinates with a
+    nonlinear decoder; ``y`` is a float32 torch tensor as in the reference (:2214)."""
+    import torch
+    y = y0.detach().clone()
+    w = decode(y).numpy().astype(np.float64)
+    weights = np.concatenate((weight, weight))
+    init_norm = np.linalg.norm(func(w) * weights)
+    resnorms = []
+    for _ in range(max_its):
+        resnorm = np.linalg.norm(func(w) * weights)
+        resnorms.append(resnorm)
+        if resnorm / init_norm < relnorm_cutoff:
+            break
+        if len(resnorms) > 1 and abs((resnorms[-2] - resnorms[-1]) / resnorms[-2]) < min_delta:
+            break
+        J = jac(w)
+        V = decode_jac(y).numpy()
+        fw = func(w) * weights
+        JVw = sp.diags(weights) @ (J @ V)
+        dy = np.linalg.lstsq(JVw, -fw, rcond=None)[0]
+        y = y + torch.tensor(dy, dtype=torch.float)
+        w = decode(y).numpy().astype(np.float64)
+    return y, resnorms
+
+
+def manifold_ecsw_trajectory(grid_x, grid_y, w0, dt, num_steps, mu, net, basis, basis2, weights):
+    """``inviscid_burgers_rnm2D_ecsw`` (hypernet2D.py:556-674): neural-manifold HPROM on the sampled mesh,
+    state = basis @ y + basis2 @ net(cat(y, mu)), float32 decoder, float64 residual / Jacobian.
+    Returns ``(red_coords (q, T+1), per-step resnorm lists)``."""
+    import torch
+    weights = np.asarray(weights, dtype=np.float64)
+    n_cells = weights.size
+    sample_inds = np.where(weights != 0)[0]
+    aug = augmented_mesh(grid_x, grid_y, sample_inds)
+    jdx_s, jdy_s, eye2 = ecsw_operators(grid_x, grid_y, sample_inds, aug)
+    sample_weights = np.concatenate((weights, weights))[sample_inds]
+    tmu = torch.tensor(list(mu), dtype=torch.float)
+    B1 = torch.tensor(np.asarray(basis), dtype=torch.float)
+    B2 = torch.tensor(np.asarray(basis2), dtype=torch.float)
+    y0 = B1.T @ torch.tensor(np.asarray(w0).ravel(), dtype=torch.float)
+    idx = np.concatenate((aug, n_cells + aug))
+    V, Vbar = B1[idx, :], B2[idx, :]
+
+    def decode32(x):
+        return V @ x + Vbar @ net(torch.cat((x, tmu)))
+
+    def decode(x):
+        with torch.no_grad():
+            return decode32(x)
+
+    jacfwd = torch.func.jacfwd(decode32)
+    red = np.zeros((y0.shape[0], num_steps + 1))
+    red[:, 0] = y0.numpy()
+    yp = y0.clone()
+    wp = decode(y0).numpy().astype(np.float64)
+    history = []
+    for i in range(num_steps):
+        y, resnorms = gauss_newton_manifold_ecsw(
+            lambda x: residual_ecsw(x, grid_x, grid_y, dt, wp, mu, jdx_s, jdy_s, sample_inds, aug),
+            lambda x: jacobian_ecsw(x, dt, jdx_s, jdy_s, eye2, sample_inds, aug),
+            yp, decode, lambda x: jacfwd(x).detach(), sample_weights)
+        history.append(resnorms)
+        red[:, i + 1] = y.numpy()
+        wp = decode(y).numpy().astype(np.float64)
+        yp = y.clone()
+    return red, history
+
+
 def ecsw_training_matrix(snaps, prev_snaps, basis, grid_x, grid_y, dt, mu):
     """``compute_ECSW_training_matrix_2D`` (hypernet2D.py:2795-2816) with the exact Jacobian:
     ``C[i*k:(i+1)*k, cell] = r_u[cell]*(JV)_u[cell, :] + r_v[cell]*(JV)_v[cell, :]``."""

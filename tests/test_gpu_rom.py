@@ -197,3 +197,38 @@ def test_ecsw_batch_equals_single_runs(h, golden):
     for mu, red in zip(mus, batch):
         single, _ = h.inviscid_burgers_ecsw_fixed(gx, gy, g["weights"], w0, float(g["dt"]), steps, mu, basis)
         assert red.shape == single.shape and max(rel(red[:, i], single[:, i]) for i in range(steps + 1)) < 1e-12
+
+
+def test_manifold_hprom_golden(h, golden):
+    """inviscid_burgers_rnm2D_ecsw drop-in (decoder hook: ManifoldEcswSolver) against the reference's own
+    run with a seeded MLP decoder.  The reference keeps the decoder and y in float32, so the tolerance
+    here is float32 rounding through a few Gauss-Newton steps (1e-4), not the 1e-8 of the float64 HPROM."""
+    from tests.test_oracle_golden import manifold_net
+    g = golden("manifold_n24.npz")
+    n, steps = int(g["n"]), int(g["steps"])
+    gx, gy = h.make_2D_grid(0, 100, 0, 100, n, n)
+    red, times, info = h.inviscid_burgers_rnm2D_ecsw(gx, gy, np.ones(2 * n * n), float(g["dt"]), steps, list(g["mu"]),
+                                                     manifold_net(g), None, g["basis"], g["basis2"], g["weights"],
+                                                     return_info=True)
+    assert red.shape == g["red_coords"].shape and times[0] == int(g["num_its"])
+    assert info["gn_its"].tolist() == g["gn_its"].tolist()
+    assert max(rel(red[:, i], g["red_coords"][:, i]) for i in range(steps + 1)) < 1e-4
+
+
+def test_manifold_hook_with_linear_decoder_equals_ecsw(h, golden):
+    """The decoder hook with decode(y) = V_red y and a constant Jacobian is the linear HPROM: float64,
+    reduced states within 1e-8 of the reference's inviscid_burgers_ecsw_fixed golden, counts equal."""
+    import torch
+    from finitedifference_b200.rom import ManifoldEcswSolver
+    g = golden("ecsw_n24.npz")
+    n, steps = int(g["n"]), int(g["steps"])
+    gx, gy = h.make_2D_grid(0, 100, 0, 100, n, n)
+    solver = ManifoldEcswSolver(gx, gy, g["weights"], float(g["dt"]), list(g["mu"]))
+    V = torch.from_numpy(np.ascontiguousarray(g["basis"])).to(solver.device)
+    Vr = V[torch.from_numpy(solver.idx).to(solver.device)].contiguous()
+    y0 = V.T @ torch.ones(2 * n * n, dtype=torch.float64, device=solver.device)
+    red, _, info = h.inviscid_burgers_manifold_ecsw(gx, gy, g["weights"], y0, float(g["dt"]), steps, list(g["mu"]),
+                                                    lambda y: Vr @ y, lambda y: Vr, return_info=True)
+    assert info["gn_its"].tolist() == g["gn_its"].tolist()
+    assert np.array_equal(info["augmented_sample"], g["augmented_sample"])
+    assert max(rel(red[:, i], g["red_coords"][:, i]) for i in range(steps + 1)) < TOL

@@ -153,3 +153,24 @@ def test_lspg_k95_at_the_coarse_grid(golden):
     assert [len(h) for h in hist] == list(g["gn_its"][:steps])
     assert rel_l2_cols(red, g["red_coords"][:, :steps + 1]).max() < 1e-10
     assert rel_l2_cols(snaps[::int(g["stride"])], g["sample"][:, :steps + 1]).max() < 1e-10
+
+
+def manifold_net(g):
+    """The seeded decoder network of the fixture, rebuilt from the stored weights."""
+    import torch
+    q, nbar = g["basis"].shape[1], g["basis2"].shape[1]
+    net = torch.nn.Sequential(torch.nn.Linear(q + 2, 10), torch.nn.ELU(), torch.nn.Linear(10, nbar))
+    net.load_state_dict({k: torch.tensor(g["net_" + k.replace(".", "_")]) for k in net.state_dict()})
+    return net
+
+
+def test_manifold_hprom_trajectory(golden):
+    """inviscid_burgers_rnm2D_ecsw (:556-674) restated: float32 decoder as in the reference, so the
+    reduced coordinates agree to float32 rounding (1e-4 relative), Gauss-Newton counts equal."""
+    g = golden("manifold_n24.npz")
+    n, steps = int(g["n"]), int(g["steps"])
+    gx, gy = grid(n)
+    red, hist = orc.manifold_ecsw_trajectory(gx, gy, np.ones(2 * n * n), float(g["dt"]), steps, list(g["mu"]),
+                                             manifold_net(g), g["basis"], g["basis2"], g["weights"])
+    assert [len(h) for h in hist] == list(g["gn_its"])
+    assert rel_l2_cols(red, g["red_coords"]).max() < 1e-4
