@@ -23,6 +23,7 @@ from .discretisation import make_2D_grid  # noqa: F401  (re-exported, hypernet2D
 from .fom import FomSolver
 from .operators import (get_ops, inviscid_burgers_exact_jac2D, inviscid_burgers_exact_jac2D_ecsw,  # noqa: F401
                         inviscid_burgers_res2D, inviscid_burgers_res2D_alt, inviscid_burgers_res2D_ecsw, make_ddx)
+from .ecm import EmpiricalCubatureMethod, ecm_weights  # noqa: F401  (empirical_cubature_method.py:15, run_HPROM_ecm.py:83)
 from .nnls import ecsw_weights, nnls  # noqa: F401  (scipy.optimize.nnls at run_HPROM_ecsw_joshua.py:83)
 from .pod import POD  # noqa: F401  (hypernet2D.py:2746)
 from .rom import (EcswSolver, LspgSolver, ManifoldEcswSolver, ecsw_batch, ecsw_training_matrix,  # noqa: F401
@@ -35,7 +36,7 @@ __all__ = [
     "compute_ECSW_training_matrix_2D",
     "make_ddx", "get_ops", "inviscid_burgers_res2D", "inviscid_burgers_res2D_alt", "inviscid_burgers_res2D_ecsw",
     "inviscid_burgers_exact_jac2D", "inviscid_burgers_exact_jac2D_ecsw",
-    "POD", "nnls", "ecsw_weights", "load_or_compute_snaps", "compute_snaps_to_cache", "param_to_snap_fn", "get_saved_params", "compute_error",
+    "POD", "nnls", "ecsw_weights", "EmpiricalCubatureMethod", "ecm_weights", "load_or_compute_snaps", "compute_snaps_to_cache", "param_to_snap_fn", "get_saved_params", "compute_error",
 ]
 
 

@@ -15,6 +15,7 @@ Fixtures (all float64 / int64, ``np.savez_compressed``):
   lspg_n24.npz       POD basis, LSPG trajectory, per-step GN iteration counts
   ecsw_n24.npz       NNLS weights, sample/augmented index sets, HPROM reduced coordinates
   ecswC_n12.npz      ECSW training matrix
+  ecm_n24.npz        EmpiricalCubatureMethod selection (indices, weights) on a 24^2 training matrix
   manifold_n24.npz   neural-manifold HPROM (inviscid_burgers_rnm2D_ecsw) with a seeded MLP decoder
   fom_n250.npz, fom_n750.npz   (--large) per-snapshot norms + strided samples
 """
@@ -214,6 +215,32 @@ def gen_manifold(ref):
                         **{"net_" + k.replace(".", "_"): v.numpy() for k, v in net.state_dict().items()})
 
 
+def gen_ecm(ref):
+    """EmpiricalCubatureMethod (empirical_cubature_method.py:15-294) driven as run_HPROM_ecm.py:55-91 does, on
+    the 24^2 fixture: training matrix of the ECSW training parameter, interior cells, basis of C^T."""
+    from empirical_cubature_method import EmpiricalCubatureMethod          # the reference's, unmodified
+    g = np.load(os.path.join(OUT, "ecsw_n24.npz"))
+    n, steps, dt, mu = int(g["n"]), 12, float(g["dt"]), [4.25, 0.0225]
+    gx, gy, w0 = grid_and_w0(ref, n)
+    with quiet():
+        S = ref.inviscid_burgers_implicit2D(gx, gy, w0, dt, steps, mu)
+        C = ref.compute_ECSW_training_matrix_2D(S[:, 3:steps:2], S[:, 0:steps - 3:2], g["basis"],
+                                                ref.inviscid_burgers_res2D, ref.inviscid_burgers_exact_jac2D, gx, gy, dt, mu)
+    idxs = np.zeros((n, n)); idxs[1:-1, 1:-1] = 1
+    C = np.ascontiguousarray(C[:, (idxs == 1).ravel()])
+    u, sv, _ = np.linalg.svd(C.T, full_matrices=False)
+    u = np.ascontiguousarray(u[:, sv > 1e-8 * sv[0]])
+    sel = EmpiricalCubatureMethod()
+    with quiet():
+        sel.SetUp(u, InitialCandidatesSet=None, constrain_sum_of_weights=True, constrain_conditions=False)
+        sel.Run()
+    weights = np.zeros(C.shape[1])
+    weights[sel.z] = sel.w
+    np.savez_compressed(os.path.join(OUT, "ecm_n24.npz"), n=n, C=C, u=u, z=np.asarray(sel.z, dtype=np.int64),
+                        w=np.squeeze(sel.w), weights=weights, nerror=sel.nerror,
+                        residual=np.linalg.norm(C @ weights - C.sum(axis=1)) / np.linalg.norm(C.sum(axis=1)))
+
+
 def gen_large(ref, n, steps, mu, stride):
     gx, gy, w0 = grid_and_w0(ref, n)
     counts, restore = record_counts(ref, "newton_raphson")
@@ -238,6 +265,7 @@ def main():
     gen_lspg_ecsw(ref)
     gen_training_matrix(ref)
     gen_manifold(ref)
+    gen_ecm(ref)
     if args.large:
         gen_large(ref, 250, 3, [5.19, 0.026], 7)
         gen_large(ref, 750, 2, [4.75, 0.02], 61)
