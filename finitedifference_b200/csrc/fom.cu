@@ -1139,9 +1139,6 @@ static int fom_run_impl(const bfd_fom_desc *d, const SlabView &v, void *ws, cons
     bool finished = false;
     while (!finished && rc == BFD_OK) {
         a.launch_index = (int)launched;
-#ifdef BFD_EMULATE
-        if (getenv("BFD_EMU_DEBUG")) fprintf(stderr, "launch %lld: t %d kbase %d k_first %d k_spec %d gate %x\n", launched, a.ctl[0].t, a.ctl[0].kbase, a.ctl[0].k_first, a.ctl[0].k_spec, a.ctl[0].gate);
-#endif
         rc = launch_chunk(a, st);
         ++launched;
         if (rc != BFD_OK) break;

@@ -478,8 +478,7 @@ static int basis_times_y_rows(const double *V, const double *y, long long M, int
 extern "C" int bfd_basis_times_y(const double *V, const double *y, int64_t M, int k, double *w, void *stream) {
     if (!V || !y || !w || M < 1 || k < 1 || k > 96) return BFD_EINVAL;
     cudaStream_t st = (cudaStream_t)stream;
-    static const char *variant = getenv("BFD_VY_VARIANT");                  // tuning: "rows" = 8-byte loads per row
-    const long long nquads = (variant && variant[0] == 'r') || ((uintptr_t)V & 15) ? 0 : M / 4;
+    const long long nquads = ((uintptr_t)V & 15) ? 0 : M / 4;      // the ring kernel copies 16 bytes at a time
     if (nquads > 0) {
         long long blocks = (nquads + kVyWarps - 1) / kVyWarps;
         if (blocks > 148 * 5) blocks = 148 * 5;             // 89 registers, 36.9 KB of shared memory: 5 CTAs per SM

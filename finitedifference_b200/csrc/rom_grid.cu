@@ -189,157 +189,6 @@ __global__ void __launch_bounds__(128) rom_jv_grid_kernel(const JvGridArgs a) {
     }
 }
 
-// ------------------------------------------------------------------------------------------
-// OPT-IN variant (rows_per_warp = 9 or BFD_JV_RING=1; one grid row per warp, 64 < k <= 96): the
-// operands of a column step -- the basis rows, the state values and the coefficients -- reach the
-// warp through a private 3-stage shared-memory ring filled with cp.async, two steps ahead, so the
-// bytes in flight do not depend on the register allocator (what took bfd_basis_times_y from 3.6 to
-// 5.7 TB/s).  Same arithmetic in the same order as rom_jv_grid_kernel (bit-identical on the
-// emulator).  Not the default: it has been validated on the SIMT emulator only, not yet timed.
-// Stage layout (doubles): slot i at i*96; scalars at kSlots*96:
-//   slots  0: A(r-1).u  1: A(r).u  2: A(r-1).v  3: A(r).v ; :167 operator  4: P.u  5: P.v ;
-//          then L.u, L.v (left neighbour, first step of a segment only)
-//   scalars 0-3: w at A(r-1).u A(r).u A(r-1).v A(r).v  4-5: w at P  6-7: w at L  8-11: cx cxl cy cyd
-// ------------------------------------------------------------------------------------------
-constexpr int kRingStages = 3;
-
-template <bool TRANSPOSED>
-struct RingCfg {
-    static constexpr int kSlots = TRANSPOSED ? 8 : 6, kLeft = TRANSPOSED ? 6 : 4;
-    static constexpr int kWarps = TRANSPOSED ? 2 : 3;
-    static constexpr int kStageDoubles = kSlots * 96 + 16;
-};
-
-template <bool TRANSPOSED>
-__global__ void __launch_bounds__(32 * RingCfg<TRANSPOSED>::kWarps) rom_jv_ring_kernel(const JvGridArgs a) {
-    using Cfg = RingCfg<TRANSPOSED>;
-    BFD_SHARED_ARRAY(double, ring, [Cfg::kWarps][kRingStages][Cfg::kStageDoubles]);
-    const int nx = a.nx, k = a.k, r_hi = a.r_hi;
-    const size_t nP = a.nP, nA = TRANSPOSED ? a.nA : a.nP, n_out = a.n_out;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const double *V = a.V, *w = a.w;
-    const double *VA = TRANSPOSED ? a.VA : a.V, *wA = TRANSPOSED ? a.wA : a.w;
-    const saddr mine = smem_addr(&ring[warp][0][0]);
-    const long long ntasks = (long long)a.ngroups * a.nseg;
-    const long long warp0 = (long long)blockIdx.x * Cfg::kWarps + warp, nwarps = (long long)gridDim.x * Cfg::kWarps;
-
-    // copy one k-vector (a basis row) into a slot, or zero it
-    auto row_in = [&](saddr dst, const double *src, bool ok) {
-#pragma unroll
-        for (int m = 0; m < 3; ++m) {
-            const int j = lane + 32 * m;
-            if (j < k) { if (ok) cp_async8(dst + (saddr)(j * 8), src + j); else sts(dst + (saddr)(j * 8), 0.0); }
-        }
-    };
-    // fill stage `st` with the operands of column c of task `task`
-    auto issue = [&](long long task, int c, int st) {
-        if (task < ntasks) {
-            const int g = (int)(task / a.nseg), sg = (int)(task % a.nseg);
-            const int r = a.r_lo + g, c0 = sg * a.seg_len;
-            const saddr sb = mine + (saddr)(st * Cfg::kStageDoubles * 8);
-            const bool lo_ok = r - 1 >= 0;
-            const size_t cA1 = TRANSPOSED ? (size_t)c * a.a_len + (r - a.a_row0) : (size_t)(r - a.p_row0) * nx + c;
-            const size_t cA0 = !lo_ok ? 0 : TRANSPOSED ? cA1 - 1 : cA1 - nx;
-            const size_t cP = (size_t)(r - a.p_row0) * nx + c;
-            const size_t cell = (size_t)(r - a.r_lo) * nx + c;
-            const bool first = c == c0, left_ok = first && c0 > 0;
-            row_in(sb + 0 * 768, VA + cA0 * k, lo_ok);
-            row_in(sb + 1 * 768, VA + cA1 * k, true);
-            row_in(sb + 2 * 768, VA + (nA + cA0) * k, lo_ok);
-            row_in(sb + 3 * 768, VA + (nA + cA1) * k, true);
-            if (TRANSPOSED) {
-                row_in(sb + 4 * 768, V + cP * k, true);
-                row_in(sb + 5 * 768, V + (nP + cP) * k, true);
-            }
-            if (first) {
-                row_in(sb + (saddr)(Cfg::kLeft * 768), V + (cP - (left_ok ? 1 : 0)) * k, left_ok);
-                row_in(sb + (saddr)((Cfg::kLeft + 1) * 768), V + (nP + cP - (left_ok ? 1 : 0)) * k, left_ok);
-            }
-            const double *src = nullptr;
-            switch (lane) {
-            case 0: src = lo_ok ? wA + cA0 : nullptr; break;
-            case 1: src = wA + cA1; break;
-            case 2: src = lo_ok ? wA + nA + cA0 : nullptr; break;
-            case 3: src = wA + nA + cA1; break;
-            case 4: src = w + cP; break;
-            case 5: src = w + nP + cP; break;
-            case 6: src = left_ok ? w + cP - 1 : nullptr; break;
-            case 7: src = left_ok ? w + nP + cP - 1 : nullptr; break;
-            case 8: src = a.cx + cell; break;
-            case 9: src = c > 0 ? a.cxl + cell : nullptr; break;
-            case 10: src = a.cy + cell; break;
-            case 11: src = r > 0 ? a.cyd + cell : nullptr; break;
-            default: break;
-            }
-            if (lane < 12) {
-                const saddr dst = sb + (saddr)((Cfg::kSlots * 96 + lane) * 8);
-                if (src) cp_async8(dst, src); else sts(dst, 0.0);
-            }
-        }
-        cp_async_commit();
-    };
-    // step streams: (task, column) of the consumer and of the producer kRingStages-1 steps ahead
-    auto seg_begin = [&](long long task) { return (int)(task % a.nseg) * a.seg_len; };
-    auto seg_end = [&](long long task) { const int c0 = seg_begin(task); return c0 + a.seg_len < nx ? c0 + a.seg_len : nx; };
-    long long ptask = warp0;
-    int pc = ptask < ntasks ? seg_begin(ptask) : 0;
-    auto advance = [&](long long &task, int &c) {
-        if (task >= ntasks) return;
-        if (++c >= seg_end(task)) { task += nwarps; c = task < ntasks ? seg_begin(task) : 0; }
-    };
-    for (int s = 0; s < kRingStages - 1; ++s) { issue(ptask, pc, s); advance(ptask, pc); }
-    double Lu[3], Lv[3], wLu = 0.0, wLv = 0.0;
-    int it = 0;
-    for (long long task = warp0; task < ntasks; task += nwarps) {
-        const int g = (int)(task / a.nseg);
-        const int r = a.r_lo + g, c0 = seg_begin(task), c1 = seg_end(task);
-        for (int c = c0; c < c1; ++c, ++it) {
-            cp_async_wait_pending<kRingStages - 2>();
-            __syncwarp();
-            issue(ptask, pc, (it + kRingStages - 1) % kRingStages);
-            advance(ptask, pc);
-            const saddr sb = mine + (saddr)((it % kRingStages) * Cfg::kStageDoubles * 8);
-            const saddr sc = sb + (saddr)(Cfg::kSlots * 96 * 8);
-            const double wA0u = lds(sc + 0), wA1u = lds(sc + 8), wA0v = lds(sc + 16), wA1v = lds(sc + 24);
-            const double wPu = TRANSPOSED ? lds(sc + 32) : wA1u, wPv = TRANSPOSED ? lds(sc + 40) : wA1v;
-            if (c == c0) { wLu = lds(sc + 48); wLv = lds(sc + 56); }
-            const double cx = lds(sc + 64), cxl = lds(sc + 72), cy = lds(sc + 80), cyd = lds(sc + 88);
-            const size_t cell = (size_t)(r - a.r_lo) * nx + c;
-            const double pxu = cx * wPu, pxv = cx * wPv, lxu = cxl * wLu, lxv = cxl * wLv;
-            const double ayu = cy * wA1u, ayv = cy * wA1v, byu = cyd * wA0u, byv = cyd * wA0v;
-            double *ou = a.JV + cell * k, *ov = a.JV + (n_out + cell) * k;
-#pragma unroll
-            for (int m = 0; m < 3; ++m) {
-                const int j = lane + 32 * m;
-                const saddr col = (saddr)(j * 8);
-                const double vbu = lds(sb + 0 * 768 + col), vau = lds(sb + 1 * 768 + col);
-                const double vbv = lds(sb + 2 * 768 + col), vav = lds(sb + 3 * 768 + col);
-                const double vpu = TRANSPOSED ? lds(sb + 4 * 768 + col) : vau, vpv = TRANSPOSED ? lds(sb + 5 * 768 + col) : vav;
-                if (c == c0) { Lu[m] = lds(sb + (saddr)(Cfg::kLeft * 768) + col); Lv[m] = lds(sb + (saddr)((Cfg::kLeft + 1) * 768) + col); }
-                const double vlu = Lu[m], vlv = Lv[m];
-                const double ju = vpu + (pxu * vpu - lxu * vlu) + 0.5 * (ayv * vau - byv * vbu) + 0.5 * (ayu * vav - byu * vbv);
-                const double jv = vpv + 0.5 * (pxv * vpu - lxv * vlu) + (ayv * vav - byv * vbv) + 0.5 * (pxu * vpv - lxu * vlv);
-                if (j < k) { ou[j] = ju; ov[j] = jv; }
-                Lu[m] = vpu;
-                Lv[m] = vpv;
-            }
-            wLu = wPu;
-            wLv = wPv;
-        }
-    }
-    (void)r_hi;
-}
-
-template <bool T>
-static int launch_ring(const JvGridArgs &a, cudaStream_t st) {
-    const long long ntasks = (long long)a.ngroups * a.nseg;
-    long long blocks = (ntasks + RingCfg<T>::kWarps - 1) / RingCfg<T>::kWarps;
-    if (blocks > 148 * 5) blocks = 148 * 5;
-    BFD_LAUNCH((rom_jv_ring_kernel<T>), (int)BFD_GRID((int)blocks), 32 * RingCfg<T>::kWarps, 0, st, a);
-    BFD_LAUNCHED();
-    return BFD_OK;
-}
-
 template <int R, bool T>
 static int launch_mc(const JvGridArgs &a, int mc, dim3 grid, cudaStream_t st) {
     switch (mc) {
@@ -391,8 +240,7 @@ static int jv_grid_launch(const bfd_rom_mesh *m, int nx, int ny, int transposed,
     if (m->weight) return BFD_EINVAL;                       // weighted rows belong to the sampled mesh
     if (transposed && nx != ny) return BFD_EINVAL;          // :167 permutes a square grid
     const int R = rows_per_warp == 4 ? 4 : rows_per_warp == 2 ? 2 : 1;   // measured at 750^2, k = 95: 1 row per warp is fastest for both operators (0.34 / 0.44 ms), 4 rows slowest (registers)
-    int mc = k > 64 ? 3 : k > 32 ? 2 : 1;
-    if (const char *e = getenv("BFD_JV_MC")) { const int v = atoi(e); if (v >= 1 && v < mc) mc = v; }   // tuning
+    const int mc = k > 64 ? 3 : k > 32 ? 2 : 1;
     JvGridArgs a{};
     a.nx = nx; a.ny = ny; a.k = k;
     a.r_lo = r_lo; a.r_hi = r_hi;
@@ -409,18 +257,12 @@ static int jv_grid_launch(const bfd_rom_mesh *m, int nx, int ny, int transposed,
     // neighbour load from L2 per segment.
     a.seg_len = transposed ? 16 : 8;
     if (a.seg_len > nx) a.seg_len = nx;
-    if (const char *e = getenv("BFD_JV_SEG")) { const int v = atoi(e); if (v >= 1) a.seg_len = v < nx ? v : nx; }   // tuning
     a.nseg = (nx + a.seg_len - 1) / a.seg_len;
     a.cx = m->cx; a.cxl = m->cxl; a.cy = m->cy; a.cyd = m->cyd;
     a.w = w; a.V = V; a.rw = nullptr; a.JV = JV;
     const long long ntasks = (long long)a.ngroups * a.nseg;
     dim3 grid((unsigned)BFD_GRID((int)((ntasks + 3) / 4)), (unsigned)((k + 32 * mc - 1) / (32 * mc)));
     cudaStream_t st = (cudaStream_t)stream;
-    static const char *ring_env = getenv("BFD_JV_RING");
-    if ((rows_per_warp == 9 || (ring_env && ring_env[0] == '1')) && k > 64 && k <= 96) {       // opt-in cp.async ring
-        a.ngroups = r_hi - r_lo;
-        return transposed ? launch_ring<true>(a, st) : launch_ring<false>(a, st);
-    }
     if (R == 1) return transposed ? launch_mc<1, true>(a, mc, grid, st) : launch_mc<1, false>(a, mc, grid, st);
     if (R == 2) return transposed ? launch_mc<2, true>(a, mc, grid, st) : launch_mc<2, false>(a, mc, grid, st);
     return transposed ? launch_mc<4, true>(a, mc, grid, st) : launch_mc<4, false>(a, mc, grid, st);

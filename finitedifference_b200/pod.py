@@ -35,9 +35,18 @@ def _svd_flip_u(u, vt):
 
 
 def _lu_normalise(a):
-    """``scipy.linalg.lu(a, permute_l=True)[0]``: P @ L."""
-    p, l, _ = torch.linalg.lu(a)
-    return p @ l
+    """``scipy.linalg.lu(a, permute_l=True)[0]``: P @ L for a tall matrix, without ever forming the
+    m x m permutation matrix (at the fine grid m = 1 125 000: ``torch.linalg.lu`` would ask for 9.4 TB)."""
+    m, n = a.shape
+    LU, piv = torch.linalg.lu_factor(a)
+    L = torch.tril(LU[:, :n], diagonal=-1)
+    L.diagonal().fill_(1.0)
+    perm = np.arange(m)
+    for i, p in enumerate(piv.cpu().numpy() - 1):           # LAPACK's sequential row interchanges
+        perm[i], perm[p] = perm[p], perm[i]
+    out = torch.empty_like(L)
+    out[torch.from_numpy(perm).to(a.device)] = L            # row perm[i] of P L is row i of L
+    return out
 
 
 def pod_tensor(S: torch.Tensor, num_modes=None, method="svd", random_state=None, n_oversamples=10, n_iter="auto"):

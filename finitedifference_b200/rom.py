@@ -29,7 +29,7 @@ from .fom import _require_cuda
 
 GRAM_KERNEL_MIN_ROWS = 65536
 SPD_SOLVE_KERNEL = True      # False: cuSOLVER potrf + potrs through torch (comparison)
-JV_ROWS_PER_WARP = 0     # grid rows a warp of bfd_rom_jv_grid owns: 0 = library default, 1, 2 or 4 (tuning); 9 = cp.async ring variant
+JV_ROWS_PER_WARP = 0     # grid rows a warp of bfd_rom_jv_grid owns: 0 = library default, 1, 2 or 4 (tuning)
 
 
 def generate_augmented_mesh(grid_x, grid_y, sample_inds):
@@ -467,12 +467,13 @@ class EcswSolver(_RomBase):
         self.V_red = self.V[torch.from_numpy(self.idx).to(self.device)].contiguous()   # :245
         self.graph_kernel_launches = 0      # this library's kernels replayed inside CUDA graphs
 
-    def run(self, w0, num_steps, graphs=True):
+    def run(self, w0, num_steps, graphs=True, speculate=True):
         """Returns ``(red_coords_dev (T+1, k), per-step resnorm lists)``.
 
         ``graphs=True`` (default): a Gauss-Newton iteration is one CUDA-graph launch and one host
         look at ``||f||`` (the stopping rules stay on the host, in the reference's order);
-        ``graphs=False`` issues the same operations one by one."""
+        ``graphs=False`` issues the same operations one by one.  ``speculate`` (graphs only): the iterations
+        of a time step are launched back to back and judged afterwards, see ``_run_graphs``."""
         w0 = w0 if isinstance(w0, torch.Tensor) else self._dev(np.asarray(w0, dtype=np.float64).ravel())
         y = self.V.T @ w0                                   # :213
         red = torch.empty((num_steps + 1, self.V.shape[1]), dtype=torch.float64, device=self.device)
@@ -480,7 +481,7 @@ class EcswSolver(_RomBase):
         wp = self.V_red @ y                                 # == (basis @ y0)[idx]  (:214, :243)
         history = []
         if graphs and self.device.type == "cuda":
-            return self._run_graphs(y, wp, red, num_steps)
+            return self._run_graphs(y, wp, red, num_steps, speculate=speculate)
         for i in range(num_steps):
             y, w, resnorms = self.gauss_newton(self.mesh, self.mesh, self.V_red, y, wp)
             history.append(resnorms)
@@ -499,6 +500,11 @@ class EcswSolver(_RomBase):
         self._y, self._w, self._wp = torch.zeros(k, **f64), torch.zeros(n_state, **f64), torch.zeros(n_state, **f64)
         self._f, self._n2, self._JV = torch.zeros(n_rows, **f64), torch.zeros(1, **f64), torch.zeros((n_rows, k), **f64)
         self._h_n2 = torch.zeros(1, dtype=torch.float64).pin_memory()
+        # evaluation j of a time step leaves ||f||^2 in _norms[j] and the iterate it was taken at in _ys[j]:
+        # several iterations can then be launched back to back and judged afterwards (_run_graphs)
+        self._norms, self._ys = torch.zeros(self.MAX_ITS + 2, **f64), torch.zeros((self.MAX_ITS + 2, k), **f64)
+        self._it = torch.zeros(1, dtype=torch.long, device=dev)
+        self._h_norms = torch.zeros(self.MAX_ITS + 2, dtype=torch.float64).pin_memory()
         mesh, lib = self.mesh, self.lib
 
         def residual_part():
@@ -506,6 +512,9 @@ class EcswSolver(_RomBase):
             _lib.check(lib.bfd_rom_residual(C.byref(mesh.c), self._w.data_ptr(), self._wp.data_ptr(), self._f.data_ptr(),
                                             self._n2.data_ptr(), self._stream()), lib, "bfd_rom_residual")
             self._h_n2.copy_(self._n2, non_blocking=True)
+            self._norms.index_copy_(0, self._it, self._n2)
+            self._ys.index_copy_(0, self._it, self._y[None, :])
+            self._it.add_(1)
 
         def iteration():
             _lib.check(lib.bfd_rom_jv(C.byref(mesh.c), self._w.data_ptr(), V.data_ptr(), k, self._JV.data_ptr(),
@@ -526,11 +535,26 @@ class EcswSolver(_RomBase):
         torch.cuda.synchronize(dev)
         self._g_res, self._g_iter = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
         with torch.cuda.graph(self._g_res):
+            self._it.zero_()                                # evaluation 0 of a time step
             residual_part()
         with torch.cuda.graph(self._g_iter, pool=self._g_res.pool()):
             iteration()
 
-    def _run_graphs(self, y, wp, red, num_steps, max_its=20, relnorm_cutoff=1e-5, min_delta=0.1):
+    MAX_ITS = 20            # gauss_newton_ECSW_2D's max_its (:2008)
+
+    def _run_graphs(self, y, wp, red, num_steps, max_its=20, relnorm_cutoff=1e-5, min_delta=0.1, speculate=True,
+                    first_spec=2, adapt=True):
+        """Time stepping with the Gauss-Newton iterations replayed as CUDA graphs.  ``speculate``: the
+        iterations the previous time step needed are launched back to back after the first evaluation and
+        judged afterwards from the norms they left behind -- one host synchronisation per time step instead
+        of one per iteration; the stopping rules are applied to the same norms in the same order (:2022-2025),
+        and when they would have stopped earlier the iterate of that evaluation is restored."""
+        if max_its > self.MAX_ITS:
+            raise ValueError(f"max_its <= {self.MAX_ITS}")
+
+        def stop(r):
+            return r[-1] / r[0] < relnorm_cutoff or (len(r) > 1 and abs((r[-2] - r[-1]) / r[-2]) < min_delta)
+
         with torch.cuda.device(self.device):
             if not hasattr(self, "_g_iter"):
                 self._capture()
@@ -539,34 +563,48 @@ class EcswSolver(_RomBase):
             self._wp.copy_(wp)
             self._w.copy_(wp)                               # w of the first iterate: V_red @ y0 == wp
             history = []
+            spec = first_spec if speculate else 0           # updates launched before the first look
             for i in range(num_steps):
                 t0 = time.perf_counter()
                 self._g_res.replay()
-                stream.synchronize()
-                self.res_time += time.perf_counter() - t0
-                self.graph_kernel_launches += 1             # rom_residual_kernel
-                init_norm = float(np.sqrt(self._h_n2[0].item()))
-                _check_finite(init_norm, "EcswSolver")
-                resnorms = [init_norm]                      # resnorms[0] is the same evaluation as init_norm
-                for _ in range(max_its - 1):
-                    if resnorms[-1] / init_norm < relnorm_cutoff:
-                        break
-                    if len(resnorms) > 1 and abs((resnorms[-2] - resnorms[-1]) / resnorms[-2]) < min_delta:
-                        break
-                    t0 = time.perf_counter()
+                launched = min(spec, max_its - 1)
+                for _ in range(launched):
                     self._g_iter.replay()
-                    stream.synchronize()
-                    self.ls_time += time.perf_counter() - t0
-                    self.graph_kernel_launches += 2         # rom_jv_kernel, rom_residual_kernel
-                    resnorms.append(float(np.sqrt(self._h_n2[0].item())))
-                    _check_finite(resnorms[-1], "EcswSolver")
-                else:
-                    # max_its evaluations without a stop: the reference still takes its last step (:2024-2043)
-                    if not (resnorms[-1] / init_norm < relnorm_cutoff or
-                            abs((resnorms[-2] - resnorms[-1]) / resnorms[-2]) < min_delta):
+                self._h_norms.copy_(self._norms, non_blocking=True)
+                stream.synchronize()
+                self.ls_time += time.perf_counter() - t0
+                self.graph_kernel_launches += 1 + 2 * launched
+                norms = np.sqrt(self._h_norms.numpy()[:launched + 1].copy())
+                _check_finite(float(norms[0]), "EcswSolver")
+                resnorms, done = [float(norms[0])], None
+                for j in range(launched + 1):               # judge the evaluations in order
+                    if j > 0:
+                        resnorms.append(float(norms[j]))
+                        _check_finite(resnorms[-1], "EcswSolver")
+                    if stop(resnorms):
+                        done = j
+                        break
+                if done is not None and done < launched:    # over-speculated: back to the iterate of evaluation `done`
+                    self._y.copy_(self._ys[done])
+                    self.basis_times(self.V_red, self._y, out=self._w)
+                elif done is None:                          # more iterations, one look each (as without speculation)
+                    for _ in range(max_its - 1 - launched):
+                        t0 = time.perf_counter()
+                        self._g_iter.replay()
+                        stream.synchronize()
+                        self.ls_time += time.perf_counter() - t0
+                        self.graph_kernel_launches += 2
+                        resnorms.append(float(np.sqrt(self._h_n2[0].item())))
+                        _check_finite(resnorms[-1], "EcswSolver")
+                        if stop(resnorms):
+                            break
+                    else:
+                        # max_its evaluations without a stop: the reference still takes its last step (:2024-2043)
                         self._g_iter.replay()
                         stream.synchronize()
                 history.append(resnorms)
+                if speculate and adapt:                     # what this step needed is what the next one gets
+                    spec = max(1, min(len(resnorms) - 1, 6))
                 red[i + 1].copy_(self._y)
                 self._wp.copy_(self._w)                     # :271
         return red, history

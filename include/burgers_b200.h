@@ -215,8 +215,7 @@ int bfd_rom_jv(const bfd_rom_mesh *mesh, const double *w, const double *V, int k
 
 /* The same J V for a mesh that is the WHOLE nx x ny grid in row order (nrows == ncells == nx*ny,
  * p[i] == i, no weights), computed by walking the grid instead of gathering: left neighbours stay
- * in registers and a warp that owns `rows_per_warp` (1, 2 or 4; 0 = default; 9 = the opt-in variant
- * that stages a step's operands through a per-warp cp.async ring, 64 < k <= 96) grid rows shares the
+ * in registers and a warp that owns `rows_per_warp` (1, 2 or 4; 0 = default) grid rows shares the
  * y-difference cells between them, so the basis is read ~1.25x (exact operator) instead of 4x.
  * transposed = 0: the exact operator of get_ops (:2509-2520), ja = p, jb = yd;
  * transposed = 1: the operator inviscid_burgers_implicit2D_LSPG builds at :167 (nx == ny),

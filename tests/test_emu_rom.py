@@ -74,7 +74,7 @@ def test_grid_walk_jv_equals_gather_jv(lib, nx, ny, k):
     for name, transposed in modes:
         mesh = MeshTables(gx, gy, 0.05, [4.3, 0.021], CPU, jacobian=name)
         want = run_jv(lib, mesh, w, V)
-        for rows_per_warp in (0, 2, 4, 9):          # 9: the opt-in cp.async ring variant (64 < k <= 96)
+        for rows_per_warp in (0, 2, 4):
             got = run_jv_grid(lib, mesh, nx, ny, transposed, rows_per_warp, w, V)
             assert np.array_equal(got, want), (name, rows_per_warp, np.nanmax(np.abs(got - want)))
     mesh = MeshTables(gx, gy, 0.05, [4.3, 0.021], CPU)
@@ -265,16 +265,3 @@ def test_basis_times_y(lib, M, k):
     assert lib.bfd_basis_times_y(E.ptr(V), E.ptr(y), M, k, E.ptr(w), None) == 0
     assert np.allclose(w[:M], V @ y, rtol=1e-13, atol=1e-13) and np.isnan(w[M:]).all()
     assert lib.bfd_basis_times_y(E.ptr(V), E.ptr(y), M, 97, E.ptr(w), None) == -1
-
-
-def test_ring_variant_on_row_slabs():
-    """The opt-in cp.async ring variant of the J V walk with slab-local indexing: the slab tests again in
-    a process that selects it through BFD_JV_RING=1 (the slab entry point has no variant argument)."""
-    import os
-    import subprocess
-    import sys
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_emu_rom.py"), "-q", "-x", "-k",
-                        "row_slabs and not ring"], env=dict(os.environ, BFD_JV_RING="1"), capture_output=True, text=True,
-                       cwd=root, timeout=900)
-    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]

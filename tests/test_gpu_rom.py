@@ -144,6 +144,16 @@ def test_sharded_lspg_one_rank_equals_lspg(h, golden, mode):
         assert max(rel(full[:, i], g["snaps"][:, i]) for i in range(steps + 1)) < TOL
 
 
+def over_start(solver, w0, steps):
+    """(y, wp, red) as EcswSolver.run prepares them."""
+    import torch
+    w0d = solver._dev(np.asarray(w0, dtype=np.float64))
+    y = solver.V.T @ w0d
+    red = torch.empty((steps + 1, solver.V.shape[1]), dtype=torch.float64, device=solver.device)
+    red[0] = y
+    return y, solver.V_red @ y, red
+
+
 def test_ecsw_graph_iterations_equal_eager(h, golden):
     """Gauss-Newton iterations replayed as CUDA graphs against the same operations issued one by one."""
     from finitedifference_b200.rom import EcswSolver
@@ -160,6 +170,16 @@ def test_ecsw_graph_iterations_equal_eager(h, golden):
     a, _ = solver.run(w0, 3)
     b, _ = solver.run(w0, 3)                       # captured graphs are reused by a second trajectory
     assert np.array_equal(a.cpu().numpy(), b.cpu().numpy())
+    # iterations launched back to back and judged afterwards (default) against one look per iteration:
+    # the same norms, the same counts, the same iterates -- also when the speculated count is too high
+    # (forced here: six updates in flight where two are needed, so every step is rolled back)
+    red_1, hist_1 = EcswSolver(*args).run(w0, steps, speculate=False)
+    assert [len(x) for x in hist_1] == g["gn_its"].tolist()
+    assert np.array_equal(red_g.cpu().numpy(), red_1.cpu().numpy()) and hist_g == hist_1
+    over = EcswSolver(*args)
+    red_o, hist_o = over._run_graphs(*over_start(over, w0, steps), steps, speculate=True, first_spec=6, adapt=False)
+    assert [len(x) for x in hist_o] == g["gn_its"].tolist()
+    assert max(rel(red_o[i].cpu().numpy(), red_1[i].cpu().numpy()) for i in range(steps + 1)) < 1e-13
 
 
 @pytest.mark.parametrize("M,k", [(200000, 95), (12345, 96), (999, 7), (70001, 40)])

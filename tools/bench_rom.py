@@ -94,9 +94,6 @@ def main():
         for rows in (1, 2, 4):
             rom_mod.JV_ROWS_PER_WARP = rows
             _, variants[f"{mode}_grid_rows{rows}_ms"] = timed(lambda: lspg.jv(mesh, w, V), 5)
-        rom_mod.JV_ROWS_PER_WARP = 9            # opt-in cp.async ring variant (validated on the emulator only so far)
-        _, variants[f"{mode}_ring_ms"] = timed(lambda: lspg.jv(mesh, w, V), 5)
-        variants[f"{mode}_ring_max_abs_diff"] = float((lspg.jv(mesh, w, V) - lspg.jv(mesh, w, V, gather=True)).abs().max())
         rom_mod.JV_ROWS_PER_WARP = 0
     JV = lspg.jv(lspg.jac_mesh, w, V)
     _, gram_ms = timed(lambda: JV.T @ JV, 5)

@@ -249,7 +249,7 @@ def ecsw_record(P, dev, lib, weights, steps=100, gpu_index=0):
             "clocks": clk.summary()}
 
 
-def slab_record(dev, rank, world, dist, grid=8192, T=20, dx=100.0 / 750.0, check=512, gpu_index=0):
+def slab_record(dev, rank, world, dist, grid=8192, T=20, dx=100.0 / 750.0, check=512, gpu_index=0, kernel="chunk"):
     """BASELINE.json config [4]: one `grid`^2 FOM trajectory over `world` GPUs by slab decomposition
     (peer stores over NVLink inside the sweep kernel, finitedifference_b200/slab.py).  Strong scaling;
     time = max over ranks of the device time of run().  With `check`, a smaller grid is first compared
@@ -263,7 +263,7 @@ def slab_record(dev, rank, world, dist, grid=8192, T=20, dx=100.0 / 750.0, check
 
     def make(n, steps):
         gx, gy = make_2D_grid(0, n * dx, 0, n * dx, n, n)
-        s = FomSlab(gx, gy, DT, steps, [TEST_MU], rank, world, device=dev)
+        s = FomSlab(gx, gy, DT, steps, [TEST_MU], rank, world, device=dev, kernel=kernel)
         connect_distributed(s) if world > 1 else s.connect()
         return gx, gy, s
 
@@ -284,7 +284,7 @@ def slab_record(dev, rank, world, dist, grid=8192, T=20, dx=100.0 / 750.0, check
         gx, gy, s = make(check, 6)
         trajectory(s)
         mine = s.snapshots_device(0)
-        solo = FomSolver(gx, gy, DT, 6, [TEST_MU], device=dev)
+        solo = FomSolver(gx, gy, DT, 6, [TEST_MU], device=dev, kernel=kernel)
         solo.set_initial(torch.ones(2 * check * check, dtype=torch.float64, device=dev))
         solo.run()
         whole = solo.snapshots_device(0, layout=0).reshape(7, 2, check, check)[:, :, :, s.c0:s.c1]
@@ -301,7 +301,7 @@ def slab_record(dev, rank, world, dist, grid=8192, T=20, dx=100.0 / 750.0, check
     with ClockSampler(gpu_index, 100) as clk:
         ms = float(np.mean([trajectory(s) for _ in range(2)]))
     its, rel = s.diagnostics()
-    rec = {"grid": grid, "num_steps": T, "n_gpus": world, "scaling": "strong", "ms_per_trajectory": ms,
+    rec = {"grid": grid, "num_steps": T, "n_gpus": world, "scaling": "strong", "kernel": kernel, "ms_per_trajectory": ms,
            "cell_updates_per_s": grid * grid * T / (ms * 1e-3), "newton_its_mean": float(its.mean()),
            "max_relnorm": float(rel.max()), "steps_redone": int(s.steps_redone), "dx": dx,
            "bit_exact_vs_single_gpu": exact, "check_grid": check,
