@@ -175,7 +175,8 @@ def test_ecsw_graph_iterations_equal_eager(h, golden):
     # (forced here: six updates in flight where two are needed, so every step is rolled back)
     red_1, hist_1 = EcswSolver(*args).run(w0, steps, speculate=False)
     assert [len(x) for x in hist_1] == g["gn_its"].tolist()
-    assert np.array_equal(red_g.cpu().numpy(), red_1.cpu().numpy()) and hist_g == hist_1
+    assert np.array_equal(red_g.cpu().numpy(), red_1.cpu().numpy())
+    assert all(np.allclose(a, b, rtol=1e-13, atol=0) for a, b in zip(hist_g, hist_1))      # ||f||^2 is summed with atomics
     over = EcswSolver(*args)
     red_o, hist_o = over._run_graphs(*over_start(over, w0, steps), steps, speculate=True, first_spec=6, adapt=False)
     assert [len(x) for x in hist_o] == g["gn_its"].tolist()
