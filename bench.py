@@ -337,6 +337,9 @@ def main():
         P = None
         torch.cuda.empty_cache()
         records["slab"] = R.slab_record(dev, rank, world, dist, gpu_index=local_rank)
+        # the same grid over 60 steps: the first ~20 steps of a trajectory from w0 = 1 need up to 10 Newton solves and
+        # pay for mis-speculated counts; steps 21-60 show the steady rate
+        records["slab_T60"] = R.slab_record(dev, rank, world, dist, T=60, check=0, gpu_index=local_rank)
 
     if rank == 0:
         cb = None

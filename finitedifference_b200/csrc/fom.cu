@@ -534,13 +534,13 @@ __device__ __forceinline__ void dma_part(const StepIo &io) {
         // wait for a global-memory round trip in every step.
         const int rw = kStartRow < ny ? kStartRow : ny - 1;
         const double *gw = io.edge_in + (size_t)rw * kRecDoubles + 2 * ((NPR - 1) & ~1);   // last Newton level: written last
-        unsigned spins = 0;
+        SpinClock spins;
         for (;;) {
             double a = 0.0, b = 0.0;
             if (lane == 0) { if (in_remote) ld_sys2(gw, a, b); else ld_volatile2(gw, a, b); }
             if (__all_sync(0xffffffffu, !(is_sentinel(a) || is_sentinel(b)))) break;
             ++spins_total;
-            if (++spins > kSpinLimit) { err = BFD_ETIMEOUT; break; }
+            if (spins.expired()) { err = BFD_ETIMEOUT; break; }
             spin_pause();
         }
         if (take) {
@@ -555,12 +555,12 @@ __device__ __forceinline__ void dma_part(const StepIo &io) {
         if (take && (unsigned)rc < (unsigned)ny) {
             if (is_sentinel_hi(va) || is_sentinel_hi(vb)) {          // had not arrived when the row was copied
                 ++misses;
-                unsigned spins = 0;
+                SpinClock spins;
                 for (;;) {
                     if (in_remote) ld_sys2(gin, va, vb); else ld_volatile2(gin, va, vb);
                     if (!(is_sentinel(va) || is_sentinel(vb))) break;
                     ++spins_total;
-                    if (++spins > kSpinLimit) { err = BFD_ETIMEOUT; va = 0.0; vb = 0.0; break; }
+                    if (spins.expired()) { err = BFD_ETIMEOUT; va = 0.0; vb = 0.0; break; }
                     if (spins > 2) spin_pause();
                 }
             }
@@ -825,11 +825,11 @@ __global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk
     if (SLAB) {
         if (threadIdx.x == 0 && a.launch_index > 0) {
             const unsigned need = (unsigned)a.launch_index * (unsigned)nsg;
-            unsigned spins = 0;
+            SpinClock spins;
             while (*(volatile unsigned *)&ctl->exits < need && *(volatile int *)&ctl->t < a.num_steps &&
                    *(volatile int *)&a.glob->error == 0) {
                 spin_pause();
-                if (++spins > kSpinLimit) { atomicExch(&a.glob->error, BFD_ETIMEOUT); break; }
+                if (spins.expired()) { atomicExch(&a.glob->error, BFD_ETIMEOUT); break; }
             }
             fence<SLAB>();
         }
@@ -944,10 +944,10 @@ __global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk
                 fence<SLAB>();
                 a_add<SLAB>(&ctl->epoch, 1u);
             } else if (refused) {
-                unsigned spins = 0;
+                SpinClock spins;
                 while (*(volatile unsigned *)&ctl->epoch == epoch0) {
                     spin_pause();
-                    if (++spins > kSpinLimit) { atomicExch(&a.glob->error, BFD_ETIMEOUT); break; }
+                    if (spins.expired()) { atomicExch(&a.glob->error, BFD_ETIMEOUT); break; }
                 }
                 fence<SLAB>();
             }

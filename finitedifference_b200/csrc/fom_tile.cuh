@@ -152,13 +152,13 @@ __device__ __forceinline__ void tile_step(const TileIo &io) {
         // start distance: not before the strip on the left is kStartRow rows into this time step
         const int rw = kTStartRow < ny ? kTStartRow : ny - 1;
         const double *gw = io.edge_in + (size_t)rw * kRecDoubles + 2 * ((NPR - 1) & ~1);
-        unsigned spins = 0;
+        SpinClock spins;
         const unsigned long long tw0 = global_timer_ns();
         for (;;) {
             double a = 0.0, b = 0.0;
             if (lane == 0) { if (in_remote) ld_sys2(gw, a, b); else ld_volatile2(gw, a, b); }
             if (__all_sync(0xffffffffu, !(is_sentinel(a) || is_sentinel(b)))) break;
-            if (++spins > kSpinLimit) { err = BFD_ETIMEOUT; break; }
+            if (spins.expired()) { err = BFD_ETIMEOUT; break; }
             start_pause();                                   // a waiting warp must not eat the issue slots of the running ones
         }
         if (lane == 0) *io.wait_ns = global_timer_ns() - tw0;
@@ -176,11 +176,11 @@ __device__ __forceinline__ void tile_step(const TileIo &io) {
         if (take && (unsigned)(rc + 1) < (unsigned)ny) lds2(ering_row(rc + 1), na, nb);
         if (take && (unsigned)rc < (unsigned)ny) {
             if (is_sentinel_hi(va) || is_sentinel_hi(vb)) {          // had not arrived when the row was copied
-                unsigned spins = 0;
+                SpinClock spins;
                 for (;;) {
                     if (in_remote) ld_sys2(gin, va, vb); else ld_volatile2(gin, va, vb);
                     if (!(is_sentinel(va) || is_sentinel(vb))) break;
-                    if (++spins > kSpinLimit) { err = BFD_ETIMEOUT; va = 0.0; vb = 0.0; break; }
+                    if (spins.expired()) { err = BFD_ETIMEOUT; va = 0.0; vb = 0.0; break; }
                     if (spins > 2) spin_pause();
                 }
             }
@@ -211,10 +211,10 @@ __device__ __forceinline__ void tile_step(const TileIo &io) {
             if (gated) {
                 const int need = in_base + pf_row + 1;
                 if (need > prod_seen) {
-                    unsigned spins = 0;
+                    SpinClock spins;
                     while ((prod_seen = ld_shared_volatile(io.prod_in)) < need) {
                         BFD_TRACE_SPIN(spins, "wait prod: strip %d in_base %d row %d need %d seen %d\n", io.strip, in_base, pf_row, need, prod_seen);
-                        if (++spins > kSpinLimit) { err = BFD_ETIMEOUT; break; }
+                        if (spins.expired()) { err = BFD_ETIMEOUT; break; }
                     }
                     __threadfence_block();
                 }
@@ -413,11 +413,11 @@ __global__ void __launch_bounds__(32 * kTileDepth, 4) fom_tile_kernel(const FomA
     if (SLAB) {
         if (threadIdx.x == 0 && a.launch_index > 0) {
             const unsigned need = (unsigned)a.launch_index * (unsigned)nsg;
-            unsigned spins = 0;
+            SpinClock spins;
             while (*(volatile unsigned *)&ctl->exits < need && *(volatile int *)&ctl->t < a.num_steps &&
                    *(volatile int *)&a.glob->error == 0) {
                 spin_pause();
-                if (++spins > kSpinLimit) { atomicExch(&a.glob->error, BFD_ETIMEOUT); break; }
+                if (spins.expired()) { atomicExch(&a.glob->error, BFD_ETIMEOUT); break; }
             }
             fence<SLAB>();
         }
@@ -540,11 +540,11 @@ __global__ void __launch_bounds__(32 * kTileDepth, 4) fom_tile_kernel(const FomA
                 fence<SLAB>();
                 a_add<SLAB>(&ctl->epoch, 1u);
             } else if (was_refused) {
-                unsigned spins = 0;
+                SpinClock spins;
                 while (*(volatile unsigned *)&ctl->epoch == epoch0) {
                     spin_pause();
                     BFD_TRACE_SPIN(spins, "wait epoch: strip %d attempt %d\n", jg, attempt);
-                    if (++spins > kSpinLimit) { atomicExch(&a.glob->error, BFD_ETIMEOUT); break; }
+                    if (spins.expired()) { atomicExch(&a.glob->error, BFD_ETIMEOUT); break; }
                 }
                 fence<SLAB>();
             }

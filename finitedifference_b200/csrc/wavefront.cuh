@@ -131,7 +131,29 @@ constexpr int kEdgeBlock = 8;
 constexpr int kPiecesMax = 2 * BFD_FOM_KMAX + 2;   // pieces per row in global memory (fixed pitch)
 constexpr int kRecDoubles = 2 * kPiecesMax;        // doubles per row record
 constexpr int kInRing = 32;                        // rows in the consumer's ring
-constexpr unsigned kSpinLimit = 1u << 22;
+constexpr unsigned kSpinLimit = 1u << 22;                       // emulator: iterations
+constexpr unsigned long long kSpinTimeoutNs = 20000000000ull;   // device: 20 s of %globaltimer
+
+// Deadline of a device-side wait.  A wait gives up (BFD_ETIMEOUT) after kSpinTimeoutNs of wall time, not
+// after a number of iterations: how long an iteration takes depends on where the polled word lives (L2,
+// a peer GPU over NVLink) and on what else runs on the SM, and in multi-process slab runs the neighbour's
+// kernel is launched by another process (launch skew of seconds is possible on a busy host).  The timer
+// is read every 1024 iterations only.
+struct SpinClock {
+    unsigned n = 0;
+    unsigned long long t0 = 0;
+    __device__ __forceinline__ bool expired() {
+#ifdef BFD_EMULATE
+        return ++n > kSpinLimit;
+#else
+        if ((++n & 1023u) != 0) return false;
+        const unsigned long long t = global_timer_ns();
+        if (t0 == 0) { t0 = t; return false; }
+        return t - t0 > kSpinTimeoutNs;
+#endif
+    }
+    __device__ __forceinline__ operator unsigned() const { return n; }
+};
 
 constexpr int kRecBytes = kRecDoubles * 8;
 

@@ -112,14 +112,15 @@ def inviscid_burgers_res2D_alt(w, grid_x, grid_y, dt, wp, mu, JDxec=None, JDyec=
 def inviscid_burgers_res2D_ecsw(w, grid_x, grid_y, dt, wp, mu, JDxec, JDyec, sample_inds, augmented_sample,
                                 lbc=None, src=None, *, device=None):
     """Residual rows at the sampled cells, ``(2 n_s,)`` (:2648-2701).  ``w``/``wp`` are either the
-    full state or its restriction ``w[[aug, N + aug]]``, as in the reference."""
+    full state or its restriction ``w[[aug, N + aug]]``, as in the reference; ``lbc`` / ``src`` (one value
+    per sampled cell) replace the terms derived from the grids when given."""
     device = _require_cuda(device)
     s = np.asarray(sample_inds, dtype=np.int64)
     a = np.asarray(augmented_sample, dtype=np.int64)
     key = ("ecsw", device.index, float(dt), float(mu[0]), float(mu[1])) + _digest(grid_x, grid_y, s, a)
     mesh = _cached(key, lambda: MeshTables(grid_x, grid_y, dt, list(mu)[:2], device, rows=s, state_cells=a))
-    if lbc is not None or src is not None:
-        raise NotImplementedError("precomputed lbc/src are not taken: they are derived from the grids")
+    if lbc is not None or src is not None:                                     # precomputed terms (:2658-2669), as the
+        mesh = mesh.with_terms(src=src, lbc=lbc)                               # manifold drivers pass them (:652, :856, :1081)
     idx = np.concatenate((a, (np.asarray(grid_x).size - 1) * (np.asarray(grid_y).size - 1) + a))
     w, wp = _host(w), _host(wp)
     w = w[idx] if w.size > 2 * a.size else w                                   # :2672

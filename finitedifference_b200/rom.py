@@ -116,6 +116,23 @@ class MeshTables:
 
     grid = None          # (nx, ny, transposed) when the rows are the whole grid in row order
 
+    def with_terms(self, src=None, lbc=None):
+        """The same mesh with caller-supplied per-row source / inlet terms (the reference's manifold drivers pass
+        precomputed ``lbc`` and ``src`` to ``inviscid_burgers_res2D_ecsw``, hypernet2D.py:652, :856, :1081):
+        index and coefficient tables are shared, only the two term arrays are uploaded."""
+        other = MeshTables.__new__(MeshTables)
+        other.nrows, other.ncells, other.device, other.grid = self.nrows, self.ncells, self.device, self.grid
+        other._t = list(self._t)
+        for slot, a in ((9, src), (10, lbc)):
+            if a is not None:
+                a = np.ascontiguousarray(np.asarray(a, dtype=np.float64).ravel())
+                if a.size != self.nrows:
+                    raise ValueError(f"expected {self.nrows} per-row terms, got {a.size}")
+                other._t[slot] = torch.from_numpy(a).to(self.device)
+        wptr = other._t[11].data_ptr() if len(other._t) > 11 else None
+        other.c = _lib.RomMesh(other.nrows, other.ncells, *[x.data_ptr() for x in other._t[:11]], wptr)
+        return other
+
     def _upload(self, t, ncells, device, weight):
         self.nrows, self.ncells, self.device = int(np.asarray(t["p"]).size), int(ncells), device
         i32 = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.int32)).to(device)

@@ -41,6 +41,16 @@ def test_sampled_residual_and_jacobian_golden(h, golden):
     full = h.inviscid_burgers_res2D_ecsw(w, gx, gy, dt, wp, mu, jdx_s, jdy_s, sample, aug)
     red = h.inviscid_burgers_res2D_ecsw(w[idx], gx, gy, dt, wp[idx], mu, jdx_s, jdy_s, sample, aug)
     assert np.max(np.abs(full - g["r_full"])) < 1e-14 and np.max(np.abs(red - g["r_red"])) < 1e-14
+    # precomputed inlet / source terms, as the manifold drivers pass them (hypernet2D.py:630-652): the reference's
+    # own formulas give the same residual; other values shift it by exactly their difference
+    dx, xc = gx[1:] - gx[:-1], (gx[1:] + gx[:-1]) / 2
+    lbc = np.where(sample % n == 0, 0.5 * dt * mu[0] ** 2 / dx[0], 0.0)
+    src = np.tile(dt * 0.02 * np.exp(mu[1] * xc), n)[sample]
+    same = h.inviscid_burgers_res2D_ecsw(w[idx], gx, gy, dt, wp[idx], mu, jdx_s, jdy_s, sample, aug, lbc, src)
+    assert np.max(np.abs(same - g["r_red"])) < 1e-14
+    other = h.inviscid_burgers_res2D_ecsw(w[idx], gx, gy, dt, wp[idx], mu, jdx_s, jdy_s, sample, aug, lbc + 0.25, 2 * src)
+    assert np.max(np.abs(other[:sample.size] - (g["r_red"][:sample.size] - 0.25 - src))) < 1e-13
+    assert np.max(np.abs(other[sample.size:] - g["r_red"][sample.size:])) < 1e-14
     for state in (w, w[idx]):
         J = h.inviscid_burgers_exact_jac2D_ecsw(state, dt, jdx_s, jdy_s, eye2, sample, aug)
         assert J.shape == g["J_red"].shape and np.max(np.abs(J.toarray() - g["J_red"])) < 1e-14

@@ -373,6 +373,7 @@ def main():
     P = None
     torch.cuda.empty_cache()
     out["slab"] = slab_record(dev, rank, world, dist, gpu_index=local)
+    out["slab_T60"] = slab_record(dev, rank, world, dist, T=60, check=0, gpu_index=local)
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:
