@@ -555,12 +555,12 @@ __device__ __forceinline__ void dma_part(const StepIo &io) {
         if (take && (unsigned)rc < (unsigned)ny) {
             if (is_sentinel_hi(va) || is_sentinel_hi(vb)) {          // had not arrived when the row was copied
                 ++misses;
-                SpinClock spins;
+                unsigned spins = 0;                  // inside the per-step loop: a plain counter (the producer is running)
                 for (;;) {
                     if (in_remote) ld_sys2(gin, va, vb); else ld_volatile2(gin, va, vb);
                     if (!(is_sentinel(va) || is_sentinel(vb))) break;
                     ++spins_total;
-                    if (spins.expired()) { err = BFD_ETIMEOUT; va = 0.0; vb = 0.0; break; }
+                    if (++spins > kSpinLimit) { err = BFD_ETIMEOUT; va = 0.0; vb = 0.0; break; }
                     if (spins > 2) spin_pause();
                 }
             }
