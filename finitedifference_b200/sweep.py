@@ -117,10 +117,10 @@ class SnapshotSweep:
         self.n2 = 2 * (self.grid_x.size - 1) * (self.grid_y.size - 1)
         self._pool = None
         self._pool_lock = threading.Lock()
-        self._copy_lock = threading.Lock()
         self._solvers = {}        # (worker, batch) -> FomSolver
         self._stage = {}          # worker -> list of device staging tensors
         self._streams = [torch.cuda.Stream(device=self.device) for _ in range(self.workers)]
+        self._copy_stream = torch.cuda.Stream(device=self.device)
         self.launches = 0
         self.steps_redone = 0
 
@@ -177,6 +177,52 @@ class SnapshotSweep:
         stats = {"launches": 0, "redone": 0}
         lock = threading.Lock()
 
+        # Device-to-host copies go through ONE stream, issued back to back by a copier thread (a single copy
+        # saturates the PCIe link; concurrent ones only contend for the host's ingest bandwidth, and a gap
+        # between two copies is link time lost: with the copies issued by the workers under a lock the link
+        # ran at 45 of the 57 GB/s a bare copy loop reaches on the same box, profiles/r02_d2h_probe_n1.json).
+        # A delivery thread waits for each copy and hands the array to the sink, so a slow sink does not hold
+        # the next copy back.
+        copy_q, done_q = queue.Queue(), queue.Queue()
+        copy_stream = self._copy_stream
+
+        def copier():
+            try:
+                with torch.cuda.device(self.device):
+                    while True:
+                        item = copy_q.get()
+                        if item is None:
+                            break
+                        exported, src, dst, i, pooled, free = item
+                        copy_stream.wait_event(exported)
+                        with torch.cuda.stream(copy_stream):
+                            dst.copy_(src, non_blocking=True)
+                            done = torch.cuda.Event()
+                            done.record(copy_stream)
+                        done_q.put((done, dst, i, pooled, free))
+            except BaseException as e:          # noqa: BLE001 - re-raised in the caller's thread
+                errors.append(e)
+            finally:
+                done_q.put(None)
+
+        def deliver():
+            try:
+                while True:
+                    item = done_q.get()
+                    if item is None:
+                        break
+                    done, dst, i, pooled, free = item
+                    done.synchronize()
+                    free.set()                      # the staging buffer may take the next export
+                    try:
+                        if pooled:
+                            sink(i, mus[i], dst.numpy())
+                    finally:
+                        if pooled:
+                            self._pool.put(dst)
+            except BaseException as e:          # noqa: BLE001
+                errors.append(e)
+
         def work(wid):
             stream = self._streams[wid]
             try:
@@ -195,37 +241,36 @@ class SnapshotSweep:
                             stats["redone"] += solver.steps_redone
                         stage = self._stage.setdefault(wid, [])
                         while len(stage) < len(idx):
-                            stage.append(torch.empty((self.n2, self.num_steps + 1), dtype=torch.float64,
-                                                     device=self.device))
-                        exported = torch.cuda.Event()
+                            ev = threading.Event()
+                            ev.set()
+                            stage.append((torch.empty((self.n2, self.num_steps + 1), dtype=torch.float64,
+                                                      device=self.device), ev))
                         for j, i in enumerate(idx):
-                            solver.snapshots_device(j, layout=1, out=stage[j])
+                            buf, free = stage[j]
+                            free.wait()                 # its previous content has reached the host
+                            free.clear()
+                            solver.snapshots_device(j, layout=1, out=buf)
+                            exported = torch.cuda.Event()
                             exported.record(stream)
                             pooled = out is None
                             if pooled:
                                 dst = self._get_pool().get()
                             else:
                                 dst = out[i] if isinstance(out[i], torch.Tensor) else torch.from_numpy(out[i])
-                            try:
-                                # one device-to-host copy at a time per process: a single copy saturates the
-                                # PCIe link, concurrent ones only contend (on boxes where several GPUs share
-                                # the host's ingest bandwidth they make every rank slower)
-                                exported.synchronize()       # the export kernel is not part of what is serialised
-                                with self._copy_lock:
-                                    dst.copy_(stage[j], non_blocking=True)
-                                    stream.synchronize()
-                                if pooled:
-                                    sink(i, mus[i], dst.numpy())
-                            finally:
-                                if pooled:
-                                    self._pool.put(dst)
+                            copy_q.put((exported, buf, dst, i, pooled, free))
             except BaseException as e:          # noqa: BLE001 - re-raised in the caller's thread
                 errors.append(e)
 
+        movers = [threading.Thread(target=copier, daemon=True), threading.Thread(target=deliver, daemon=True)]
+        for t in movers:
+            t.start()
         threads = [threading.Thread(target=work, args=(w,), daemon=True) for w in range(min(self.workers, groups.qsize()))]
         for t in threads:
             t.start()
         for t in threads:
+            t.join()
+        copy_q.put(None)
+        for t in movers:
             t.join()
         if errors:
             raise errors[0]
