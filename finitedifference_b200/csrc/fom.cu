@@ -270,6 +270,104 @@ struct Level {            // what a cell keeps for its lower neighbour (D) at on
     double pm, pvv;       // v*du + u*dv, v*dv
 };
 
+// Two pieces of the CTA's data movement are duties that any warp can carry: they touch nothing but
+// shared memory that the per-step barrier already orders and their own running addresses.  With four
+// compute warps they ride on the two warps that hold one solve level each and would otherwise wait
+// ~250 cycles per step at the barrier (r02: the data-movement warp was the last to arrive, 7 % barrier
+// stall against 42-45 % for those two), in the stall slots of their FP64 chains.
+enum Duty { kDutyNone = 0, kDutyFeed = 1, kDutyGive = 2 };
+#ifndef BFD_SPLIT
+#define BFD_SPLIT 0
+#endif
+#ifndef BFD_UNROLL
+#define BFD_UNROLL 2
+#endif
+constexpr int kMainUnroll = BFD_UNROLL;       // wavefront steps per trip of the main loop
+constexpr bool kSplitDuties = BFD_SPLIT && (kWarpsPerStrip == 4);
+
+// kDutyFeed: keeps the level-0 input ring kPfDepth-1 rows ahead with cp.async, one row and one commit
+// group per step: "all but the newest kPfDepth-2 groups have landed" = "the row of the next step is there".
+template <bool CONT, bool UNI>
+struct InputFeed {
+    saddr pf_lane, pf_end, pf_d;
+    const double *src, *srcp, *lbc_p, *cy, *cyd;
+    int pf_row, ny, last_row, lane;
+    bool strip0;
+    __device__ __forceinline__ explicit InputFeed(const StepIo &io) {
+        lane = io.lane; ny = io.ny; last_row = ny + kSkew - 1;
+        pf_lane = io.pf + (saddr)(lane * 8);
+        pf_end = pf_lane + (saddr)(kPfDepth * kPfValues * 256);
+        pf_d = pf_lane;
+        src = io.xin; srcp = io.xwp; lbc_p = io.lbc; cy = io.cy; cyd = io.cyd;
+        pf_row = 0;
+        strip0 = io.strip == 0;
+    }
+    __device__ __forceinline__ void issue() {
+        constexpr int W = 32;
+        cp_async8(pf_d, src);
+        cp_async8(pf_d + 256, src + W);
+        if (CONT) { cp_async8(pf_d + 512, srcp); cp_async8(pf_d + 768, srcp + W); }
+        if (strip0) {                                        // warp-uniform: only the inlet strip carries lbc
+            if (lane == 0) cp_async8(pf_d + 1024, lbc_p);
+            if (pf_row < ny - 1) ++lbc_p;
+        }
+        if (!UNI) {
+            const int r = pf_row < last_row ? pf_row : last_row;
+            const int rcy = r - lane < 0 ? 0 : (r - lane >= ny ? ny - 1 : r - lane);   // grid row of this lane's cell
+            cp_async8(pf_d + 1280, cy + rcy);
+            cp_async8(pf_d + 1536, cyd + rcy);
+        }
+        if (pf_row < last_row) { src += 2 * W; if (CONT) srcp += 2 * W; }
+        ++pf_row;
+        pf_d += (saddr)(kPfValues * 256);
+        if (pf_d == pf_end) pf_d = pf_lane;
+    }
+    __device__ __forceinline__ void prologue() {             // before the barrier that opens step 0
+#pragma unroll
+        for (int i = 0; i < kPfDepth - 1; ++i) { issue(); cp_async_commit(); }
+        cp_async_wait_pending<kPfDepth - 2>();
+    }
+    __device__ __forceinline__ void step() {                 // row s + kPfDepth - 1: refills the slot read one step ago
+        issue();
+        cp_async_commit();
+        cp_async_wait_pending<kPfDepth - 2>();
+    }
+};
+
+// kDutyGive: sends what lane 31 published in the PREVIOUS step (slot 32 of the exchange rows) to the strip
+// on the right: lane p moves piece p of the row records, one 16-byte piece per lane and step, straight to
+// the records in global (or peer) memory; the row a lane sends lags by the Newton level of its piece.
+template <int K, bool CONT>
+struct EdgeGive {
+    static constexpr int NPR = 2 * K + 1 + (CONT ? 1 : 0);
+    saddr x_prev, x_sum;
+    double *gout;
+    int ro, ny;
+    bool give, out_remote;
+    __device__ __forceinline__ explicit EdgeGive(const StepIo &io) {
+        const int lane = io.lane;
+        const bool special = CONT && lane == 2 * K + 1;
+        const int lvl = special ? 0 : (lane >> 1);
+        ny = io.ny;
+        give = lane < NPR && io.strip < io.nstrips - 1;
+        out_remote = io.out_remote;
+        const saddr p_x = io.xchg + (saddr)((special ? K + 1 : (lane >> 1)) * 4 * kXRow + (special ? 0 : (lane & 1)) * kXRow);
+        x_sum = 2 * p_x + (saddr)(2 * kXRow);                // the two exchange buffers alternate: next = x_sum - current
+        x_prev = p_x;                                        // buffer of step -2 (even)
+        ro = -2 - kSkew - lvl;                               // row sent by the call for step s: s - 1 - 31 - level
+        gout = io.edge_out + 2 * lane + (ptrdiff_t)ro * kRecDoubles;
+    }
+    __device__ __forceinline__ void step() {                 // once before step 0, once per step, once after the last
+        if (give && (unsigned)ro < (unsigned)ny) {
+            double a, b;
+            lds2(x_prev + 32 * 16, a, b);
+            if (out_remote) st_sys2(gout, a, b); else st_volatile2(gout, a, b);
+        }
+        ++ro; gout += kRecDoubles;
+        x_prev = x_sum - x_prev;
+    }
+};
+
 // Levels LO..HI-1 of one trapezoidal time step of one strip.  A time step is K fused Newton
 // solves (levels 0..K-1) plus the residual of x_K (level K); the levels are split between the
 // warps of the CTA, which pass the iterate from level HI-1 to level HI through shared memory
@@ -288,9 +386,8 @@ struct Level {            // what a cell keeps for its lower neighbour (D) at on
 // step later; lane 0 reads the same pairs from the hand-off record of the strip on its left
 // instead (only the ADDRESS differs), and lane 31 also files them in the record for the strip
 // on its right.
-template <int K, int LO, int HI, bool CONT, bool UNI>
+template <int K, int LO, int HI, bool CONT, bool UNI, int DUTY>
 __device__ __forceinline__ void sweep_part(const StepIo &io) {
-    constexpr int NPR = 2 * K + 1 + (CONT ? 1 : 0);
     constexpr bool FIRST = (LO == 0), LAST = (HI == K + 1);
     constexpr int W = 32;
     const int lane = io.lane, ny = io.ny;
@@ -323,6 +420,8 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
     const saddr xc_own = io.xchg + (saddr)((lane + 1) * 16);   // this lane's pairs (slot lane + 1)
     const saddr xc_left = io.xchg + (saddr)(lane * 16);        // the left column's: lane - 1, or the halo slot for lane 0
     auto xc_level = [](int k, int buf) { return (saddr)((k * 2 + buf) * 2 * kXRow); };
+    InputFeed<CONT, UNI> feed(io);
+    EdgeGive<K, CONT> edge(io);
 
     // One wavefront step.  EP ("edge phase"): some lane's row is outside the grid at some level
     // (first 32+K and last 31+K steps); the main phase runs without row masks.
@@ -345,6 +444,8 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
             lds2(h + kPairRow, Au[LO], Av[LO]);
             if (!UNI) lds2(h + 2 * kPairRow, Cy[LO], Cyd[LO]);
         }
+        if (DUTY == kDutyFeed) feed.step();
+        if (DUTY == kDutyGive) edge.step();
 
         // levels in descending order: level k+1 consumes xu[k+1], Au[k+1] before level k
         // replaces them with the values for the next step
@@ -391,10 +492,20 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
             const double Fh = hu * u, Gh = hu * v, Hh = hv * v;
             double DG = prev[k].Gh, DH = prev[k].Hh;
             if (EP) { DG = top ? 0.0 : DG; DH = top ? 0.0 : DH; }
+#ifdef BFD_AU_LATE
+            // level 0 forms Au, Av in this very step: add them last, so that their chain runs beside this one
+            double ru = k == 0 ? u : Au[k] + u;
+            ru = fma(cx, Fh, ru); ru = fma(cy, Gh, ru); ru = fma(ncxl, LF, ru); ru = fma(ncyd, DG, ru);
+            if (k == 0) ru += Au[0];
+            double rv = k == 0 ? v : Av[k] + v;
+            rv = fma(cy, Hh, rv); rv = fma(cx, Gh, rv); rv = fma(ncyd, DH, rv); rv = fma(ncxl, LG, rv);
+            if (k == 0) rv += Av[0];
+#else
             double ru = Au[k] + u;
             ru = fma(cx, Fh, ru); ru = fma(cy, Gh, ru); ru = fma(ncxl, LF, ru); ru = fma(ncyd, DG, ru);
             double rv = Av[k] + v;
             rv = fma(cy, Hh, rv); rv = fma(cx, Gh, rv); rv = fma(ncyd, DH, rv); rv = fma(ncxl, LG, rv);
+#endif
             const double r2 = fma(rv, rv, ru * ru);
             // main phase: every row is a cell; padding columns (last strip) are dropped after the loop
             nrm[k] += EP ? (valid ? r2 : 0.0) : r2;
@@ -444,7 +555,9 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
         __syncthreads();
     };
 
-    __syncthreads();      // row 0 and the first hand-off block are in shared memory (dma_part)
+    if (DUTY == kDutyFeed) feed.prologue();
+    if (DUTY == kDutyGive) edge.step();
+    __syncthreads();      // row 0 and the first hand-off block are in shared memory (dma_part / the feed duty)
     // head (rows entering the strip), main (0 < row < ny for every lane and level), tail; the
     // two edge phases share one copy of the masked body (code size: instruction cache)
     const int head_end = nsteps < kSkew + K + 1 ? nsteps : kSkew + K + 1;
@@ -456,11 +569,12 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
 #pragma unroll 1
         for (; s < ep_end; ++s) body(s, BoolTag<true>{});
         if (phase == 0) {
-#pragma unroll 2
+#pragma unroll kMainUnroll
             for (; s < main_end; ++s) body(s, BoolTag<false>{});
         }
     }
 
+    if (DUTY == kDutyGive) edge.step();          // what lane 31 published in the last step
     // ||r(x_k)||^2 of this strip, fixed reduction order (deterministic iteration counts)
 #pragma unroll
     for (int k = LO; k < HI; ++k) {
@@ -471,13 +585,22 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
     }
 }
 
-// A warp with no level in this pass only keeps the CTA's barrier count.
-template <int K>
+// A warp with no level in this pass keeps the CTA's barrier count and carries its duty.
+template <int K, bool CONT, bool UNI, int DUTY>
 __device__ __forceinline__ void idle_part(const StepIo &io) {
     const int nsteps = io.ny + kSkew + K;
+    InputFeed<CONT, UNI> feed(io);
+    EdgeGive<K, CONT> edge(io);
+    if (DUTY == kDutyFeed) feed.prologue();
+    if (DUTY == kDutyGive) edge.step();
     __syncthreads();
-    for (int s = 0; s < nsteps; ++s) __syncthreads();
-    (void)io;
+#pragma unroll 1
+    for (int s = 0; s < nsteps; ++s) {
+        if (DUTY == kDutyFeed) feed.step();
+        if (DUTY == kDutyGive) edge.step();
+        __syncthreads();
+    }
+    if (DUTY == kDutyGive) edge.step();
 }
 
 // The data-movement warp of the CTA: keeps the level-0 input ring kPfDepth-1 rows ahead with
@@ -492,10 +615,8 @@ __device__ __forceinline__ void idle_part(const StepIo &io) {
 template <int K, bool CONT, bool UNI>
 __device__ __forceinline__ void dma_part(const StepIo &io) {
     constexpr int NPR = 2 * K + 1 + (CONT ? 1 : 0);
-    constexpr int W = 32;
     static_assert(NPR <= 32, "one lane per piece of a record row");
     const int lane = io.lane, ny = io.ny;
-    const int last_row = ny + kSkew - 1;
     const int nsteps = ny + kSkew + K;
     int err = 0;
     unsigned misses = 0, spins_total = 0;
@@ -512,17 +633,16 @@ __device__ __forceinline__ void dma_part(const StepIo &io) {
     //   out: the records of this strip <- what lane 31 (slot 32) published in the previous step.
     const bool special = CONT && lane == 2 * K + 1;
     const int lvl = special ? 0 : (lane >> 1);
-    const bool take = lane < NPR && io.strip > 0, give = lane < NPR && io.strip < io.nstrips - 1;
-    const bool in_remote = io.in_remote, out_remote = io.out_remote;
+    const bool take = lane < NPR && io.strip > 0;
+    const bool in_remote = io.in_remote;
     const saddr p_x = io.xchg + (saddr)((special ? K + 1 : (lane >> 1)) * 4 * kXRow + (special ? 0 : (lane & 1)) * kXRow);
     const saddr x_sum = 2 * p_x + (saddr)(2 * kXRow);        // the two exchange buffers alternate: next = x_sum - current
     saddr x_cur = p_x + (saddr)(2 * kXRow);                  // buffer of step -1 (odd)
-    saddr x_prev = p_x;
+    InputFeed<CONT, UNI> feed(io);                           // the two duties, when no compute warp carries them
+    EdgeGive<K, CONT> edge(io);
     const saddr ring0 = io.ring_in + (saddr)(lane * 16), ring_end = ring0 + (saddr)(kInRing * kRecBytes);
     int rc = -lvl;                                           // row consumed by the call for step s: s + 1 - level
-    int ro = -2 - kSkew - lvl;                               // row sent by the call for step s: s - 1 - 31 - level
     double *gin = io.edge_in + 2 * lane + (ptrdiff_t)rc * kRecDoubles;
-    double *gout = io.edge_out + 2 * lane + (ptrdiff_t)ro * kRecDoubles;
     saddr sl = ring0 + (saddr)(((rc + 1) & (kInRing - 1)) * kRecBytes);          // slot of the row loaded early
     saddr pl = ring0 + (saddr)(((rc + kAhead) & (kInRing - 1)) * kRecBytes);     // slot of the row copied now
     double va = 0.0, vb = 0.0;                               // the piece consumed by the next call
@@ -570,58 +690,25 @@ __device__ __forceinline__ void dma_part(const StepIo &io) {
 #endif
             if (rc + kAhead < ny) cp_async16(pl, gin + (size_t)kAhead * kRecDoubles);
         }
-        if (give && (unsigned)ro < (unsigned)ny) {
-            double a, b;
-            lds2(x_prev + 32 * 16, a, b);
-            if (out_remote) st_sys2(gout, a, b); else st_volatile2(gout, a, b);
-        }
+        if (!kSplitDuties) edge.step();
         va = na; vb = nb;
-        ++rc; ++ro; gin += kRecDoubles; gout += kRecDoubles;
+        ++rc; gin += kRecDoubles;
         sl += (saddr)kRecBytes; if (sl == ring_end) sl = ring0;
         pl += (saddr)kRecBytes; if (pl == ring_end) pl = ring0;
-        x_prev = x_cur;
         x_cur = x_sum - x_cur;
     };
 
-    // ---- level-0 input ring: one row per step, kPfDepth - 1 rows ahead; running addresses ------
-    const saddr pf_lane = io.pf + (saddr)(lane * 8);
-    const saddr pf_end = pf_lane + (saddr)(kPfDepth * kPfValues * 256);
-    saddr pf_d = pf_lane;
-    const double *src = io.xin, *srcp = io.xwp, *lbc_p = io.lbc;
-    int pf_row = 0;
-    const bool strip0 = io.strip == 0;
-    auto pf_issue = [&]() {
-        cp_async8(pf_d, src);
-        cp_async8(pf_d + 256, src + W);
-        if (CONT) { cp_async8(pf_d + 512, srcp); cp_async8(pf_d + 768, srcp + W); }
-        if (strip0) {                                        // warp-uniform: only the inlet strip carries lbc
-            if (lane == 0) cp_async8(pf_d + 1024, lbc_p);
-            if (pf_row < ny - 1) ++lbc_p;
-        }
-        if (!UNI) {
-            const int r = pf_row < last_row ? pf_row : last_row;
-            const int rcy = r - lane < 0 ? 0 : (r - lane >= ny ? ny - 1 : r - lane);   // grid row of this lane's cell
-            cp_async8(pf_d + 1280, io.cy + rcy);
-            cp_async8(pf_d + 1536, io.cyd + rcy);
-        }
-        if (pf_row < last_row) { src += 2 * W; if (CONT) srcp += 2 * W; }
-        ++pf_row;
-        pf_d += (saddr)(kPfValues * 256);
-        if (pf_d == pf_end) pf_d = pf_lane;
-    };
-    // One commit group per step: "all but the newest kPfDepth-2 groups" = "the row of the next
-    // step, and the hand-off rows copied >= 4 steps ago, have landed".
-#pragma unroll
-    for (int i = 0; i < kPfDepth - 1; ++i) { pf_issue(); cp_async_commit(); }
-    cp_async_wait_pending<kPfDepth - 2>();
+    // One commit group per step (the feed duty's row rides in it when this warp carries that duty): "all
+    // but the newest kPfDepth-2 groups" = "the hand-off rows copied >= 4 steps ago have landed".
+    if (!kSplitDuties) feed.prologue();
+    else { cp_async_commit(); cp_async_wait_pending<0>(); }      // the first kAhead rows of the ring
     if (take && (unsigned)rc < (unsigned)ny) lds2(ring0 + (saddr)((rc & (kInRing - 1)) * kRecBytes), va, vb);
     halo();                                  // "step -1": what lane 0 reads in step 0
     __syncthreads();
 #pragma unroll 1
     for (int s = 0; s < nsteps; ++s) {
-        pf_issue();                          // row s + kPfDepth - 1: refills the slot read one step ago
-        cp_async_commit();
-        cp_async_wait_pending<kPfDepth - 2>();
+        if (!kSplitDuties) feed.step();
+        else { cp_async_commit(); cp_async_wait_pending<kPfDepth - 2>(); }
         halo();
         __syncthreads();
     }
@@ -644,6 +731,11 @@ __device__ __forceinline__ void dma_part(const StepIo &io) {
 __host__ __device__ constexpr int part(int K, int w) {
     if (kWarpsPerStrip == 1) return w == 0 ? 0 : K + 1;
     if (kWarpsPerStrip == 2) return w == 0 ? 0 : (w == 1 ? (K + 1) / 2 : K + 1);
+    if (kWarpsPerStrip == 5) {
+        if (K + 1 <= 5) return w < K + 1 ? w : K + 1;
+        if (K == 5) return w < 4 ? w : (w == 4 ? 4 : 6);                 // 0 | 1 | 2 | 3 | 4 5
+        return w == 0 ? 0 : w == 1 ? 1 : w == 2 ? 2 : w == 3 ? 3 : w == 4 ? 5 : 7;   // K == 6: 0 | 1 | 2 | 3 4 | 5 6
+    }
     if (K + 1 <= 4) return w < K + 1 ? w : K + 1;
     if (K == 4) return w == 0 ? 0 : w == 1 ? 1 : w == 2 ? 2 : w == 3 ? 3 : 5;
     if (K == 5) return w == 0 ? 0 : w == 1 ? 1 : w == 2 ? 3 : w == 3 ? 4 : 6;
@@ -653,20 +745,23 @@ __host__ __device__ constexpr int part(int K, int w) {
 template <int K, int WARP, bool CONT, bool UNI>
 __device__ __forceinline__ void sweep_warp(const StepIo &io) {
     constexpr int LO = part(K, WARP), HI = part(K, WARP + 1);
-    if constexpr (LO < HI) sweep_part<K, LO, HI, CONT, UNI>(io);
-    else idle_part<K>(io);
+    constexpr int DUTY = !kSplitDuties ? kDutyNone : WARP == 1 ? kDutyFeed : WARP == 2 ? kDutyGive : kDutyNone;
+    if constexpr (LO < HI) sweep_part<K, LO, HI, CONT, UNI, DUTY>(io);
+    else idle_part<K, CONT, UNI, DUTY>(io);
 }
 
-// The K+1 levels of a time step split between the warps of the CTA.
-template <int K, bool CONT, bool UNI>
+// The K+1 levels of a time step split between the warps of the CTA.  DMA: this copy of the code is the one
+// the data-movement warp runs (the kernel splits the two kinds of warp at the top: register budgets).
+template <int K, bool CONT, bool UNI, bool DMA>
 __device__ __forceinline__ void sweep_step(const StepIo &io, int warp) {
+    if constexpr (DMA) { dma_part<K, CONT, UNI>(io); return; }
     if (warp == 0) sweep_warp<K, 0, CONT, UNI>(io);
     if constexpr (kWarpsPerStrip > 1) { if (warp == 1) sweep_warp<K, 1, CONT, UNI>(io); }
     if constexpr (kWarpsPerStrip > 2) {
         if (warp == 2) sweep_warp<K, 2, CONT, UNI>(io);
         if (warp == 3) sweep_warp<K, 3, CONT, UNI>(io);
     }
-    if (warp == kWarpsPerStrip) dma_part<K, CONT, UNI>(io);
+    if constexpr (kWarpsPerStrip > 4) { if (warp == 4) sweep_warp<K, 4, CONT, UNI>(io); }
 }
 
 }  // namespace bfd
@@ -806,24 +901,22 @@ template <bool SLAB> __device__ __forceinline__ unsigned a_add(unsigned *p, unsi
     return atomicAdd(p, v);
 }
 
-template <bool UNI, bool SLAB>
-__global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk_kernel(const FomArgs a) {
-    constexpr int kSmemDoubles = kInRing * kRecDoubles + (kHandIfaces * kHandBytes + kXchgBytes + kPfBytes) / 8;
-    BFD_SHARED_ARRAY(double, s_mem, [kSmemDoubles]);
-    BFD_SHARED_ARRAY(int, s_ctl, [8]);
-    BFD_SHARED_ARRAY(double, s_dbl, [2]);
-    const int lane = lane_id(), warp = threadIdx.x >> 5;
+constexpr int kChunkSmemDoubles = kInRing * kRecDoubles + (kHandIfaces * kHandBytes + kXchgBytes + kPfBytes) / 8;
+
+// The work of one CTA of fom_chunk_kernel, as the compute warps (DMA = false) or the data-movement warp
+// (DMA = true) run it: the same control flow and the same barriers, two copies of the code (the commit logic
+// of the leader thread exists in the compute copy only, the record hand-off in the other).
+template <bool UNI, bool SLAB, bool DMA>
+__device__ __forceinline__ void chunk_main(const FomArgs &a, double *s_mem, int *s_ctl, double *s_dbl, int item,
+                                           const int warp) {
+    const int lane = lane_id();
+    const bool leader = !DMA && warp == 0 && lane == 0;     // `warp` is the role: 0 .. kWarpsPerStrip-1 compute, then data movement
     const int nstrips = a.ssl.nstrips;
-    for (int i = threadIdx.x; i < kSmemDoubles; i += blockDim.x) s_mem[i] = 0.0;
-    if (threadIdx.x == 0) s_ctl[0] = (int)atomicInc(a.ticket, gridDim.x - 1);
-    __syncthreads();
-    const int item = __shfl_sync(0xffffffffu, s_ctl[0], 0);
-    if (item >= a.batch * nstrips) return;
     const int m = item / nstrips, j = item - m * nstrips;
     const int jg = j + a.strip0, nsg = a.ns_global;        // this strip and the strip count in the whole grid
     FomCtl *ctl = a.ctl + m;
     if (SLAB) {
-        if (threadIdx.x == 0 && a.launch_index > 0) {
+        if (leader && a.launch_index > 0) {
             const unsigned need = (unsigned)a.launch_index * (unsigned)nsg;
             SpinClock spins;
             while (*(volatile unsigned *)&ctl->exits < need && *(volatile int *)&ctl->t < a.num_steps &&
@@ -864,7 +957,7 @@ __global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk
     for (;;) {                       // segments: runs of steps between two commits
         __syncthreads();
         unsigned epoch0 = 0;
-        if (threadIdx.x == 0) {
+        if (leader) {
             // control words are read by one thread and broadcast by shuffle: the compiler then
             // knows they are warp-uniform
             const volatile FomCtl *vc = ctl;       // written by other CTAs (other GPUs in slab runs)
@@ -885,7 +978,7 @@ __global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk
             const int ii = attempt - i0, t = t0 + ii;
             if (t >= a.num_steps) break;
             __syncthreads();
-            if (threadIdx.x == 0) {
+            if (leader) {
                 const unsigned old = a_max<SLAB>(&ctl->gate, (unsigned)attempt);
                 s_ctl[5] = ((old & kGateStop) && (unsigned)attempt > (old & (kGateStop - 1))) ? 0 : 1;
             }
@@ -909,22 +1002,22 @@ __global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk
             }
             io.partial = a.partial + ((size_t)(m * a.chunk + i) * nsg + jg) * kNormSlots;
             unsigned long long *tr = a.trace + ((size_t)(m * a.chunk + i) * nstrips + j) * 3;
-            if (threadIdx.x == 0) tr[0] = global_timer_ns();
+            if (leader) tr[0] = global_timer_ns();
             io.stats = tr + 2;
             if (kb) {
-                sweep_step<1, true, UNI>(io, warp);
+                sweep_step<1, true, UNI, DMA>(io, warp);
             } else {
                 switch (K) {
-                case 1: sweep_step<1, false, UNI>(io, warp); break;
-                case 2: sweep_step<2, false, UNI>(io, warp); break;
-                case 3: sweep_step<3, false, UNI>(io, warp); break;
-                case 4: sweep_step<4, false, UNI>(io, warp); break;
-                case 5: sweep_step<5, false, UNI>(io, warp); break;
-                default: sweep_step<6, false, UNI>(io, warp); break;
+                case 1: sweep_step<1, false, UNI, DMA>(io, warp); break;
+                case 2: sweep_step<2, false, UNI, DMA>(io, warp); break;
+                case 3: sweep_step<3, false, UNI, DMA>(io, warp); break;
+                case 4: sweep_step<4, false, UNI, DMA>(io, warp); break;
+                case 5: sweep_step<5, false, UNI, DMA>(io, warp); break;
+                default: sweep_step<6, false, UNI, DMA>(io, warp); break;
                 }
             }
             __syncthreads();       // every warp has published its norms
-            if (threadIdx.x == 0) {
+            if (leader) {
                 tr[1] = global_timer_ns();
                 fence<SLAB>();
                 if (a_inc<SLAB>(&a.arrive[(size_t)m * a.chunk + i], (unsigned)nsg - 1) == (unsigned)nsg - 1) {
@@ -934,7 +1027,7 @@ __global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk
             }
         }
         // end of the segment: the last strip commits; refused strips wait for it and restart
-        if (threadIdx.x == 0) {
+        if (leader) {
             fence<SLAB>();
             if (a_inc<SLAB>(&ctl->arrive, (unsigned)nsg - 1) == (unsigned)nsg - 1) {
                 fence<SLAB>();
@@ -956,8 +1049,27 @@ __global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk
     }
     if (SLAB) {   // this strip is done with the launch: its re-armed records and commits are visible
         __syncthreads();
-        if (threadIdx.x == 0) { fence<SLAB>(); a_add<SLAB>(&ctl->exits, 1u); }
+        if (leader) { fence<SLAB>(); a_add<SLAB>(&ctl->exits, 1u); }
     }
+}
+
+template <bool UNI, bool SLAB>
+__global__ void __launch_bounds__(32 * (kWarpsPerStrip + 1), BFD_MINB) fom_chunk_kernel(const FomArgs a) {
+    BFD_SHARED_ARRAY(double, s_mem, [kChunkSmemDoubles]);
+    BFD_SHARED_ARRAY(int, s_ctl, [8]);
+    BFD_SHARED_ARRAY(double, s_dbl, [2]);
+    for (int i = threadIdx.x; i < kChunkSmemDoubles; i += blockDim.x) s_mem[i] = 0.0;
+    if (threadIdx.x == 0) s_ctl[0] = (int)atomicInc(a.ticket, gridDim.x - 1);
+    __syncthreads();
+    const int item = __shfl_sync(0xffffffffu, s_ctl[0], 0);
+    if (item >= a.batch * a.ssl.nstrips) return;
+    // Roles by warp index.  The 5 warps of a CTA sit on consecutive hardware warp slots and slot mod 4 is the SM
+    // sub-partition, so with 4 CTAs per SM every sub-partition holds one warp of each role; giving every
+    // sub-partition ONE compute role instead (roles by %warpid: two loop bodies in its instruction cache instead
+    // of five) was measured 19 % slower -- the heavy roles then share an FP64 pipe (profiles/r02_notes.md, 8).
+    const int role = threadIdx.x >> 5;
+    if (role == kWarpsPerStrip) chunk_main<UNI, SLAB, true>(a, s_mem, s_ctl, s_dbl, item, role);
+    else chunk_main<UNI, SLAB, false>(a, s_mem, s_ctl, s_dbl, item, role);
 }
 
 }  // namespace bfd
