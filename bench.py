@@ -302,9 +302,11 @@ def main():
         dist.barrier()
     e2e_reps = max(1, min(args.steps, 3))
     t0 = time.perf_counter()
+    copy_stats = []
     for _ in range(e2e_reps):
         seen.clear()
         sweep.run(w0_np, mus_e, sink=sink)
+        copy_stats.append(sweep.copy_stats)
         assert len(seen) == Be and all(np.isfinite(v[1]) and v[0] == len(w0_np[::4099]) for v in seen.values()), seen
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
@@ -318,6 +320,11 @@ def main():
            "mu_per_gpu": Be, "seconds_per_step": e2e_s / e2e_reps, "pinned_buffers_per_gpu": pool,
            "host_numa_node": numa,
            "d2h_GBps_per_gpu": Be * 2 * cells * (T + 1) * 8 * e2e_reps / e2e_s / 1e9,
+           "link": {"GBps_while_copying": float(np.mean([c["GBps_while_copying"] for c in copy_stats])),
+                    "seconds_in_copies_per_step": float(np.mean([c["seconds_in_copies"] for c in copy_stats])),
+                    "seconds_first_to_last_copy_per_step": float(np.mean([c["seconds_first_to_last"] for c in copy_stats])),
+                    "worker_seconds_per_step": {k[7:]: float(np.mean([c[k] for c in copy_stats])) for k in copy_stats[0]
+                                                if k.startswith("worker_")}},
            "api": f"SnapshotSweep(group={args.e2e_group}, workers={args.e2e_workers}).run(w0, mus, sink): every "
                   "(2N, T+1) trajectory copied to pinned host memory and handed to the sink"}
     del sweep

@@ -1205,6 +1205,18 @@ static int fom_set_initial_impl(const bfd_fom_desc *d, const SlabView &v, void *
     return BFD_OK;
 }
 
+// The run's status words, written by the GPU straight into the caller's page-locked memory (zero-copy):
+// polling must not go through a copy engine, where an 8-byte cudaMemcpyAsync queues behind whatever bulk
+// device-to-host copies the process has in flight -- a sweep that streams 4.5 GB trajectories to the host held
+// every poll back by one or more 79 ms copies and ran its launches one at a time (profiles/r02_notes.md, 9).
+__global__ void fom_status_kernel(const FomGlobal *g, int *host_words) {
+    const volatile FomGlobal *v = g;
+    host_words[0] = v->done;
+    host_words[1] = v->error;
+    host_words[2] = v->redone;
+    __threadfence_system();
+}
+
 static int launch_chunk(const FomArgs &a, cudaStream_t st) {
     const int grid = a.batch * a.ssl.nstrips;
     if (a.variant == 1) {
@@ -1244,7 +1256,9 @@ static int fom_run_impl(const bfd_fom_desc *d, const SlabView &v, void *ws, cons
     cudaEvent_t ev[2];
     BFD_CUDA(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming));
     BFD_CUDA(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
-    int *h_poll = (int *)h_pinned + 4;   // two 2-int landing zones at h[4..5], h[6..7]
+    int *h_poll = (int *)h_pinned + 4;   // two landing zones of 3 ints at h[4..6], h[7..9]; final status at h[10..12]
+    int *d_poll = nullptr;               // the same words as the device sees them; null: not mapped, copy instead
+    if (cudaHostGetDevicePointer((void **)&d_poll, h_poll, 0) != cudaSuccess) { cudaGetLastError(); d_poll = nullptr; }
     const long long hard_cap = (long long)d->num_steps * d->max_its + 8;
     long long launched = 0;
     int rc = BFD_OK, pending = 0, slot = 0;
@@ -1254,19 +1268,29 @@ static int fom_run_impl(const bfd_fom_desc *d, const SlabView &v, void *ws, cons
         rc = launch_chunk(a, st);
         ++launched;
         if (rc != BFD_OK) break;
-        cudaError_t e = cudaMemcpyAsync(h_poll + 2 * slot, &a.glob->done, 2 * sizeof(int),
-                                        cudaMemcpyDeviceToHost, st);
+        cudaError_t e = cudaSuccess;
+        if (d_poll) {
+            BFD_LAUNCH(fom_status_kernel, 1, 1, 0, st, a.glob, d_poll + 3 * slot);
+            BFD_LAUNCHED();
+        } else {
+            e = cudaMemcpyAsync(h_poll + 3 * slot, &a.glob->done, 3 * sizeof(int), cudaMemcpyDeviceToHost, st);
+        }
         if (e == cudaSuccess) e = cudaEventRecord(ev[slot], st);
         if (e != cudaSuccess) { rc = record_cuda_error(e, "fom poll"); break; }
         if (pending) {   // look at the poll issued one launch ago
             const int prev = slot ^ 1;
             e = cudaEventSynchronize(ev[prev]);
             if (e != cudaSuccess) { rc = record_cuda_error(e, "fom poll sync"); break; }
-            if (h_poll[2 * prev] >= d->batch || h_poll[2 * prev + 1] != 0) finished = true;
+            const volatile int *hp = h_poll + 3 * prev;
+            if (hp[0] >= d->batch || hp[1] != 0) finished = true;
         }
         pending = 1;
         slot ^= 1;
         if (launched > hard_cap) { rc = BFD_ENOTCONVERGED; break; }
+    }
+    if (rc == BFD_OK && d_poll) {
+        BFD_LAUNCH(fom_status_kernel, 1, 1, 0, st, a.glob, d_poll + 6);
+        BFD_LAUNCHED();
     }
     cudaError_t e = cudaStreamSynchronize(st);
     if (e != cudaSuccess && rc == BFD_OK) rc = record_cuda_error(e, "fom run sync");
@@ -1274,8 +1298,13 @@ static int fom_run_impl(const bfd_fom_desc *d, const SlabView &v, void *ws, cons
     cudaEventDestroy(ev[1]);
     if (rc == BFD_OK) {
         int fin[4] = {0, 0, 0, 0};
-        e = cudaMemcpy(fin, &a.glob->done, 3 * sizeof(int), cudaMemcpyDeviceToHost);
-        if (e != cudaSuccess) return record_cuda_error(e, "fom final status");
+        if (d_poll) {
+            const volatile int *hp = h_poll + 6;
+            fin[0] = hp[0]; fin[1] = hp[1]; fin[2] = hp[2];
+        } else {
+            e = cudaMemcpy(fin, &a.glob->done, 3 * sizeof(int), cudaMemcpyDeviceToHost);
+            if (e != cudaSuccess) return record_cuda_error(e, "fom final status");
+        }
         h[0] = fin[0]; h[1] = fin[1]; h[2] = (int)launched; h[3] = fin[2];
         if (fin[1] != 0) rc = fin[1];
         else if (fin[0] < d->batch) rc = BFD_ENOTCONVERGED;

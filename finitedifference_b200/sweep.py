@@ -22,6 +22,7 @@ from __future__ import annotations
 import os
 import queue
 import threading
+import time
 
 import numpy as np
 import torch
@@ -121,6 +122,7 @@ class SnapshotSweep:
         self._stage = {}          # worker -> list of device staging tensors
         self._streams = [torch.cuda.Stream(device=self.device) for _ in range(self.workers)]
         self._copy_stream = torch.cuda.Stream(device=self.device)
+        self.copy_stats = None
         self.launches = 0
         self.steps_redone = 0
 
@@ -174,7 +176,7 @@ class SnapshotSweep:
         for lo in range(0, n, self.group):
             groups.put(list(range(lo, min(lo + self.group, n))))
         errors = []
-        stats = {"launches": 0, "redone": 0}
+        stats = {"launches": 0, "redone": 0, "sweeps": 0.0, "stage_wait": 0.0, "pool_wait": 0.0}
         lock = threading.Lock()
 
         # Device-to-host copies go through ONE stream, issued back to back by a copier thread (a single copy
@@ -185,6 +187,7 @@ class SnapshotSweep:
         # the next copy back.
         copy_q, done_q = queue.Queue(), queue.Queue()
         copy_stream = self._copy_stream
+        spans = []                                  # (begin, done, bytes) of every copy, on the copy stream
 
         def copier():
             try:
@@ -196,9 +199,12 @@ class SnapshotSweep:
                         exported, src, dst, i, pooled, free = item
                         copy_stream.wait_event(exported)
                         with torch.cuda.stream(copy_stream):
+                            begin = torch.cuda.Event(enable_timing=True)
+                            begin.record(copy_stream)
                             dst.copy_(src, non_blocking=True)
-                            done = torch.cuda.Event()
+                            done = torch.cuda.Event(enable_timing=True)
                             done.record(copy_stream)
+                        spans.append((begin, done, src.numel() * src.element_size()))
                         done_q.put((done, dst, i, pooled, free))
             except BaseException as e:          # noqa: BLE001 - re-raised in the caller's thread
                 errors.append(e)
@@ -234,11 +240,13 @@ class SnapshotSweep:
                         except queue.Empty:
                             break
                         solver = self._solver(wid, len(idx), [mus[i] for i in idx])
+                        tw = time.perf_counter()
                         solver.set_initial(w0_dev)
                         solver.run()
                         with lock:
                             stats["launches"] += solver.launches
                             stats["redone"] += solver.steps_redone
+                            stats["sweeps"] += time.perf_counter() - tw
                         stage = self._stage.setdefault(wid, [])
                         while len(stage) < len(idx):
                             ev = threading.Event()
@@ -247,14 +255,18 @@ class SnapshotSweep:
                                                       device=self.device), ev))
                         for j, i in enumerate(idx):
                             buf, free = stage[j]
+                            tw = time.perf_counter()
                             free.wait()                 # its previous content has reached the host
                             free.clear()
+                            stats["stage_wait"] += time.perf_counter() - tw
                             solver.snapshots_device(j, layout=1, out=buf)
                             exported = torch.cuda.Event()
                             exported.record(stream)
                             pooled = out is None
                             if pooled:
+                                tw = time.perf_counter()
                                 dst = self._get_pool().get()
+                                stats["pool_wait"] += time.perf_counter() - tw
                             else:
                                 dst = out[i] if isinstance(out[i], torch.Tensor) else torch.from_numpy(out[i])
                             copy_q.put((exported, buf, dst, i, pooled, free))
@@ -275,6 +287,17 @@ class SnapshotSweep:
         if errors:
             raise errors[0]
         self.launches, self.steps_redone = stats["launches"], stats["redone"]
+        if spans:
+            # how busy the link was: time inside copies against first-copy-start .. last-copy-end, and the wall
+            # time of the call before the first copy could start (the first group's sweeps)
+            torch.cuda.synchronize(self.device)
+            busy = sum(b.elapsed_time(d) for b, d, _ in spans) * 1e-3
+            span = spans[0][0].elapsed_time(spans[-1][1]) * 1e-3
+            self.copy_stats = {"copies": len(spans), "bytes": int(sum(n for _, _, n in spans)),
+                               "seconds_in_copies": busy, "seconds_first_to_last": span,
+                               "GBps_while_copying": sum(n for _, _, n in spans) / busy / 1e9 if busy > 0 else None,
+                               "worker_seconds_in_sweeps": stats["sweeps"], "worker_seconds_waiting_for_staging": stats["stage_wait"],
+                               "worker_seconds_waiting_for_pinned": stats["pool_wait"]}
         if out is None:
             return None
         return [o.numpy() if isinstance(o, torch.Tensor) else o for o in out]

@@ -2,7 +2,7 @@
 pinned host memory back to back, all ranks at once -- the ceiling of any API that returns the reference's
 arrays to the host (bench.py's `e2e`).  One JSON line from rank 0.
 
-    python tools/d2h_probe.py
+    python tools/d2h_probe.py [--buffers 6]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \\
         --master-port 29544 tools/d2h_probe.py
 """
@@ -28,10 +28,11 @@ def main():
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     numa = bind_host_to_gpu_node(dev)
+    nbuf = int(sys.argv[sys.argv.index("--buffers") + 1]) if "--buffers" in sys.argv else 2   # distinct pinned destinations, round robin
     n2, t1 = 2 * 750 * 750, 501
     src = torch.ones((n2, t1), dtype=torch.float64, device=dev)
-    dst = [torch.empty((n2, t1), dtype=torch.float64).pin_memory() for _ in range(2)]
-    reps = 6
+    dst = [torch.empty((n2, t1), dtype=torch.float64).pin_memory() for _ in range(nbuf)]
+    reps = max(6, 2 * nbuf)
     for d in dst:
         d.copy_(src, non_blocking=True)
     torch.cuda.synchronize()
@@ -40,7 +41,7 @@ def main():
     with ClockSampler(local, 100) as clk:
         t0 = time.perf_counter()
         for i in range(reps):
-            dst[i % 2].copy_(src, non_blocking=True)
+            dst[i % nbuf].copy_(src, non_blocking=True)
         torch.cuda.synchronize()
         el = time.perf_counter() - t0
     t = torch.tensor([el], dtype=torch.float64, device=dev)
@@ -49,7 +50,7 @@ def main():
     gb = reps * src.numel() * 8 / 1e9
     if rank == 0:
         print(json.dumps({"probe": "pinned D2H, all ranks at once", "n_gpus": world, "bytes_per_copy": src.numel() * 8,
-                          "copies_per_rank": reps, "seconds_max_over_ranks": float(t.item()),
+                          "copies_per_rank": reps, "pinned_buffers": nbuf, "seconds_max_over_ranks": float(t.item()),
                           "GBps_per_gpu": gb / float(t.item()), "GBps_aggregate": world * gb / float(t.item()),
                           "host_numa_node_rank0": numa, "cpu_count": os.cpu_count(), "clocks": clk.summary()}), flush=True)
     if world > 1:
