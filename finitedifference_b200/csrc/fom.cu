@@ -294,9 +294,9 @@ struct InputFeed {
     int pf_row, ny, last_row, lane;
     bool strip0;
     __device__ __forceinline__ explicit InputFeed(const StepIo &io) {
-        lane = io.lane; ny = io.ny; last_row = ny + kSkew - 1;
-        pf_lane = io.pf + (saddr)(lane * 8);
-        pf_end = pf_lane + (saddr)(kPfDepth * kPfValues * 256);
+        lane = io.lane; ny = keep_reg(io.ny); last_row = keep_reg(ny + kSkew - 1);
+        pf_lane = keep_reg(io.pf + (saddr)(lane * 8));
+        pf_end = keep_reg(pf_lane + (saddr)(kPfDepth * kPfValues * 256));
         pf_d = pf_lane;
         src = io.xin; srcp = io.xwp; lbc_p = io.lbc; cy = io.cy; cyd = io.cyd;
         pf_row = 0;
@@ -321,6 +321,21 @@ struct InputFeed {
         ++pf_row;
         pf_d += (saddr)(kPfValues * 256);
         if (pf_d == pf_end) pf_d = pf_lane;
+    }
+    // the same for a row that is neither the last row of the state nor (inlet strip) past the last grid row
+    __device__ __forceinline__ void step_main() {
+        constexpr int W = 32;
+        static_assert(UNI || !UNI, "");
+        cp_async8(pf_d, src);
+        cp_async8(pf_d + 256, src + W);
+        if (CONT) { cp_async8(pf_d + 512, srcp); cp_async8(pf_d + 768, srcp + W); }
+        if (strip0) { if (lane == 0) cp_async8(pf_d + 1024, lbc_p); ++lbc_p; }
+        src += 2 * W; if (CONT) srcp += 2 * W;
+        ++pf_row;
+        pf_d += (saddr)(kPfValues * 256);
+        if (pf_d == pf_end) pf_d = pf_lane;
+        cp_async_commit();
+        cp_async_wait_pending<kPfDepth - 2>();
     }
     __device__ __forceinline__ void prologue() {             // before the barrier that opens step 0
 #pragma unroll
@@ -366,6 +381,15 @@ struct EdgeGive {
         ++ro; gout += kRecDoubles;
         x_prev = x_sum - x_prev;
     }
+    __device__ __forceinline__ void step_main() {            // the row sent is a grid row for every lane
+        if (give) {
+            double a, b;
+            lds2(x_prev + 32 * 16, a, b);
+            if (out_remote) st_sys2(gout, a, b); else st_volatile2(gout, a, b);
+        }
+        ++ro; gout += kRecDoubles;
+        x_prev = x_sum - x_prev;
+    }
 };
 
 // Levels LO..HI-1 of one trapezoidal time step of one strip.  A time step is K fused Newton
@@ -402,8 +426,8 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
     if (UNI) { cyU = __ldg(io.cy + (ny > 1 ? 1 : 0)); cydU = __ldg(io.cyd + (ny > 1 ? 1 : 0)); }
 
     // level-0 input: rows land in the shared-memory ring one step ahead (dma_part)
-    const saddr pf_lane = io.pf + (saddr)(lane * 8);
-    const saddr pf_end = pf_lane + (saddr)(kPfDepth * kPfValues * 256);
+    const saddr pf_lane = keep_reg(io.pf + (saddr)(lane * 8));
+    const saddr pf_end = keep_reg(pf_lane + (saddr)(kPfDepth * kPfValues * 256));
     saddr pf_rd = pf_lane;                  // slot of the row read this step (running, no modulo)
 
     Level prev[K + 1];        // own cell of the previous step at each level = upper neighbour now
@@ -603,6 +627,20 @@ __device__ __forceinline__ void idle_part(const StepIo &io) {
     if (DUTY == kDutyGive) edge.step();
 }
 
+// A piece that had not arrived when its row was copied into the ring: polled from global (or peer) memory.
+// Out of line: the per-step loop of the data-movement warp stays one run of instructions in the
+// instruction cache.  Inside the per-step loop a plain counter bounds the wait (the producer is running).
+struct PolledPiece { double a, b; unsigned spins; int ok; };
+__device__ __noinline__ PolledPiece poll_piece(const double *gin, bool in_remote) {
+    PolledPiece p{0.0, 0.0, 0u, 1};
+    for (;;) {
+        if (in_remote) ld_sys2(gin, p.a, p.b); else ld_volatile2(gin, p.a, p.b);
+        if (!(is_sentinel(p.a) || is_sentinel(p.b))) return p;
+        if (++p.spins > kSpinLimit) { p.a = 0.0; p.b = 0.0; p.ok = 0; return p; }
+        if (p.spins > 2) spin_pause();
+    }
+}
+
 // The data-movement warp of the CTA: keeps the level-0 input ring kPfDepth-1 rows ahead with
 // cp.async, brings the hand-off blocks of the strip on the left into the shared-memory ring
 // ahead of time (spinning there, off the compute warps' critical path, if the producer is late),
@@ -616,10 +654,11 @@ template <int K, bool CONT, bool UNI>
 __device__ __forceinline__ void dma_part(const StepIo &io) {
     constexpr int NPR = 2 * K + 1 + (CONT ? 1 : 0);
     static_assert(NPR <= 32, "one lane per piece of a record row");
-    const int lane = io.lane, ny = io.ny;
+    const int lane = io.lane, ny = keep_reg(io.ny);
     const int nsteps = ny + kSkew + K;
     int err = 0;
     unsigned misses = 0, spins_total = 0;
+    const double armed = keep_reg(sentinel_value());         // what a consumed piece is overwritten with
 
     // ---- strip-to-strip hand-off: lane p moves piece p of the row records -------------------
     // Every lane runs its own stream of rows, one per step, offset by the Newton level its piece
@@ -640,7 +679,7 @@ __device__ __forceinline__ void dma_part(const StepIo &io) {
     saddr x_cur = p_x + (saddr)(2 * kXRow);                  // buffer of step -1 (odd)
     InputFeed<CONT, UNI> feed(io);                           // the two duties, when no compute warp carries them
     EdgeGive<K, CONT> edge(io);
-    const saddr ring0 = io.ring_in + (saddr)(lane * 16), ring_end = ring0 + (saddr)(kInRing * kRecBytes);
+    const saddr ring0 = keep_reg(io.ring_in + (saddr)(lane * 16)), ring_end = keep_reg(ring0 + (saddr)(kInRing * kRecBytes));
     int rc = -lvl;                                           // row consumed by the call for step s: s + 1 - level
     double *gin = io.edge_in + 2 * lane + (ptrdiff_t)rc * kRecDoubles;
     saddr sl = ring0 + (saddr)(((rc + 1) & (kInRing - 1)) * kRecBytes);          // slot of the row loaded early
@@ -669,28 +708,25 @@ __device__ __forceinline__ void dma_part(const StepIo &io) {
                 if (r < ny) cp_async16(ring0 + (saddr)(r * kRecBytes), io.edge_in + 2 * lane + (size_t)r * kRecDoubles);
         }
     }
-    auto halo = [&]() {
+    // MAIN: every row this call touches is a grid row for every lane (no range tests): steps kMainLo .. ny - kAhead - 2
+    auto halo = [&](auto main_phase) {
+        constexpr bool MAIN = decltype(main_phase)::value;
         double na = 0.0, nb = 0.0;
-        if (take && (unsigned)(rc + 1) < (unsigned)ny) lds2(sl, na, nb);
-        if (take && (unsigned)rc < (unsigned)ny) {
+        if (take && (MAIN || (unsigned)(rc + 1) < (unsigned)ny)) lds2(sl, na, nb);
+        if (take && (MAIN || (unsigned)rc < (unsigned)ny)) {
             if (is_sentinel_hi(va) || is_sentinel_hi(vb)) {          // had not arrived when the row was copied
                 ++misses;
-                unsigned spins = 0;                  // inside the per-step loop: a plain counter (the producer is running)
-                for (;;) {
-                    if (in_remote) ld_sys2(gin, va, vb); else ld_volatile2(gin, va, vb);
-                    if (!(is_sentinel(va) || is_sentinel(vb))) break;
-                    ++spins_total;
-                    if (++spins > kSpinLimit) { err = BFD_ETIMEOUT; va = 0.0; vb = 0.0; break; }
-                    if (spins > 2) spin_pause();
-                }
+                const PolledPiece p = poll_piece(gin, in_remote);
+                va = p.a; vb = p.b; spins_total += p.spins;
+                if (!p.ok) err = BFD_ETIMEOUT;
             }
             sts2(x_cur, va, vb);
 #ifndef BFD_X_NOREARM
-            st_weak2(gin, sentinel_value(), sentinel_value());       // re-arm for the next launch
+            st_weak2(gin, armed, armed);                             // re-arm for the next launch
 #endif
-            if (rc + kAhead < ny) cp_async16(pl, gin + (size_t)kAhead * kRecDoubles);
+            if (MAIN || rc + kAhead < ny) cp_async16(pl, gin + (size_t)kAhead * kRecDoubles);
         }
-        if (!kSplitDuties) edge.step();
+        if (!kSplitDuties) { if (MAIN) edge.step_main(); else edge.step(); }
         va = na; vb = nb;
         ++rc; gin += kRecDoubles;
         sl += (saddr)kRecBytes; if (sl == ring_end) sl = ring0;
@@ -703,16 +739,32 @@ __device__ __forceinline__ void dma_part(const StepIo &io) {
     if (!kSplitDuties) feed.prologue();
     else { cp_async_commit(); cp_async_wait_pending<0>(); }      // the first kAhead rows of the ring
     if (take && (unsigned)rc < (unsigned)ny) lds2(ring0 + (saddr)((rc & (kInRing - 1)) * kRecBytes), va, vb);
-    halo();                                  // "step -1": what lane 0 reads in step 0
+    halo(BoolTag<false>{});                  // "step -1": what lane 0 reads in step 0
     __syncthreads();
+    // head, main (no range tests: rows s + 1 - level .. s + kAhead + 1 - level consumed / copied, row s - 33 - level sent,
+    // row s + kPfDepth - 1 fed are grid rows for every level 0..K), tail; the two edge phases share one copy of the code
+    const int main_lo = kSkew + 2 + K + 1, main_hi = ny - kAhead - 1;
+    int s = 0;
 #pragma unroll 1
-    for (int s = 0; s < nsteps; ++s) {
-        if (!kSplitDuties) feed.step();
-        else { cp_async_commit(); cp_async_wait_pending<kPfDepth - 2>(); }
-        halo();
-        __syncthreads();
+    for (int phase = 0; phase < 2; ++phase) {
+        const int ep_end = phase == 0 ? (main_lo < nsteps ? main_lo : nsteps) : nsteps;
+#pragma unroll 1
+        for (; s < ep_end; ++s) {
+            if (!kSplitDuties) feed.step();
+            else { cp_async_commit(); cp_async_wait_pending<kPfDepth - 2>(); }
+            halo(BoolTag<false>{});
+            __syncthreads();
+        }
+        if (phase == 0 && UNI && !kSplitDuties) {
+#pragma unroll 2
+            for (; s < main_hi; ++s) {
+                feed.step_main();
+                halo(BoolTag<true>{});
+                __syncthreads();
+            }
+        }
     }
-    halo();                                  // what lane 31 published in the last step
+    halo(BoolTag<false>{});                  // what lane 31 published in the last step
     if (io.stats) {
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) {

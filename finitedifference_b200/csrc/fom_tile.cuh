@@ -95,13 +95,7 @@ inline int ld_shared_volatile(const volatile int *p) { std::this_thread::yield()
 // A value the compiler must keep in a register instead of recomputing it where it is used (under
 // register pressure it rematerialises shared-window addresses with S2R SR_CgaCtaId + arithmetic in
 // every wavefront step: profiles/r02_notes.md).
-#ifndef BFD_EMULATE
-__device__ __forceinline__ unsigned keep_reg(unsigned v) { asm volatile("" : "+r"(v)); return v; }
-__device__ __forceinline__ int keep_reg(int v) { asm volatile("" : "+r"(v)); return v; }
-#else
-inline saddr keep_reg(saddr v) { return v; }
-inline int keep_reg(int v) { return v; }
-#endif
+// keep_reg: wavefront.cuh
 
 // All K+1 levels of one trapezoidal time step of one strip, by one warp.  Arithmetic identical to
 // sweep_part up to exact power-of-two rescalings (the 0.5 factors ride on the iterate): the same bits.

@@ -103,6 +103,18 @@ inline void spin_pause() { std::this_thread::yield(); }
 inline unsigned long long global_timer_ns() { return 0; }
 #endif
 
+// keep_reg: stops the compiler from rematerialising a loop-invariant value (shared-window addresses cost an
+// S2R + LEA, constants a MOV each) in every wavefront step: the value stays in the register it is in.
+#ifndef BFD_EMULATE
+__device__ __forceinline__ unsigned keep_reg(unsigned v) { asm volatile("" : "+r"(v)); return v; }
+__device__ __forceinline__ int keep_reg(int v) { asm volatile("" : "+r"(v)); return v; }
+__device__ __forceinline__ double keep_reg(double v) { asm volatile("" : "+d"(v)); return v; }
+#else
+inline saddr keep_reg(saddr v) { return v; }
+inline int keep_reg(int v) { return v; }
+inline double keep_reg(double v) { return v; }
+#endif
+
 __device__ __forceinline__ bool is_sentinel(double x) {
     return (unsigned long long)__double_as_longlong(x) == kSentinelBits;
 }
