@@ -516,20 +516,10 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
             const double Fh = hu * u, Gh = hu * v, Hh = hv * v;
             double DG = prev[k].Gh, DH = prev[k].Hh;
             if (EP) { DG = top ? 0.0 : DG; DH = top ? 0.0 : DH; }
-#ifdef BFD_AU_LATE
-            // level 0 forms Au, Av in this very step: add them last, so that their chain runs beside this one
-            double ru = k == 0 ? u : Au[k] + u;
-            ru = fma(cx, Fh, ru); ru = fma(cy, Gh, ru); ru = fma(ncxl, LF, ru); ru = fma(ncyd, DG, ru);
-            if (k == 0) ru += Au[0];
-            double rv = k == 0 ? v : Av[k] + v;
-            rv = fma(cy, Hh, rv); rv = fma(cx, Gh, rv); rv = fma(ncyd, DH, rv); rv = fma(ncxl, LG, rv);
-            if (k == 0) rv += Av[0];
-#else
             double ru = Au[k] + u;
             ru = fma(cx, Fh, ru); ru = fma(cy, Gh, ru); ru = fma(ncxl, LF, ru); ru = fma(ncyd, DG, ru);
             double rv = Av[k] + v;
             rv = fma(cy, Hh, rv); rv = fma(cx, Gh, rv); rv = fma(ncyd, DH, rv); rv = fma(ncxl, LG, rv);
-#endif
             const double r2 = fma(rv, rv, ru * ru);
             // main phase: every row is a cell; padding columns (last strip) are dropped after the loop
             nrm[k] += EP ? (valid ? r2 : 0.0) : r2;
