@@ -34,8 +34,8 @@ METRIC = "fom_cell_updates_per_s"
 UNIT = "cell-updates/s"
 # Constants read off one ncu capture of the sweep kernel (profiles/r02_fom_chunk_ncu.md).  They describe the
 # kernel SOURCE they were profiled on: the line carries `stale: true` when the sources' hash has moved on.
-NCU_PROFILED_SHA = "345372db62ee8cd2"             # sha256 of csrc/{fom.cu,wavefront.cuh,common.cuh} at profiling time, first 16 hex digits
-NCU_DRAM_BYTES_PER_CELL_UPDATE = 42.8     # dram__bytes_read.sum + dram__bytes_write.sum per cell-update (r02 capture)
+NCU_PROFILED_SHA = "8e68565daebdc74b"             # sha256 of csrc/{fom.cu,wavefront.cuh,common.cuh} at profiling time, first 16 hex digits
+NCU_DRAM_BYTES_PER_CELL_UPDATE = 43.3     # dram__bytes_read.sum + dram__bytes_write.sum per cell-update (r02 capture)
 NCU_FP64_INSTR_PER_CELL_UPDATE = 235.1    # FP64-pipe warp instructions x 32 lanes / real cell-updates of the profiled launch, 4 solves (padding lanes included)
 CPU_SECONDS_PER_CELL_UPDATE = 65e-6       # one core, first time step (5 solves) at 750^2: 36.5 s / 562 500 cells (r01)
 
