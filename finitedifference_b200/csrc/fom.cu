@@ -238,6 +238,8 @@ constexpr int kXchgLevels = kKMax + 2;         // levels 0..K, plus (Fp, Gp) of 
 constexpr int kXRow = 33 * 16;                  // exchange row: slot 0 = halo (last column of the strip on the left), slot l+1 = lane l
 constexpr int kXchgBytes = kXchgLevels * 2 * 2 * kXRow;      // left-neighbour exchange: [level][2 buffers][(Fh,Gh),(pu,pm)][slot]
 constexpr int kPfDepth = 6;                    // rows of level-0 input in flight (cp.async ring)
+constexpr int kPfPending = kPfDepth - 3;       // commit groups that may be in flight after a step's wait: rows <= s + 2 have landed
+                                               // after step s, i.e. the row used in step s + 1 and the one it loads ahead
 constexpr int kPfValues = 7;                   // u, v, up, vp (CONT), lbc (inlet lane), cy, cyd (non-uniform grids)
 constexpr int kPfBytes = kPfDepth * kPfValues * 32 * 8;
 
@@ -286,7 +288,7 @@ constexpr int kMainUnroll = BFD_UNROLL;       // wavefront steps per trip of the
 constexpr bool kSplitDuties = BFD_SPLIT && (kWarpsPerStrip == 4);
 
 // kDutyFeed: keeps the level-0 input ring kPfDepth-1 rows ahead with cp.async, one row and one commit
-// group per step: "all but the newest kPfDepth-2 groups have landed" = "the row of the next step is there".
+// group per step: "all but the newest kPfPending groups have landed" = "the rows of the next two steps are there".
 template <bool CONT, bool UNI>
 struct InputFeed {
     saddr pf_lane, pf_end, pf_d;
@@ -335,17 +337,17 @@ struct InputFeed {
         pf_d += (saddr)(kPfValues * 256);
         if (pf_d == pf_end) pf_d = pf_lane;
         cp_async_commit();
-        cp_async_wait_pending<kPfDepth - 2>();
+        cp_async_wait_pending<kPfPending>();
     }
     __device__ __forceinline__ void prologue() {             // before the barrier that opens step 0
 #pragma unroll
         for (int i = 0; i < kPfDepth - 1; ++i) { issue(); cp_async_commit(); }
-        cp_async_wait_pending<kPfDepth - 2>();
+        cp_async_wait_pending<kPfPending>();
     }
     __device__ __forceinline__ void step() {                 // row s + kPfDepth - 1: refills the slot read one step ago
         issue();
         cp_async_commit();
-        cp_async_wait_pending<kPfDepth - 2>();
+        cp_async_wait_pending<kPfPending>();
     }
 };
 
@@ -446,6 +448,18 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
     auto xc_level = [](int k, int buf) { return (saddr)((k * 2 + buf) * 2 * kXRow); };
     InputFeed<CONT, UNI> feed(io);
     EdgeGive<K, CONT> edge(io);
+    // level-0 input of the NEXT step, read from the ring at the end of a step: its shared-memory latency is
+    // spent beside the tail of this step's chain and the barrier instead of at the head of the next chain
+    struct { double u, v, up, vp, lb, cy, cyd; } nx = {0.0, 0.0, 0.0, 0.0, 0.0, cyU, cydU};
+    auto load_row = [&]() {
+        const saddr d = pf_rd;
+        pf_rd += (saddr)(kPfValues * 256);
+        if (pf_rd == pf_end) pf_rd = pf_lane;
+        nx.u = lds(d); nx.v = lds(d + 256);
+        if (CONT) { nx.up = lds(d + 512); nx.vp = lds(d + 768); }
+        if (io.inlet) nx.lb = lds(d + 1024);
+        if (!UNI) { nx.cy = lds(d + 1280); nx.cyd = lds(d + 1536); }
+    };
 
     // One wavefront step.  EP ("edge phase"): some lane's row is outside the grid at some level
     // (first 32+K and last 31+K steps); the main phase runs without row masks.
@@ -454,13 +468,11 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
         const int rbuf = (s + 1) & 1, wbuf = s & 1;      // exchange buffers: written last step / this step
         double up = 0.0, vp = 0.0, lb = 0.0;
         if (FIRST) {
-            const saddr d = pf_rd;
-            pf_rd += (saddr)(kPfValues * 256);
-            if (pf_rd == pf_end) pf_rd = pf_lane;
-            xu[0] = lds(d); xv[0] = lds(d + 256);
-            up = CONT ? lds(d + 512) : xu[0]; vp = CONT ? lds(d + 768) : xv[0];
-            if (io.inlet) lb = lds(d + 1024);
-            if (!UNI) { Cy[0] = lds(d + 1280); Cyd[0] = lds(d + 1536); }
+            // the row of this step was loaded before the barrier that opened it (load_row)
+            xu[0] = nx.u; xv[0] = nx.v;
+            up = CONT ? nx.up : xu[0]; vp = CONT ? nx.vp : xv[0];
+            lb = nx.lb;
+            if (!UNI) { Cy[0] = nx.cy; Cyd[0] = nx.cyd; }
         } else {
             // x_LO and the level-independent terms of row s - lane - LO, from the previous warp
             const saddr h = hand_in + (saddr)(rbuf * 3 * kPairRow);
@@ -566,12 +578,14 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
             sts2(h + kPairRow, Au[HI], Av[HI]);
             if (!UNI) sts2(h + 2 * kPairRow, Cy[HI], Cyd[HI]);
         }
+        if (FIRST) load_row();               // row s + 1: landed before the barrier that opened this step
         __syncthreads();
     };
 
     if (DUTY == kDutyFeed) feed.prologue();
     if (DUTY == kDutyGive) edge.step();
-    __syncthreads();      // row 0 and the first hand-off block are in shared memory (dma_part / the feed duty)
+    __syncthreads();      // rows 0, 1 and the first hand-off block are in shared memory (dma_part / the feed duty)
+    if (FIRST) load_row();
     // head (rows entering the strip), main (0 < row < ny for every lane and level), tail; the
     // two edge phases share one copy of the masked body (code size: instruction cache)
     const int head_end = nsteps < kSkew + K + 1 ? nsteps : kSkew + K + 1;
@@ -725,7 +739,7 @@ __device__ __forceinline__ void dma_part(const StepIo &io) {
     };
 
     // One commit group per step (the feed duty's row rides in it when this warp carries that duty): "all
-    // but the newest kPfDepth-2 groups" = "the hand-off rows copied >= 4 steps ago have landed".
+    // but the newest kPfPending groups" = "the hand-off rows copied >= 3 steps ago have landed".
     if (!kSplitDuties) feed.prologue();
     else { cp_async_commit(); cp_async_wait_pending<0>(); }      // the first kAhead rows of the ring
     if (take && (unsigned)rc < (unsigned)ny) lds2(ring0 + (saddr)((rc & (kInRing - 1)) * kRecBytes), va, vb);
@@ -741,7 +755,7 @@ __device__ __forceinline__ void dma_part(const StepIo &io) {
 #pragma unroll 1
         for (; s < ep_end; ++s) {
             if (!kSplitDuties) feed.step();
-            else { cp_async_commit(); cp_async_wait_pending<kPfDepth - 2>(); }
+            else { cp_async_commit(); cp_async_wait_pending<kPfPending>(); }
             halo(BoolTag<false>{});
             __syncthreads();
         }
