@@ -269,7 +269,7 @@ struct StepIo {
 
 struct Level {            // what a cell keeps for its lower neighbour (D) at one level
     double Gh, Hh;        // current-iterate flux parts uv/2, v^2/2
-    double pm, pvv;       // v*du + u*dv, v*dv
+    double pm, pvv;       // (v*du + u*dv) / 2, v*dv
 };
 
 // Two pieces of the CTA's data movement are duties that any warp can carry: they touch nothing but
@@ -422,7 +422,11 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
 
     const bool colok = io.colok;
 
-    const double cx = io.cx, cxl = io.cxl, hcx = 0.5 * io.cx, hcxl = 0.5 * io.cxl, ncxl = -io.cxl;
+    // The 0.5 factors of the Jacobian ride on the iterate (hu = u/2, hv = v/2) and on the published pair
+    // (hpm = (v du + u dv)/2), exact power-of-two rescalings: the same bits as with halved coefficients, and
+    // four coefficient registers (cx, cxl, cy, cyd) instead of eight -- ptxas recomputed the halved ones with
+    // four DMULs per level and step rather than hold them.
+    const double cx = io.cx, cxl = io.cxl, ncxl = -io.cxl;
     const double src = io.src;
     double cyU = 0.0, cydU = 0.0;
     if (UNI) { cyU = __ldg(io.cy + (ny > 1 ? 1 : 0)); cydU = __ldg(io.cyd + (ny > 1 ? 1 : 0)); }
@@ -492,7 +496,7 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
             const bool valid = rowok && colok;
             const bool top = EP ? (rk <= 0) : false;   // no upper neighbour (row -1 is not a cell)
             const double cy = UNI ? cyU : Cy[k], cyd = UNI ? cydU : Cyd[k];
-            const double hcy = 0.5 * cy, hcyd = 0.5 * cyd, ncyd = -cyd;
+            const double ncyd = -cyd;
 
             // left neighbour (r, c-1): the pairs slot `lane` received in the previous step -- from
             // lane - 1, or (lane 0) from the strip on the left through the data-movement warp
@@ -541,15 +545,15 @@ __device__ __forceinline__ void sweep_part(const StepIo &io) {
             if (k < K) {
                 double Dpm = prev[k].pm, Dpvv = prev[k].pvv;
                 if (EP) { Dpm = top ? 0.0 : Dpm; Dpvv = top ? 0.0 : Dpvv; }
-                const double bu_ = fma(hcyd, Dpm, fma(cxl, Lpu, ru));
-                const double bv_ = fma(cyd, Dpvv, fma(hcxl, Lpm, rv));
-                const double d00 = fma(cx, u, fma(hcy, v, 1.0));
-                const double d11 = fma(cy, v, fma(hcx, u, 1.0));
-                const double d01 = hcy * u, d10 = hcx * v;
+                const double bu_ = fma(cyd, Dpm, fma(cxl, Lpu, ru));       // Dpm, Lpm hold the halved pair
+                const double bv_ = fma(cyd, Dpvv, fma(cxl, Lpm, rv));
+                const double d00 = fma(cx, u, fma(cy, hv, 1.0));
+                const double d11 = fma(cy, v, fma(cx, hu, 1.0));
+                const double d01 = cy * hu, d10 = cx * hv;
                 const double inv = rcp_fast(fma(d00, d11, -(d01 * d10)));
                 const double du = fma(d11, bu_, -(d01 * bv_)) * inv;
                 const double dv = fma(d00, bv_, -(d10 * bu_)) * inv;
-                const double pu = u * du, pm = fma(v, du, u * dv);
+                const double pu = u * du, pm = fma(hv, du, hu * dv);       // (v du + u dv) / 2
                 prev[k].pm = pm; prev[k].pvv = v * dv;
                 sts2(xc_own + xc_level(k, wbuf) + kXRow, pu, pm);
                 xu[k + 1] = u - du; xv[k + 1] = v - dv;

@@ -129,7 +129,7 @@ __device__ __forceinline__ double sentinel_value() { return __longlong_as_double
 // first column of the strip on its right needs from its left neighbour, for every Newton level
 // of the fused pass: NPR 16-byte pieces per row
 //     piece 2k   = (Fh_k, Gh_k)      current-iterate flux parts of level k  (k = 0..K)
-//     piece 2k+1 = (pu_k, pm_k)      u*du and v*du + u*dv of level k        (k < K)
+//     piece 2k+1 = (pu_k, pm_k)      u*du and (v*du + u*dv)/2 of level k    (k < K)
 //     piece 2K+1 = (Fp, Gp)          previous-time-level flux parts (continuation passes only)
 // The producer's data-movement warp stores each piece the step after it was computed (one
 // 16-byte relaxed store per lane); the consumer's copies a block of kEdgeBlock rows
