@@ -34,9 +34,9 @@ METRIC = "fom_cell_updates_per_s"
 UNIT = "cell-updates/s"
 # Constants read off one ncu capture of the sweep kernel (profiles/r02_fom_chunk_ncu.md).  They describe the
 # kernel SOURCE they were profiled on: the line carries `stale: true` when the sources' hash has moved on.
-NCU_PROFILED_SHA = "8e68565daebdc74b"             # sha256 of csrc/{fom.cu,wavefront.cuh,common.cuh} at profiling time, first 16 hex digits
-NCU_DRAM_BYTES_PER_CELL_UPDATE = 43.3     # dram__bytes_read.sum + dram__bytes_write.sum per cell-update (r02 capture)
-NCU_FP64_INSTR_PER_CELL_UPDATE = 235.1    # FP64-pipe warp instructions x 32 lanes / real cell-updates of the profiled launch, 4 solves (padding lanes included)
+NCU_PROFILED_SHA = "c7c8e73c9e2256ab"             # sha256 of csrc/{fom.cu,wavefront.cuh,common.cuh} at profiling time, first 16 hex digits
+NCU_DRAM_BYTES_PER_CELL_UPDATE = 43.0     # dram__bytes_read.sum + dram__bytes_write.sum per cell-update (r02 capture)
+NCU_FP64_INSTR_PER_CELL_UPDATE = 227.3    # FP64-pipe warp instructions x 32 lanes / real cell-updates of the profiled launch, 4 solves (padding lanes included)
 CPU_SECONDS_PER_CELL_UPDATE = 65e-6       # one core, first time step (5 solves) at 750^2: 36.5 s / 562 500 cells (r01)
 
 
@@ -252,7 +252,7 @@ def main():
     dfma_peak = R.dfma_peak_tflops(dev, lib)
     dgemm_peak = R.dgemm_peak_tflops(dev)
     solves = float(its.mean()) - 1.0
-    fp64_instr = NCU_FP64_INSTR_PER_CELL_UPDATE * (11.0 + 46.0 * solves + 17.0) / (11.0 + 46.0 * 4 + 17.0)   # scaled to this run's solves
+    fp64_instr = NCU_FP64_INSTR_PER_CELL_UPDATE * (10.0 + 46.0 * solves + 18.0) / (10.0 + 46.0 * 4 + 18.0)   # Au/Av 10, a solve level 46, the last residual 18 (SASS counts): scaled to this run's solves
     fp64_tflops = 2e-12 * fp64_instr * (B * cells * T) / run_s
     sha = kernel_source_sha()
     stale = sha != NCU_PROFILED_SHA
