@@ -87,7 +87,10 @@ int bfd_fom_set_initial(const bfd_fom_desc *d, void *workspace, const double *w0
                         size_t w0_stride, void *stream);
 
 /* Advance every sample num_steps steps (Newton to rel_tol each step); returns when done.
- * h_pinned: >= 64 bytes of page-locked host memory used to poll completion.
+ * h_pinned: >= 64 bytes of page-locked host memory used to poll completion.  When the memory is mapped into
+ * the device's address space (cudaHostAlloc / cudaHostRegister memory is: cudaHostGetDevicePointer succeeds) the
+ * GPU writes its status words there itself after every launch (one-thread kernel, no copy engine: a small
+ * device-to-host copy would wait behind whatever bulk copies the process has in flight); otherwise they are copied.
  * On return h_pinned[0..3] (int32) = {samples finished, device error code, kernels launched,
  * time steps that were redone or continued because the speculated solve count was wrong}. */
 int bfd_fom_run(const bfd_fom_desc *d, void *workspace, const bfd_fom_coef *coef, void *h_pinned,
