@@ -258,7 +258,8 @@ class SnapshotSweep:
                             tw = time.perf_counter()
                             free.wait()                 # its previous content has reached the host
                             free.clear()
-                            stats["stage_wait"] += time.perf_counter() - tw
+                            with lock:
+                                stats["stage_wait"] += time.perf_counter() - tw
                             solver.snapshots_device(j, layout=1, out=buf)
                             exported = torch.cuda.Event()
                             exported.record(stream)
@@ -266,7 +267,8 @@ class SnapshotSweep:
                             if pooled:
                                 tw = time.perf_counter()
                                 dst = self._get_pool().get()
-                                stats["pool_wait"] += time.perf_counter() - tw
+                                with lock:
+                                    stats["pool_wait"] += time.perf_counter() - tw
                             else:
                                 dst = out[i] if isinstance(out[i], torch.Tensor) else torch.from_numpy(out[i])
                             copy_q.put((exported, buf, dst, i, pooled, free))
