@@ -13,6 +13,11 @@ residual (minimum-norm solution through ``eigh`` when the columns are dependent)
 SciPy installed in this image (1.18) on problems with a unique solution, and check the KKT conditions
 where the solution is not unique (more columns than rows, the reference's case: the active set is
 then rounding-sensitive).
+
+Two more of the reference's trainers are compositions over the same pieces: its own ``lsqnonneg``
+(BurgersFD_CleanCoarse/lsqnonneg.py:4, MATLAB's active-set method with an absolute tolerance, a relative-error
+early stop and a cap on the support) and the three-level block training of
+run_HPROM_ecsw_multilevel_complete.py:95-177.
 """
 from __future__ import annotations
 
@@ -170,3 +175,143 @@ def ecsw_weights(C, blocks=20, *, maxiter=None, device=None):
             x, _, _ = nnls_tensor(c, c.sum(dim=1), maxiter if maxiter else 9999999999)   # the reference's maxiter (:83)
             out.append(x.cpu().numpy())
     return np.hstack(out)
+
+
+def lsqnonneg_tensor(C: torch.Tensor, d: torch.Tensor, x0=None, tol=None, itmax_factor=100, max_support=None,
+                     rel_err_thresh=0.01):
+    """The reference's ``lsqnonneg`` (BurgersFD_CleanCoarse/lsqnonneg.py:4-109) on C's device: returns
+    ``(x, resnorm, residual)`` with ``resnorm = sum(residual**2)``.
+
+    Same rules as the reference's: tolerance ``10 * 2.22e-16 * sum|C| * (max(C.shape) + 1)`` (:20-21; its
+    ``norm1`` is the sum of all absolute entries), the entering variable is the largest dual among the zero set
+    (:45-47), a passive solution with an entry ``<= tol`` steps back along ``x + alpha (z - x)`` and drops
+    ``|x| < tol`` (:66-79), and after every outer iteration the loop stops once ``||resid|| / ||d|| <
+    rel_err_thresh`` (default 0.01: the reference's default is an APPROXIMATE fit) or the support has reached
+    ``max_support`` (:93-98).  The reference solves each passive set with ``pinv`` of the column-masked matrix
+    (:58, :82); here it is the Cholesky factor of the passive Gram block with one refinement step, or its
+    eigen-decomposition when the columns are dependent -- the same minimum-norm solution.  ``it > itmax_factor
+    * n`` inner iterations raise, as in the reference (:68-71)."""
+    if C.ndim != 2 or d.ndim != 1 or C.shape[0] != d.shape[0]:
+        raise ValueError(f"incompatible shapes {tuple(C.shape)} and {tuple(d.shape)}")
+    C, d = C.to(torch.float64), d.to(torch.float64)
+    m, n = C.shape
+    dev = C.device
+    if tol is None:
+        tol = 10.0 * 2.22e-16 * float(C.abs().sum()) * (max(m, n) + 1)
+    x = torch.zeros(n, dtype=torch.float64, device=dev)
+    if x0 is not None:
+        x0 = torch.as_tensor(x0, dtype=torch.float64, device=dev)
+        if not bool((x0 < 0).any()):
+            x = x0.clone()
+    CtC, Ctd = C.T @ C, C.T @ d
+    passive = torch.zeros(n, dtype=torch.bool, device=dev)
+    fac = _PassiveFactor(CtC)
+
+    def solve_passive():
+        z = torch.zeros(n, dtype=torch.float64, device=dev)
+        if not fac.idx:
+            return z
+        idx = torch.tensor(fac.idx, dtype=torch.long, device=dev)
+        Cp = C[:, idx]
+        if fac.ok:
+            zp = torch.cholesky_solve(Ctd[idx][:, None], fac.L)[:, 0]
+            zp = zp + torch.cholesky_solve((Cp.T @ (d - Cp @ zp))[:, None], fac.L)[:, 0]
+        else:
+            lam, Q = torch.linalg.eigh(CtC[idx][:, idx])
+            keep = lam > lam.max() * len(fac.idx) * np.finfo(np.float64).eps
+            zp = Q[:, keep] @ ((Q[:, keep].T @ Ctd[idx]) / lam[keep])
+        z[idx] = zp
+        return z
+
+    resid = d - C @ x
+    w = C.T @ resid
+    it, itmax = 0, int(itmax_factor) * n
+    dnorm = float(torch.linalg.norm(d))
+    while not bool(passive.all()):
+        cand = torch.where(passive, torch.full_like(w, -np.inf), w)
+        t = int(torch.argmax(cand))
+        if not float(cand[t]) > tol:
+            break
+        passive[t] = True
+        fac.add(t)
+        z = solve_passive()
+        while bool((z[passive] <= tol).any()):
+            it += 1
+            if it > itmax:
+                raise RuntimeError(f"Iteration limit ({it}) exceeded. Increase tolerance tol "
+                                   f"(max_error={float(z[passive].max())}).")
+            qq = passive & (z <= tol)
+            alpha = float((x[qq] / (x[qq] - z[qq])).min())
+            x = x + alpha * (z - x)
+            passive = passive & ~(x.abs() < tol)
+            fac.keep(passive)
+            z = solve_passive()
+        x = z
+        resid = d - C @ x
+        w = C.T @ resid
+        rel_err = float(torch.linalg.norm(resid)) / dnorm if dnorm > 0 else 0.0
+        if rel_err < rel_err_thresh:
+            break
+        if max_support is not None and int((x > 0).sum()) >= max_support:
+            break
+    return x, float((resid * resid).sum()), resid
+
+
+def lsqnonneg(C, d, x0=None, tol=None, itmax_factor=100, max_support=None, rel_err_thresh=0.01, *, device=None):
+    """Drop-in for the reference's ``lsqnonneg(C, d, ...)`` (same arguments, same return triple as NumPy
+    arrays / float); the work runs on the GPU."""
+    dev = _require_cuda(device if device is not None else (C.device if isinstance(C, torch.Tensor) and C.is_cuda else None))
+    Ct = C if isinstance(C, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(C, dtype=np.float64))
+    dt = d if isinstance(d, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(d, dtype=np.float64).ravel())
+    with torch.cuda.device(dev):
+        x, resnorm, resid = lsqnonneg_tensor(Ct.to(dev), dt.to(dev), x0, tol, itmax_factor, max_support, rel_err_thresh)
+    return x.cpu().numpy(), resnorm, resid.cpu().numpy()
+
+
+def multilevel_weights_tensor(C: torch.Tensor, levels=(12, 2), maxiter=None):
+    """The three-level training of run_HPROM_ecsw_multilevel_complete.py:95-177 on C's device.
+
+    Level 1 (:95-117): the columns of ``C`` in ``levels[0]`` blocks (``np.array_split``), each block trained
+    against its own column sum; the non-zero weights survive.  Level 2 (:119-155): the surviving columns in
+    ``levels[1]`` blocks, again each against its own column sum (the script forms ``C_level2 @ z_level2`` at :131
+    and does not use it, so from here on the weights integrate the plain sum of the surviving columns, not the
+    level-1 quadrature: kept as the script has it).  Last level (:157-177): one NNLS on what is left against ``C_last @ z`` with ``z`` the
+    weights of the level before.  Returns ``(weights (n,), rnorm of the last solve, columns alive after each
+    level)``.  Any number of block levels is accepted; ``levels=()`` is a single NNLS against the column sum."""
+    n = C.shape[1]
+    dev = C.device
+    maxiter = maxiter if maxiter else 9999999999            # the scripts' maxiter (run_HPROM_ecsw_joshua.py:83)
+    alive = torch.arange(n, device=dev)
+    z = None
+    sizes = []
+    for li, nb in enumerate(levels):
+        Ck = C if li == 0 else C[:, alive]                   # level 1 works on views of C: no 21 GB gather
+        width = Ck.shape[1]
+        bounds = np.cumsum([0] + [len(p) for p in np.array_split(np.arange(width), nb)])
+        keep, wts = [], []
+        for lo, hi in zip(bounds[:-1], bounds[1:]):
+            c = Ck[:, int(lo):int(hi)]
+            x, _, _ = nnls_tensor(c, c.sum(dim=1), maxiter)
+            nz = torch.nonzero(x)[:, 0]
+            keep.append(nz + int(lo))
+            wts.append(x[nz])
+        sel = torch.cat(keep) if keep else torch.zeros(0, dtype=torch.long, device=dev)
+        z = torch.cat(wts) if wts else torch.zeros(0, dtype=torch.float64, device=dev)
+        alive = alive[sel]
+        sizes.append(int(alive.numel()))
+    Cl = C[:, alive]
+    b = Cl @ z if z is not None else Cl.sum(dim=1)
+    w, rnorm, _ = nnls_tensor(Cl, b, maxiter)
+    out = torch.zeros(n, dtype=torch.float64, device=dev)
+    out[alive] = w
+    return out, rnorm, sizes
+
+
+def ecsw_weights_multilevel(C, levels=(12, 2), *, maxiter=None, device=None):
+    """``multilevel_weights_tensor`` for a NumPy array or CUDA tensor ``C (k*n_snaps, n_cells)``: returns the
+    NumPy weight vector ``(n_cells,)`` (the script's ``weights_interior``, :171-172)."""
+    dev = _require_cuda(device if device is not None else (C.device if isinstance(C, torch.Tensor) and C.is_cuda else None))
+    Ct = C if isinstance(C, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(C, dtype=np.float64))
+    with torch.cuda.device(dev):
+        w, _, _ = multilevel_weights_tensor(Ct.to(dev), levels, maxiter)
+    return w.cpu().numpy()
