@@ -92,15 +92,42 @@ def bind_host_to_gpu_node(device=None):
         return None
 
 
-def save_sink(snap_folder="param_snaps", name_fn=None):
+def save_sink(snap_folder="param_snaps", name_fn=None, dtype=None, time_stride=1):
     """A sink that writes ``param_snaps/mu1_<..>+mu2_<..>.npy`` files interchangeable with the
-    reference's cache (``load_or_compute_snaps``, hypernet2D.py:3187-3221)."""
+    reference's cache (``load_or_compute_snaps``, hypernet2D.py:3187-3221): by default the same
+    ``(2N, T+1)`` float64 C-order bytes ``np.save`` gives the reference.
+
+    Two storage options the reference does not have, for sweeps whose files are the
+    bottleneck: ``dtype=np.float32`` halves them, ``time_stride=s`` keeps every s-th time level (columns
+    ``0, s, 2s, ...``; the last level is kept as well when ``T`` is not a multiple of ``s``).  Such files carry
+    a ``.f32`` / ``.every<s>`` tag before ``.npy`` so that the reference's loader never mistakes them for a
+    full trajectory."""
     from .hypernet2D import param_to_snap_fn
     os.makedirs(snap_folder, exist_ok=True)
+    time_stride = int(time_stride)
+    if time_stride < 1:
+        raise ValueError("time_stride must be >= 1")
+    dt_ = None if dtype is None else np.dtype(dtype)
+    if dt_ is not None and dt_ not in (np.dtype(np.float64), np.dtype(np.float32)):
+        raise ValueError("dtype must be float64 or float32")
 
     def sink(index, mu, snaps):
         fn = name_fn(mu) if name_fn else param_to_snap_fn(list(mu), snap_folder=snap_folder)
-        np.save(fn, snaps)
+        out = snaps
+        tag = ""
+        if time_stride > 1:
+            cols = list(range(0, snaps.shape[1], time_stride))
+            if cols[-1] != snaps.shape[1] - 1:
+                cols.append(snaps.shape[1] - 1)
+            out = snaps[:, cols]
+            tag += f".every{time_stride}"
+        if dt_ is not None and dt_ != out.dtype:
+            out = out.astype(dt_)
+            tag += ".f32"
+        if tag:
+            root, ext = os.path.splitext(fn)
+            fn = root + tag + ext
+        np.save(fn, np.ascontiguousarray(out))
     return sink
 
 
