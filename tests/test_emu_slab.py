@@ -55,11 +55,13 @@ def run_group(lib, n_x, n_y, steps, mu, world, **kw):
     (3, 96, dict(newton_hint=1)),                       # under-speculation: continuation passes across ranks
     (2, 64, dict(newton_hint=6)),                       # over-speculation: strict redo across ranks
     (2, 64, dict(chunk_steps=1)),                       # one step per launch: the launch hand-shake every step
+    (2, 64, dict(n_y=60)),                              # tall enough for the unmasked main phases, records crossing ranks
     (2, 72, dict(kernel="tile")),                       # fom_tile_kernel across ranks (peer records, system-scope control)
     (3, 96, dict(kernel="tile", newton_hint=1)),
 ])
 def test_slabs_match_oracle(lib, world, n_x, kw):
-    n_y, steps, mu = 12, 3, [4.75, 0.02]
+    kw = dict(kw)
+    n_y, steps, mu = kw.pop("n_y", 12), 3, [4.75, 0.02]
     snaps, its, ref, ref_its, stats = run_group(lib, n_x, n_y, steps, mu, world, **kw)
     err = (np.linalg.norm(snaps - ref, axis=0) / np.linalg.norm(ref, axis=0)).max()
     assert err < 1e-10, err
