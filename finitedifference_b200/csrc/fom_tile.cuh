@@ -1,8 +1,8 @@
 // fom_tile_kernel: the FOM sweep with one WARP per (strip, time step) and kTileDepth consecutive time
 // steps of a strip in flight inside one CTA.  Included by fom.cu (shares FomArgs, the verdict /
 // commit logic and the strip-to-strip hand-off records with fom_chunk_kernel).  Selectable variant
-// (bfd_fom_desc.kernel = 1); fom_chunk_kernel stays the default because it is 6 % faster on B200
-// (37.2 vs 34.5-35.2 G cell-updates/s at the bench's shape) -- what was tried and measured is in
+// (bfd_fom_desc.kernel = 1); fom_chunk_kernel stays the default because it is faster on B200
+// (37.2, later 39.4, vs 34.5-35.2 G cell-updates/s at the bench's shape) -- what was tried and measured is in
 // profiles/r02_notes.md and DESIGN.md 4.1b.
 //
 // Why it was built: fom_chunk_kernel splits the K+1 Newton levels of a time step between four warps
