@@ -54,7 +54,14 @@ static inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return cudaSuccess
 static inline cudaError_t cudaEventDestroy(cudaEvent_t) { return cudaSuccess; }
 static inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }
 static inline cudaError_t cudaGetDevice(int *d) { *d = 0; return cudaSuccess; }
-static inline cudaError_t cudaHostGetDevicePointer(void **d, void *h, unsigned) { *d = h; return cudaSuccess; }
+// page-locked memory is "mapped" unless a test says otherwise (bfd_fom_run then polls through copies)
+inline int &emu_host_unmapped_flag() { static int v = 0; return v; }
+extern "C" __attribute__((used, weak)) void emu_set_host_unmapped(int v) { emu_host_unmapped_flag() = v; }
+static inline cudaError_t cudaHostGetDevicePointer(void **d, void *h, unsigned) {
+    if (emu_host_unmapped_flag()) return (cudaError_t)1;
+    *d = h;
+    return cudaSuccess;
+}
 // a "device" array is a host array here, so its address is the symbol's own
 template <class T> static inline cudaError_t cudaGetSymbolAddress(void **p, T &sym) { *p = (void *)&sym; return cudaSuccess; }
 

@@ -44,6 +44,22 @@ def test_emulated_fom_matches_oracle(lib, nx, ny, mus, kw):
         assert np.all(rel[m] < 1e-12)
 
 
+def test_emulated_fom_polls_through_copies_when_the_status_memory_is_not_mapped(lib):
+    """bfd_fom_run writes its status words into the caller's page-locked memory from the GPU when that memory is
+    mapped (fom_status_kernel), and falls back to small device-to-host copies when it is not: same trajectory,
+    same counts either way."""
+    nx = ny = 16
+    gx, gy = orc.make_2D_grid(0, 100, 0, 100, nx, ny)
+    w0 = np.ones(2 * nx * ny)
+    mapped = E.fom_run(lib, gx, gy, w0, 0.05, 3, [[4.75, 0.02]], chunk_steps=1)
+    lib.emu_set_host_unmapped(1)
+    try:
+        copied = E.fom_run(lib, gx, gy, w0, 0.05, 3, [[4.75, 0.02]], chunk_steps=1)
+    finally:
+        lib.emu_set_host_unmapped(0)
+    assert np.array_equal(mapped[0], copied[0]) and np.array_equal(mapped[1], copied[1])
+
+
 def test_emulated_fom_golden(lib, golden):
     g = golden("fom_n16.npz")
     n = int(g["n"])
