@@ -73,15 +73,39 @@ def workload_config(n, T, B, extra=None):
 
 # ---- the reference's CPU path (oracle port: sparse Jacobian + SuperLU, as the reference does) -------------
 def _cpu_band(job):
-    """One time step of one mu on a band of `rows` grid rows of the n-column fine grid (same dx, dy, dt)."""
+    """One time step of one mu on a band of `rows` grid rows of the n-column fine grid (same dx, dy, dt): the
+    UNMODIFIED reference function when oracle/_ref/ has been made (oracle/make_ref.py), else the oracle port.
+    Returns (seconds, residual evaluations, kind)."""
     n, rows, mu = job
     for v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
         os.environ[v] = "1"
     from oracle import burgers_oracle as orc
+    from oracle import make_ref
     gx, gy = orc.make_2D_grid(0, 100, 0, 100.0 * rows / n, n, rows)
+    w0 = np.ones(2 * n * rows)
+    ref = make_ref.load()
+    if ref is not None:
+        import contextlib
+        import io
+        counts = []
+        newton = ref.newton_raphson
+
+        def counted(*a, **k):                      # hypernet2D.py:1887: returns (x, resnorms)
+            out = newton(*a, **k)
+            counts.append(len(out[1]))
+            return out
+        ref.newton_raphson = counted
+        try:
+            with contextlib.redirect_stdout(io.StringIO()):
+                t0 = time.perf_counter()
+                ref.inviscid_burgers_implicit2D(gx, gy, w0, DT, 1, mu)          # hypernet2D.py:72
+                dt = time.perf_counter() - t0
+        finally:
+            ref.newton_raphson = newton
+        return dt, sum(counts), "reference"
     t0 = time.perf_counter()
-    _, hist = orc.fom_trajectory(gx, gy, np.ones(2 * n * rows), DT, 1, mu, return_info=True)
-    return time.perf_counter() - t0, sum(len(h) for h in hist)
+    _, hist = orc.fom_trajectory(gx, gy, w0, DT, 1, mu, return_info=True)
+    return time.perf_counter() - t0, sum(len(h) for h in hist), "port"
 
 
 def cpu_sample(n, rows, procs, pool=None):
@@ -91,6 +115,8 @@ def cpu_sample(n, rows, procs, pool=None):
     mus = [[MU1_RANGE[0] + (MU1_RANGE[1] - MU1_RANGE[0]) * (i + 0.5) / procs, 0.02] for i in range(procs)]
     own = pool is None
     if own:
+        from oracle import make_ref
+        make_ref.load()                 # imported once here; the forked workers inherit it (no import inside the timed region)
         pool = mp.get_context("fork").Pool(procs)
     try:
         t0 = time.perf_counter()
@@ -100,10 +126,13 @@ def cpu_sample(n, rows, procs, pool=None):
         if own:
             pool.close()
     evals = [r[1] for r in res]
-    return {"value": procs * n * rows / wall, "unit": UNIT, "cores": procs, "kind": "port", "seconds": wall,
+    kind = "reference" if all(r[2] == "reference" for r in res) else "port"
+    what = ("the UNMODIFIED reference function inviscid_burgers_implicit2D (oracle/_ref, made by oracle/make_ref.py)"
+            if kind == "reference" else "the oracle port of the reference's path")
+    return {"value": procs * n * rows / wall, "unit": UNIT, "cores": procs, "kind": kind, "seconds": wall,
             "sample": f"first time step of {procs} mu in parallel (one process per core, {os.cpu_count()} logical CPUs) on a "
                       f"{n} x {rows} band of the {n} x {n} grid (same dx, dy, dt), {min(evals)}-{max(evals)} residual "
-                      f"evaluations each, {wall:.1f} s wall; the reference's own path: sparse Jacobian + SuperLU spsolve",
+                      f"evaluations each, {wall:.1f} s wall; {what}: sparse Jacobian + SuperLU spsolve",
             "solves_per_step": float(np.mean(evals)) - 1.0}
 
 
@@ -121,14 +150,17 @@ def host_cores():
 
 
 def run_reference_arm(args, rank, world):
-    """--impl reference: the reference algorithm's CPU path (oracle port) on all host cores.  A bench step is a
-    bounded sample of the workload, sized so that warm-up + timed steps end within ~150 s."""
+    """--impl reference: the reference's CPU path on all host cores -- the unmodified reference function when
+    oracle/_ref/ exists (oracle/make_ref.py; `kind: "reference"`), else the oracle port (`kind: "port"`).  A bench
+    step is a bounded sample of the workload, sized so that warm-up + timed steps end within ~150 s."""
     if rank != 0:
         return
     import multiprocessing as mp
     n, procs = args.grid, host_cores()
     total = args.warmup + args.steps
     rows = cpu_rows(n, procs, 150.0 / max(total, 1))
+    from oracle import make_ref
+    make_ref.load()                     # the reference's module, when oracle/_ref/ exists: imported before the fork
     pool = mp.get_context("fork").Pool(procs)
     try:
         recs = [cpu_sample(n, rows, procs, pool) for _ in range(total)][args.warmup:]

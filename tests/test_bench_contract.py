@@ -1,5 +1,6 @@
-"""bench.py's reference arm (the CPU oracle timed on the host) on a small grid: one JSON line with
-the contract's keys from rank 0, nothing from the other ranks."""
+"""bench.py's reference arm (the reference's CPU path timed on the host: the unmodified reference function when
+oracle/_ref/ has been made by oracle/make_ref.py, else the oracle port) on a small grid: one JSON line with the
+contract's keys from rank 0, nothing from the other ranks."""
 import json
 import os
 import subprocess
@@ -26,7 +27,9 @@ def test_reference_arm_line():
     assert d["value"] > 0 and d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0,
                                            "d2h_bytes_per_step": 0}
     cb = d["cpu_baseline"]
-    assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and "sample" in cb
+    made = all(os.path.exists(os.path.join(ROOT, "oracle", "_ref", f)) for f in ("hypernet2D.py", "rbf_utils.py"))
+    assert cb["kind"] == ("reference" if made else "port")
+    assert cb["cores"] >= 1 and cb["value"] == d["value"] and "sample" in cb
     assert cb["cores"] == len(os.sched_getaffinity(0))          # one process per host core
     assert d["gpu_launches"] == 0 and d["config"]["grid"] == 24
 
